@@ -1,0 +1,135 @@
+// Shared declarations for libvgaligner_gpu.so (sm_100a).  Product code: never includes oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/vga.h"
+
+typedef uint64_t u64;
+typedef uint32_t u32;
+typedef int32_t i32;
+typedef int64_t i64;
+typedef uint16_t u16;
+typedef uint8_t u8;
+
+namespace vga {
+
+void set_error(const std::string& msg);
+const char* get_error();
+
+struct CudaFail { int code; };   // thrown inside the library, caught at the C boundary
+
+#define VGA_CUDA(call)                                                                              \
+    do {                                                                                            \
+        cudaError_t e__ = (call);                                                                   \
+        if (e__ != cudaSuccess) {                                                                   \
+            vga::set_error(std::string(#call) + ": " + cudaGetErrorString(e__) + " (" + __FILE__ + ":" + \
+                           std::to_string(__LINE__) + ")");                                         \
+            throw vga::CudaFail{e__ == cudaErrorMemoryAllocation ? VGA_ERR_NOMEM : VGA_ERR_CUDA};   \
+        }                                                                                           \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Device-resident index image: ONE allocation, position independent (offsets from the blob base),
+// so that a single NCCL broadcast replicates it (BASELINE.json north_star).
+// ---------------------------------------------------------------------------------------------
+struct Slot {          // open-addressed k-mer table entry, 16 B (two per 32-B DRAM sector)
+    u64 key;           // 2-bit packed k-mer
+    u32 off;           // first position in pos_tb/pos_te
+    u32 cnt;           // number of forward/forward positions; 0 = empty slot
+};
+
+struct IndexHeader {
+    u64 magic;
+    u64 bytes;          // whole image
+    u32 k, n_nodes, n_edges, L;
+    u64 n_keys, n_pos, n_slots;   // n_slots is a power of two
+    u64 off_seq_both;   // u8[2L]: seq_fwd then seq_rev (Index.seq_fwd / seq_rev, src/index.rs:45-47)
+    u64 off_seq_idx;    // u32[n_nodes+1]  NodeRef.seq_idx
+    u64 off_edge_idx;   // u32[n_nodes+1]  NodeRef.edge_idx
+    u64 off_edges_in;   // u32[n_nodes+1]  NodeRef.edges_to_node
+    u64 off_edges;      // u32[n_edges]    packed handles
+    u64 off_pos2node;   // u32[L]          rank1(seq_bv, pos) = node id of a forward position
+    u64 off_slots;      // Slot[n_slots]
+    u64 off_pos_tb;     // u32[n_pos]      KmerPos.start.position of fwd/fwd entries, table order
+    u64 off_pos_te;     // u32[n_pos]      KmerPos.end.position
+    u64 pad[8];
+};
+static const u64 INDEX_MAGIC = 0x3158444947414756ull;  // "VGAGIDX1"
+
+struct DevIndex {       // resolved device pointers, passed to kernels by value
+    u32 k, n_nodes, n_edges, L;
+    u32 slot_mask;
+    const u8* seq_both;
+    const u32* seq_idx;
+    const u32* edge_idx;
+    const u32* edges_in;
+    const u32* edges;
+    const u32* pos2node;
+    const Slot* slots;
+    const u32* pos_tb;
+    const u32* pos_te;
+};
+
+__host__ __device__ static inline u64 kmer_slot_hash(u64 key) {
+    key *= 0x9E3779B97F4A7C15ull;
+    key ^= key >> 29;
+    key *= 0xBF58476D1CE4E5B9ull;
+    key ^= key >> 32;
+    return key;
+}
+
+// ---------------------------------------------------------------------------------------------
+// POA constants shared by fill and traceback kernels
+// ---------------------------------------------------------------------------------------------
+static const i32 POA_NEG_INF = -(1 << 29);   // same sentinel as the oracle
+static const i32 POA_DEEP = -(1 << 30);      // generator value of masked cells (never wins a max)
+
+// trace cell bits (u16 per DP cell)
+enum : u16 {
+    TB_M = 1u << 0,        // some predecessor p: in band at j-1 and H(p,j-1)+s == H(i,j)
+    TB_E1 = 1u << 1,       // fresh deletion hit through E1'
+    TB_E2 = 1u << 2,       // fresh deletion hit through E2'
+    TB_HF1 = 1u << 3,      // H(i,j) == F1(i,j)
+    TB_HF2 = 1u << 4,      // H(i,j) == F2(i,j)
+    TB_E1OPEN = 1u << 5,   // H(i,j)-oe1 == E1'(i,j)
+    TB_E2OPEN = 1u << 6,
+    TB_F1OPEN = 1u << 7,   // H(i,j-1)-oe1 == F1(i,j)
+    TB_F2OPEN = 1u << 8,
+    TB_MATCH = 1u << 9,    // query base == graph base
+    TB_E1EXT = 1u << 10,   // in-node rows: E1'(i,j) == E1'(i-1,j)-e1 with (i-1,j) in band
+    TB_E2EXT = 1u << 11,
+};
+
+// per-item status while in flight (device side); final values are VGA_ALN_*
+enum : u32 {
+    IT_PENDING = 100,
+    IT_RETRY_WIDER = 101,   // band wider than 32*C columns
+    IT_RETRY_POOL = 102,    // trace pool exhausted in this wave
+};
+
+struct AlignItem {      // one (read, chain) alignment job
+    u32 read;           // read index within the chunk
+    u32 chain;          // global chain index within the chunk
+    u32 S;              // subgraph nodes
+    u32 nrows;          // subgraph bases
+    u32 qlen;
+    u32 node_base;      // into nd_* arrays
+    u32 pred_base;      // into nd_pred
+    u32 row_base;       // into row_* arrays
+    u64 q_off;          // into the chunk's read bytes
+    u32 ext_off, ext_cnt;   // extension handles in the ext pool
+    u32 min_node, max_node; // node-id range of the chain (find_range_chain)
+    u32 E;              // pred entries
+    u32 out_base;       // into per-item traceback output regions (runs)
+    u32 status;         // IT_* / VGA_ALN_*
+    i32 score;
+    u32 end_node;       // node whose last row ends the alignment
+    u32 n_runs, n_path, path_len, start_off, end_off, n_aligned;
+    u32 run_pos, path_pos;  // where the (back-to-front) traceback output starts inside its region
+    u64 cells;
+};
+
+}  // namespace vga

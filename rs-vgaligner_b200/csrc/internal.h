@@ -1,0 +1,115 @@
+// Internal declarations shared by the translation units of libvgaligner_gpu.so.
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+struct vga_workspace;
+
+struct vga_index {
+    int device = 0;
+    void* d_blob = nullptr;
+    vga::IndexHeader hdr;
+    vga::DevIndex dv;
+    vga_workspace* ws = nullptr;
+};
+
+namespace vga {
+
+extern int g_device;
+void free_workspace(vga_index* ix);
+
+// ---- stage launchers (each returns the number of kernels it launched) -----------------------
+struct SeedBuffers {
+    const char* seqs;        // chunk read bytes (device)
+    const u64* seq_off;      // n+1, absolute into seqs
+    u32 n_reads;
+    u64* read_koff;          // n+1: k-mer index range of each read
+    u32* kcnt;               // per k-mer: matching positions
+    u32* koff;               // per k-mer: first position in pos_tb/pos_te
+    u32* read_acnt;          // n: anchors per read
+    u32* read_aoff;          // n+1: exclusive scan of read_acnt
+    // anchors in emission order (i asc, table order) — Anchor{id implicit, qb, tb, te}
+    u32* a_qb; u32* a_tb; u32* a_te;
+    u32* sort_key_in; u32* sort_val_in;   // te / local id
+};
+
+int launch_read_prep(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
+int launch_seed_count(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
+int launch_seed_emit(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
+
+struct ChainBuffers {
+    u32 n_reads;
+    const u32* read_aoff;
+    const u32* a_qb; const u32* a_tb; const u32* a_te;
+    const u32* sidx;          // sorted position -> local anchor id (per read segment)
+    const double* gapcost;    // [max_gap+1]: 0.01*k*g + 0.5*log2(g), host-computed (src/chain.rs:348-354)
+    double* f;                // by sorted position
+    i32* pred;                // sorted position of the best predecessor, -1 = None (consumed by backtracking)
+    i32* pred_dbg;            // copy taken before backtracking, as anchor ids (NULL unless debug)
+    u32* n_chains;            // per read
+    u32* n_members;           // per read: total chain anchors
+    u32* clen;                // chain lengths, region of read r at read_aoff[r] + r
+    u32* cmem;                // chain members (sorted positions), region at 2*read_aoff[r] + 2*r
+    u32 k, bandwidth, max_gap, min_anchors;
+};
+int launch_chain(const ChainBuffers& b, cudaStream_t st);
+
+struct ChainGather {
+    u32 n_reads;
+    const u32* read_aoff; const u32* a_qb; const u32* a_tb; const u32* a_te; const u32* sidx;
+    const double* f;
+    const u32* n_chains; const u32* clen; const u32* cmem;
+    const u64* chain_off;     // n+1: exclusive scan of n_chains
+    const u64* member_off;    // n+1: exclusive scan of n_members
+    u64* chain_anchor_off;    // n_chains_total+1
+    u32* ca_id; u32* ca_qb; u32* ca_tb; u32* ca_te; double* ca_score;
+};
+int launch_chain_gather(const ChainGather& g, cudaStream_t st);
+
+struct SubBuffers {
+    u32 n_items;
+    AlignItem* items;
+    const char* seqs; const u64* seq_off;
+    const u64* chain_anchor_off; const u32* ca_qb; const u32* ca_tb; const u32* ca_te;
+    // extension pool (bump allocated) + per-warp BFS scratch
+    u32* ext_pool; u32 ext_cap; u32* ext_ctr; u32* overflow;
+    u32* scratch; u32 scratch_per_warp;   // u32 words per warp
+    u32 n_warps;
+    // node arrays (filled by sub_fill at AlignItem.node_base / pred_base)
+    u32* nd_handle; u32* nd_row_start; u32* nd_src; u32* nd_pred_off; u32* nd_pred; i32* nd_first_succ;
+    i32* nd_remain_last;
+};
+int launch_sub_count(const DevIndex& ix, const SubBuffers& b, cudaStream_t st);
+int launch_sub_fill(const DevIndex& ix, const SubBuffers& b, cudaStream_t st);
+
+struct PoaBuffers {
+    u32 n_items;             // entries of work[]
+    const u32* work;         // item indices to process in this launch
+    AlignItem* items;
+    const char* seqs;
+    const u32* nd_row_start; const u32* nd_src; const u32* nd_pred_off; const u32* nd_pred;
+    const i32* nd_first_succ; const i32* nd_remain_last;
+    // per node, written by the fill kernel for later rows / traceback
+    i32* nd_beg; i32* nd_end; i32* nd_lpos; i32* nd_rpos; u32* nd_store; u32* nd_ptoff;   // nd_store: pool offset (8-byte units) of the saved last row
+    // per row
+    i32* row_beg; u32* row_toff;
+    // trace pool
+    u16* pool; u64 pool_cells; unsigned long long* pool_ctr;
+    u32* work_ctr;
+    i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
+};
+int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int C, int n_sms, cudaStream_t st);
+
+struct TraceBuffers {
+    u32 n_items; const u32* work; AlignItem* items;
+    const u32* nd_row_start; const u32* nd_pred_off; const u32* nd_pred;
+    const i32* row_beg; const u32* row_toff; const u16* pool; const u32* nd_ptoff;
+    u32* out_runs;           // per item region at out_base, capacity nrows+qlen+2, written back to front
+    u32* out_path;           // per item region at node_base, capacity S, written back to front
+};
+int launch_poa_trace(const TraceBuffers& b, cudaStream_t st);
+
+double measure_int32_peak();
+
+}  // namespace vga

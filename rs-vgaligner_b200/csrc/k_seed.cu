@@ -1,0 +1,145 @@
+// K1 — seeding: anchors_for_query (reference src/chain.rs:134-173) over a batch of reads.
+//   split_into_kmers            src/io.rs:41-56      every overlapping k-mer, raw bytes
+//   find_start_position_in_index src/index.rs:309-325 membership + start offset  -> slot probe
+//   find_positions_for_query_kmer src/index.rs:353-382 positions up to the delimiter -> (off,cnt)
+// A warp owns a read.  Pass 1 (seed_count) probes the open-addressed table once per k-mer and keeps
+// (off,cnt); pass 2 (seed_emit) turns them into anchors in (query position asc, table order) —
+// the emission order of the reference, which also defines Anchor.id.
+// Roofline: HBM.  Algorithmic bytes per k-mer: 1 (read byte) + 32 (one DRAM sector per probe)
+// + 8 per position read + 16 per anchor written.
+#include "common.cuh"
+#include "internal.h"
+
+namespace vga {
+
+static const int SEED_WARPS = 8;   // warps per CTA
+
+__global__ void read_prep_kernel(const u64* __restrict__ seq_off, u32 n, u32 k, u64* __restrict__ read_koff) {
+    u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r == 0) read_koff[0] = 0;
+    if (r >= n) return;
+    u64 len = seq_off[r + 1] - seq_off[r];
+    read_koff[r + 1] = len >= k ? len - k + 1 : 0;     // src/io.rs:47
+}
+
+// 2-bit code of an uppercase ACGT byte (A0 C1 G2 T3) or 4 for anything else; a k-mer with any
+// other byte can never equal an index k-mer (index k-mers are ACGT only, src/kmer.rs:401,459).
+__device__ __forceinline__ u32 base_code(u32 c) {
+    u32 x = (c >> 1) & 3;            // A0 C1 T2 G3
+    x ^= x >> 1;                     // A0 C1 T3 G2
+    bool ok = (c == 'A') | (c == 'C') | (c == 'G') | (c == 'T');
+    return ok ? x : 4u;
+}
+
+__global__ void __launch_bounds__(SEED_WARPS * 32)
+seed_count_kernel(DevIndex ix, const char* __restrict__ seqs, const u64* __restrict__ seq_off, u32 n,
+                  const u64* __restrict__ read_koff, u32* __restrict__ kcnt, u32* __restrict__ koff,
+                  u32* __restrict__ read_acnt) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
+    const u32 k = ix.k;
+    for (u32 r = warp; r < n; r += n_warps) {
+        const u64 sb = seq_off[r];
+        const u64 kb = read_koff[r];
+        const u32 nk = (u32)(read_koff[r + 1] - kb);
+        const u8* s = (const u8*)seqs + sb;
+        u32 total = 0;
+        for (u32 i0 = 0; i0 < nk; i0 += 32) {
+            const u32 i = i0 + lane;
+            u32 cnt = 0, off = 0;
+            if (i < nk) {
+                u64 key = 0;
+                u32 bad = 0;
+                for (u32 t = 0; t < k; t++) {
+                    u32 c = base_code(s[i + t]);
+                    bad |= c & 4;
+                    key = (key << 2) | (c & 3);
+                }
+                if (!bad) {
+                    u32 h = (u32)kmer_slot_hash(key) & ix.slot_mask;
+                    while (true) {
+                        const uint4 raw = __ldg((const uint4*)(ix.slots + h));
+                        const u64 skey = ((u64)raw.y << 32) | raw.x;
+                        if (raw.w == 0) break;                      // empty slot: not in index
+                        if (skey == key) { off = raw.z; cnt = raw.w; break; }
+                        h = (h + 1) & ix.slot_mask;
+                    }
+                }
+                kcnt[kb + i] = cnt;
+                koff[kb + i] = off;
+            }
+            total += __reduce_add_sync(0xffffffffu, cnt);
+        }
+        if (lane == 0) read_acnt[r] = total;
+    }
+}
+
+__global__ void __launch_bounds__(SEED_WARPS * 32)
+seed_emit_kernel(DevIndex ix, u32 n, const u64* __restrict__ read_koff, const u32* __restrict__ kcnt,
+                 const u32* __restrict__ koff, const u32* __restrict__ read_aoff, u32* __restrict__ a_qb,
+                 u32* __restrict__ a_tb, u32* __restrict__ a_te, u32* __restrict__ sort_key,
+                 u32* __restrict__ sort_val) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (u32 r = warp; r < n; r += n_warps) {
+        const u64 kb = read_koff[r];
+        const u32 nk = (u32)(read_koff[r + 1] - kb);
+        const u32 abase = read_aoff[r];
+        if (read_aoff[r + 1] == abase) continue;
+        u32 carry = 0;
+        for (u32 i0 = 0; i0 < nk; i0 += 32) {
+            const u32 i = i0 + lane;
+            u32 cnt = 0, off = 0;
+            if (i < nk) { cnt = kcnt[kb + i]; off = koff[kb + i]; }
+            u32 incl = cnt;                                // warp inclusive scan
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                u32 t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= (u32)d) incl += t;
+            }
+            const u32 first = carry + incl - cnt;          // Anchor.id of this k-mer's first anchor
+            for (u32 t = 0; t < cnt; t++) {                // table order (src/index.rs:372-378)
+                const u32 id = first + t;
+                const u32 tb = __ldg(ix.pos_tb + off + t), te = __ldg(ix.pos_te + off + t);
+                a_qb[abase + id] = i;                      // query_begin = i, query_end = i + k
+                a_tb[abase + id] = tb;
+                a_te[abase + id] = te;
+                sort_key[abase + id] = te;
+                sort_val[abase + id] = id;
+            }
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+        }
+    }
+}
+
+static int grid_for_warps(u32 n_items, int warps_per_cta) {
+    long long ctas = ((long long)n_items + warps_per_cta - 1) / warps_per_cta;
+    const long long cap = 148 * 16;        // grid-stride beyond this
+    if (ctas > cap) ctas = cap;
+    if (ctas < 1) ctas = 1;
+    return (int)ctas;
+}
+
+int launch_read_prep(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st) {
+    u32 threads = 256, blocks = (b.n_reads + threads - 1) / threads;
+    if (blocks == 0) blocks = 1;
+    read_prep_kernel<<<blocks, threads, 0, st>>>(b.seq_off, b.n_reads, ix.k, b.read_koff);
+    return 1;
+}
+
+int launch_seed_count(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st) {
+    seed_count_kernel<<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
+        ix, b.seqs, b.seq_off, b.n_reads, b.read_koff, b.kcnt, b.koff, b.read_acnt);
+    return 1;
+}
+
+int launch_seed_emit(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st) {
+    seed_emit_kernel<<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
+        ix, b.n_reads, b.read_koff, b.kcnt, b.koff, b.read_aoff, b.a_qb, b.a_tb, b.a_te, b.sort_key_in,
+        b.sort_val_in);
+    return 1;
+}
+
+}  // namespace vga

@@ -1,0 +1,783 @@
+// vga_map_batch: the batched replacement of map_reads' per-read loops (reference src/map.rs:56-111
+// and 162-167).  Stages per chunk of reads, all on one stream:
+//   H2D reads -> K1 seeding -> K2 segmented stable sort (CUB) -> K3 chaining -> K4 subgraphs ->
+//   K5 POA fill + traceback (in waves that fit the trace pool) -> selection/compaction -> D2H.
+// No CPU fallback: every stage is a CUDA kernel of this library (or CUB scan/sort).
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstddef>
+#include <cstring>
+#include <vector>
+
+#include "common.cuh"
+#include "internal.h"
+
+using namespace vga;
+
+// ---------------------------------------------------------------------------------------------
+// workspace: grow-only device buffers reused across calls
+// ---------------------------------------------------------------------------------------------
+struct DBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    void* ensure(size_t bytes) {
+        if (bytes > cap) {
+            if (p) VGA_CUDA(cudaFree(p));
+            p = nullptr; cap = 0;
+            size_t want = bytes + bytes / 8 + 256;
+            VGA_CUDA(cudaMalloc(&p, want));
+            cap = want;
+        }
+        return p;
+    }
+    template <class T> T* get(size_t n) { return (T*)ensure(std::max<size_t>(n, 1) * sizeof(T)); }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+enum {
+    B_SEQS, B_SEQOFF, B_KOFF, B_KCNT, B_KSLOT, B_ACNT, B_AOFF, B_AQB, B_ATB, B_ATE, B_KEYIN, B_VALIN, B_KEYOUT, B_VALOUT,
+    B_CUB, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
+    B_CATE, B_CASC, B_GAP, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
+    B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDBEG, B_NDEND, B_NDL, B_NDR, B_NDST, B_NDPT, B_ROWBEG, B_ROWTOFF,
+    B_POOL, B_WORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
+    B_DBGSUBCNT, B_DBGSUBOFF, B_DBGSUB, B_DBGEDGECNT, B_DBGEDGEOFF, B_DBGEDGE, B_CELLS, B_COUNT
+};
+
+struct vga_workspace {
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev[12];
+    DBuf b[B_COUNT];
+    int n_sms = 148;
+    u32 scratch_words = 0;      // BFS scratch per warp currently allocated
+    u32 sub_warps = 0;
+    bool scratch_zeroed = false;
+    double gap_k = -1, gap_max = -1;
+};
+
+namespace vga {
+void free_workspace(vga_index* ix) {
+    if (!ix->ws) return;
+    for (auto& d : ix->ws->b) d.release();
+    for (auto& e : ix->ws->ev) cudaEventDestroy(e);
+    if (ix->ws->st) cudaStreamDestroy(ix->ws->st);
+    delete ix->ws;
+    ix->ws = nullptr;
+}
+}  // namespace vga
+
+static vga_workspace* workspace(vga_index* ix) {
+    if (ix->ws) return ix->ws;
+    vga_workspace* w = new vga_workspace();
+    VGA_CUDA(cudaStreamCreate(&w->st));
+    for (auto& e : w->ev) VGA_CUDA(cudaEventCreate(&e));
+    cudaDeviceProp prop;
+    VGA_CUDA(cudaGetDeviceProperties(&prop, ix->device));
+    w->n_sms = prop.multiProcessorCount;
+    ix->ws = w;
+    return w;
+}
+
+// ---------------------------------------------------------------------------------------------
+// results
+// ---------------------------------------------------------------------------------------------
+struct vga_results {
+    u32 n = 0;
+    std::vector<u32> n_anchors, aln_chain, aln_path_len, aln_start_off, aln_end_off, aln_n_aligned;
+    std::vector<u64> chain_off, chain_anchor_off, aln_path_off, aln_path, aln_run_off, aln_cells;
+    std::vector<u32> ca_id, ca_qb, ca_tb, ca_te, aln_runs;
+    std::vector<double> ca_score;
+    std::vector<u8> aln_status;
+    std::vector<i32> aln_score;
+    bool debug = false;
+    std::vector<u64> dbg_anchor_off, dbg_sub_off, dbg_sub_handles, dbg_edge_off;
+    std::vector<u32> dbg_qb, dbg_tb, dbg_te, dbg_sorted, dbg_edges;
+    std::vector<double> dbg_f;
+    std::vector<i32> dbg_pred;
+    VgaStats stats;
+    void begin(bool dbg) {
+        debug = dbg;
+        chain_off.assign(1, 0); chain_anchor_off.assign(1, 0); aln_path_off.assign(1, 0); aln_run_off.assign(1, 0);
+        dbg_anchor_off.assign(1, 0); dbg_sub_off.assign(1, 0); dbg_edge_off.assign(1, 0);
+        memset(&stats, 0, sizeof(stats));
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// small glue kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void item_count_kernel(const u32* n_chains, u32 n, u32 best_n, u32* cnt) {
+    u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n) cnt[r] = min(n_chains[r], best_n);      // first min(best_n, len) chains (src/align.rs:43-45)
+}
+
+__global__ void item_build_kernel(const u32* cnt, const u64* item_off, const u64* chain_off, u32 n, AlignItem* items) {
+    u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    for (u32 c = 0; c < cnt[r]; c++) {
+        AlignItem it;
+        memset(&it, 0, sizeof(it));
+        it.read = r;
+        it.chain = (u32)(chain_off[r] + c);
+        it.status = IT_PENDING;
+        items[item_off[r] + c] = it;
+    }
+}
+
+// per item: sizes[0..3] = S+1, E, nrows, nrows+qlen+2
+__global__ void item_sizes_kernel(const AlignItem* items, u32 n, u64* s0, u64* s1, u64* s2, u64* s3) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const AlignItem& it = items[i];
+    s0[i] = it.S + 1; s1[i] = it.E; s2[i] = it.nrows; s3[i] = (u64)it.nrows + it.qlen + 2;
+}
+
+__global__ void item_bases_kernel(AlignItem* items, u32 n, const u64* o0, const u64* o1, const u64* o2, const u64* o3,
+                                  u32* nrows_out, u32* qlen_out, u32* s_out) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    AlignItem& it = items[i];
+    it.node_base = (u32)o0[i]; it.pred_base = (u32)o1[i]; it.row_base = (u32)o2[i]; it.out_base = (u32)o3[i];
+    nrows_out[i] = it.nrows; qlen_out[i] = it.qlen; s_out[i] = it.S;
+}
+
+__global__ void item_status_kernel(const AlignItem* items, const u32* work, u32 n, u32* status) {
+    u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) status[i] = items[work[i]].status;
+}
+
+struct ReadScalars { u32 chain, path_len, start_off, end_off, n_aligned; i32 score; };
+
+// best_alignment_for_query (src/align.rs:34-55): stable sort by path_length descending, first wins
+__global__ void select_kernel(const AlignItem* items, const u32* cnt, const u64* item_off, u32 n, u32 max_c_status,
+                              i32* sel, u8* status, ReadScalars* sc, u64* cells, u64* run_cnt, u64* path_cnt,
+                              u64* sub_cnt, u64* edge_cnt) {
+    u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    i32 best = -1;
+    u32 best_len = 0;
+    for (u32 c = 0; c < cnt[r]; c++) {
+        const AlignItem& it = items[item_off[r] + c];
+        const u32 pl = it.status == VGA_ALN_OK ? it.path_len : 0;
+        if (best < 0 || pl > best_len) { best = (i32)(item_off[r] + c); best_len = pl; }
+    }
+    sel[r] = best;
+    ReadScalars s = {0, 0, 0, 0, 0, 0};
+    u8 st = VGA_ALN_PLACEHOLDER;
+    u64 rc = 0, pc = 0, ce = 0, sn = 0, en = 0;
+    if (best >= 0) {
+        const AlignItem& it = items[best];
+        st = (u8)(it.status >= IT_PENDING ? max_c_status : it.status);
+        s.chain = (u32)(best - (i32)item_off[r]);
+        if (it.status == VGA_ALN_OK) {
+            s.path_len = it.path_len; s.start_off = it.start_off; s.end_off = it.end_off; s.n_aligned = it.n_aligned;
+            s.score = it.score; rc = it.n_runs; pc = it.n_path;
+        }
+        ce = it.cells; sn = it.S; en = it.E;
+    }
+    status[r] = st; sc[r] = s; cells[r] = ce; run_cnt[r] = rc; path_cnt[r] = pc;
+    if (sub_cnt) { sub_cnt[r] = sn; edge_cnt[r] = en; }
+}
+
+__global__ void gather_kernel(const AlignItem* items, const i32* sel, u32 n, const u64* run_off, const u64* path_off,
+                              const u32* out_runs, const u32* out_path, const u32* nd_handle, u32* runs, u64* path) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (u32 r = warp; r < n; r += n_warps) {
+        if (sel[r] < 0) continue;
+        const AlignItem& it = items[sel[r]];
+        if (it.status != VGA_ALN_OK) continue;
+        for (u32 x = lane; x < it.n_runs; x += 32) runs[run_off[r] + x] = out_runs[it.out_base + it.run_pos + x];
+        for (u32 x = lane; x < it.n_path; x += 32)
+            path[path_off[r] + x] = nd_handle[it.node_base + out_path[it.node_base + it.path_pos + x]];
+    }
+}
+
+__global__ void dbg_sub_kernel(const AlignItem* items, const i32* sel, u32 n, const u64* sub_off, const u64* edge_off,
+                               const u32* nd_handle, const u32* nd_pred_off, const u32* nd_pred, u64* sub, u32* edges) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (u32 r = warp; r < n; r += n_warps) {
+        if (sel[r] < 0) continue;
+        const AlignItem& it = items[sel[r]];
+        for (u32 x = lane; x < it.S; x += 32) {
+            sub[sub_off[r] + x] = nd_handle[it.node_base + x];
+            const u32 pb = nd_pred_off[it.node_base + x], pe = nd_pred_off[it.node_base + x + 1];
+            for (u32 y = pb; y < pe; y++) {
+                edges[2 * (edge_off[r] + y)] = nd_pred[it.pred_base + y];
+                edges[2 * (edge_off[r] + y) + 1] = x;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// helpers
+// ---------------------------------------------------------------------------------------------
+struct Ctx {
+    vga_index* ix;
+    vga_workspace* ws;
+    cudaStream_t st;
+    const VgaParams* P;
+    vga_results* R;
+    u32 launches = 0;
+};
+
+template <class T> static T d2h_one(const T* dptr, cudaStream_t st) {
+    T v;
+    VGA_CUDA(cudaMemcpyAsync(&v, dptr, sizeof(T), cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaStreamSynchronize(st));
+    return v;
+}
+
+template <class T> static void d2h_append(std::vector<T>& dst, const T* dptr, size_t n, cudaStream_t st) {
+    size_t o = dst.size();
+    dst.resize(o + n);
+    if (n) VGA_CUDA(cudaMemcpyAsync(dst.data() + o, dptr, n * sizeof(T), cudaMemcpyDeviceToHost, st));
+}
+
+// inclusive scan of in[0..n) into out[1..n], out[0]=0  (u64 output)
+template <class InT> static void scan_to_offsets(Ctx& c, const InT* in, u64* out, u32 n) {
+    VGA_CUDA(cudaMemsetAsync(out, 0, sizeof(u64), c.st));
+    if (n == 0) return;
+    size_t tb = 0;
+    cub::DeviceScan::InclusiveSum(nullptr, tb, in, out + 1, (int)n, c.st);
+    void* tmp = c.ws->b[B_CUB].ensure(tb);
+    VGA_CUDA(cub::DeviceScan::InclusiveSum(tmp, tb, in, out + 1, (int)n, c.st));
+    c.launches += 2;
+}
+
+static void scan_to_offsets_u32(Ctx& c, const u32* in, u32* out, u32 n) {
+    VGA_CUDA(cudaMemsetAsync(out, 0, sizeof(u32), c.st));
+    if (n == 0) return;
+    size_t tb = 0;
+    cub::DeviceScan::InclusiveSum(nullptr, tb, in, out + 1, (int)n, c.st);
+    void* tmp = c.ws->b[B_CUB].ensure(tb);
+    VGA_CUDA(cub::DeviceScan::InclusiveSum(tmp, tb, in, out + 1, (int)n, c.st));
+    c.launches += 2;
+}
+
+static void upload_gapcost(Ctx& c, u32 k, u32 max_gap) {
+    vga_workspace* w = c.ws;
+    if (w->gap_k == k && w->gap_max == max_gap) return;
+    // gamma_c of the reference, evaluated on the host exactly as written (src/chain.rs:348-354):
+    // 0.01 * seed_length * gap_length + 0.5 * log2(gap_length); entry 0 is the `gap_length == 0` arm.
+    std::vector<double> g(max_gap + 1);
+    g[0] = 0.0;
+    for (u32 x = 1; x <= max_gap; x++) {
+        volatile double a = 0.01 * (double)k;
+        volatile double b = a * (double)x;
+        volatile double l = 0.5 * std::log2((double)x);
+        g[x] = b + l;
+    }
+    double* d = w->b[B_GAP].get<double>(max_gap + 1);
+    VGA_CUDA(cudaMemcpyAsync(d, g.data(), g.size() * sizeof(double), cudaMemcpyHostToDevice, c.st));
+    VGA_CUDA(cudaStreamSynchronize(c.st));
+    w->gap_k = k; w->gap_max = max_gap;
+}
+
+static int class_for_width(i64 w) {
+    int C = 1;
+    while (32 * C < w && C < 32) C <<= 1;
+    return C;
+}
+
+// ---------------------------------------------------------------------------------------------
+// one chunk of reads already resident on the device
+// returns false when the chunk must be split (too many anchors for 32-bit offsets)
+// ---------------------------------------------------------------------------------------------
+static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 n, u64 n_bases) {
+    vga_workspace* w = c.ws;
+    cudaStream_t st = c.st;
+    const DevIndex& dv = c.ix->dv;
+    const VgaParams& P = *c.P;
+    vga_results& R = *c.R;
+    const bool dbg = P.flags & VGA_FLAG_KEEP_DEBUG;
+    VGA_CUDA(cudaEventRecord(w->ev[0], st));
+    // ---- K1 seeding
+    SeedBuffers sb;
+    sb.seqs = d_seqs; sb.seq_off = d_seq_off; sb.n_reads = n;
+    sb.read_koff = w->b[B_KOFF].get<u64>(n + 1);
+    c.launches += launch_read_prep(dv, sb, st);
+    {
+        size_t tb = 0;
+        cub::DeviceScan::InclusiveSum(nullptr, tb, sb.read_koff + 1, sb.read_koff + 1, (int)n, st);
+        void* tmp = w->b[B_CUB].ensure(tb);
+        VGA_CUDA(cub::DeviceScan::InclusiveSum(tmp, tb, sb.read_koff + 1, sb.read_koff + 1, (int)n, st));
+        c.launches += 2;
+    }
+    const u64 total_k = d2h_one(sb.read_koff + n, st);
+    sb.kcnt = w->b[B_KCNT].get<u32>(total_k);
+    sb.koff = w->b[B_KSLOT].get<u32>(total_k);
+    sb.read_acnt = w->b[B_ACNT].get<u32>(n);
+    sb.read_aoff = w->b[B_AOFF].get<u32>(n + 1);
+    c.launches += launch_seed_count(dv, sb, st);
+    {   // anchors may not exceed 2^31 per chunk (CUB segmented sort takes int counts)
+        u64* tmp64 = w->b[B_SZOFF].get<u64>(n + 1);
+        scan_to_offsets(c, sb.read_acnt, tmp64, n);
+        const u64 total64 = d2h_one(tmp64 + n, st);
+        if (total64 >= (1ull << 31) - 1) return false;
+    }
+    scan_to_offsets_u32(c, sb.read_acnt, sb.read_aoff, n);
+    const u32 A = d2h_one(sb.read_aoff + n, st);
+    sb.a_qb = w->b[B_AQB].get<u32>(A); sb.a_tb = w->b[B_ATB].get<u32>(A); sb.a_te = w->b[B_ATE].get<u32>(A);
+    sb.sort_key_in = w->b[B_KEYIN].get<u32>(A); sb.sort_val_in = w->b[B_VALIN].get<u32>(A);
+    u32* key_out = w->b[B_KEYOUT].get<u32>(A);
+    u32* val_out = w->b[B_VALOUT].get<u32>(A);
+    c.launches += launch_seed_emit(dv, sb, st);
+    VGA_CUDA(cudaEventRecord(w->ev[1], st));
+    // ---- K2 per-read stable sort by target_end.position (src/chain.rs:386-389)
+    if (A > 0) {
+        size_t tb = 0;
+        cub::DeviceSegmentedSort::StableSortPairs(nullptr, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out, (int)A,
+                                                  (int)n, sb.read_aoff, sb.read_aoff + 1, st);
+        void* tmp = w->b[B_CUB].ensure(tb);
+        VGA_CUDA(cub::DeviceSegmentedSort::StableSortPairs(tmp, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out,
+                                                           (int)A, (int)n, sb.read_aoff, sb.read_aoff + 1, st));
+        c.launches += 3;
+    }
+    VGA_CUDA(cudaEventRecord(w->ev[2], st));
+    // ---- K3 chaining
+    upload_gapcost(c, dv.k, P.max_gap);
+    ChainBuffers cb;
+    cb.n_reads = n; cb.read_aoff = sb.read_aoff; cb.a_qb = sb.a_qb; cb.a_tb = sb.a_tb; cb.a_te = sb.a_te;
+    cb.sidx = val_out; cb.gapcost = (const double*)w->b[B_GAP].p;
+    cb.f = w->b[B_F].get<double>(A); cb.pred = w->b[B_PRED].get<i32>(A);
+    cb.pred_dbg = dbg ? w->b[B_PREDDBG].get<i32>(A) : nullptr;
+    cb.n_chains = w->b[B_NCH].get<u32>(n); cb.n_members = w->b[B_NMEM].get<u32>(n);
+    cb.clen = w->b[B_CLEN].get<u32>((u64)A + n); cb.cmem = w->b[B_CMEM].get<u32>(2ull * A + 2ull * n);
+    cb.k = dv.k; cb.bandwidth = P.bandwidth; cb.max_gap = P.max_gap; cb.min_anchors = P.min_anchors;
+    c.launches += launch_chain(cb, st);
+    u64* chain_off = w->b[B_CHOFF].get<u64>(n + 1);
+    u64* member_off = w->b[B_MEMOFF].get<u64>(n + 1);
+    scan_to_offsets(c, cb.n_chains, chain_off, n);
+    scan_to_offsets(c, cb.n_members, member_off, n);
+    const u64 NC = d2h_one(chain_off + n, st), NM = d2h_one(member_off + n, st);
+    ChainGather cg;
+    cg.n_reads = n; cg.read_aoff = sb.read_aoff; cg.a_qb = sb.a_qb; cg.a_tb = sb.a_tb; cg.a_te = sb.a_te; cg.sidx = val_out;
+    cg.f = cb.f; cg.n_chains = cb.n_chains; cg.clen = cb.clen; cg.cmem = cb.cmem; cg.chain_off = chain_off;
+    cg.member_off = member_off;
+    cg.chain_anchor_off = w->b[B_CAOFF].get<u64>(NC + 1);
+    cg.ca_id = w->b[B_CAID].get<u32>(NM); cg.ca_qb = w->b[B_CAQB].get<u32>(NM); cg.ca_tb = w->b[B_CATB].get<u32>(NM);
+    cg.ca_te = w->b[B_CATE].get<u32>(NM); cg.ca_score = w->b[B_CASC].get<double>(NM);
+    c.launches += launch_chain_gather(cg, st);
+    VGA_CUDA(cudaEventRecord(w->ev[3], st));
+
+    // ---- per-chunk result bookkeeping (chains)
+    const u64 chain_base = R.chain_anchor_off.size() - 1, member_base = R.ca_id.size();
+    d2h_append(R.n_anchors, sb.read_acnt, n, st);
+    std::vector<u64> h_chain_off(n + 1), h_caoff(NC + 1);
+    VGA_CUDA(cudaMemcpyAsync(h_chain_off.data(), chain_off, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaMemcpyAsync(h_caoff.data(), cg.chain_anchor_off, (NC + 1) * 8, cudaMemcpyDeviceToHost, st));
+    d2h_append(R.ca_id, cg.ca_id, NM, st); d2h_append(R.ca_qb, cg.ca_qb, NM, st); d2h_append(R.ca_tb, cg.ca_tb, NM, st);
+    d2h_append(R.ca_te, cg.ca_te, NM, st); d2h_append(R.ca_score, cg.ca_score, NM, st);
+    if (dbg) {
+        std::vector<u32> h_aoff(n + 1);
+        VGA_CUDA(cudaMemcpyAsync(h_aoff.data(), sb.read_aoff, (n + 1) * 4, cudaMemcpyDeviceToHost, st));
+        const u64 abase = R.dbg_qb.size();
+        d2h_append(R.dbg_qb, sb.a_qb, A, st); d2h_append(R.dbg_tb, sb.a_tb, A, st); d2h_append(R.dbg_te, sb.a_te, A, st);
+        d2h_append(R.dbg_sorted, val_out, A, st); d2h_append(R.dbg_f, cb.f, A, st); d2h_append(R.dbg_pred, cb.pred_dbg, A, st);
+        VGA_CUDA(cudaStreamSynchronize(st));
+        for (u32 i = 1; i <= n; i++) R.dbg_anchor_off.push_back(abase + h_aoff[i]);
+    }
+    VGA_CUDA(cudaStreamSynchronize(st));
+    for (u32 i = 1; i <= n; i++) R.chain_off.push_back(chain_base + h_chain_off[i]);
+    for (u64 i = 1; i <= NC; i++) R.chain_anchor_off.push_back(member_base + h_caoff[i]);
+    R.stats.n_probes += total_k; R.stats.n_anchors += A; R.stats.n_positions_read += A; R.stats.n_chains += NC;
+    R.stats.n_bases += n_bases;
+    R.stats.lookup_bytes += n_bases + 32ull * total_k + 8ull * A + 16ull * A;
+
+    // ---- alignment
+    u32 NI = 0;
+    u32* item_cnt = w->b[B_ITEMCNT].get<u32>(n);
+    u64* item_off = w->b[B_ITEMOFF].get<u64>(n + 1);
+    AlignItem* items = nullptr;
+    if (!(P.flags & VGA_FLAG_NO_ALIGN)) {
+        item_count_kernel<<<(n + 255) / 256, 256, 0, st>>>(cb.n_chains, n, P.best_n, item_cnt);
+        c.launches++;
+        scan_to_offsets(c, item_cnt, item_off, n);
+        NI = (u32)d2h_one(item_off + n, st);
+    }
+    const size_t rbase = R.aln_status.size();
+    if (NI == 0) {
+        // every read is a placeholder (or alignment was not requested)
+        R.aln_status.resize(rbase + n, VGA_ALN_PLACEHOLDER); R.aln_chain.resize(rbase + n, 0);
+        R.aln_path_len.resize(rbase + n, 0); R.aln_start_off.resize(rbase + n, 0); R.aln_end_off.resize(rbase + n, 0);
+        R.aln_n_aligned.resize(rbase + n, 0); R.aln_score.resize(rbase + n, 0); R.aln_cells.resize(rbase + n, 0);
+        for (u32 i = 0; i < n; i++) { R.aln_path_off.push_back(R.aln_path.size()); R.aln_run_off.push_back(R.aln_runs.size()); }
+        if (dbg) for (u32 i = 0; i < n; i++) { R.dbg_sub_off.push_back(R.dbg_sub_handles.size()); R.dbg_edge_off.push_back(R.dbg_edges.size() / 2); }
+        VGA_CUDA(cudaEventRecord(w->ev[4], st)); VGA_CUDA(cudaEventRecord(w->ev[5], st)); VGA_CUDA(cudaEventRecord(w->ev[6], st));
+        VGA_CUDA(cudaEventRecord(w->ev[7], st));
+        return true;
+    }
+    items = w->b[B_ITEMS].get<AlignItem>(NI);
+    item_build_kernel<<<(n + 255) / 256, 256, 0, st>>>(item_cnt, item_off, chain_off, n, items);
+    c.launches++;
+    // ---- K4 subgraphs
+    SubBuffers sub;
+    memset(&sub, 0, sizeof(sub));
+    sub.n_items = NI; sub.items = items; sub.seqs = d_seqs; sub.seq_off = d_seq_off;
+    sub.chain_anchor_off = cg.chain_anchor_off; sub.ca_qb = cg.ca_qb; sub.ca_tb = cg.ca_tb; sub.ca_te = cg.ca_te;
+    u32* ctr = w->b[B_CTR].get<u32>(16);     // [0] ext ctr, [1] overflow, [2] work ctr, [4..5] pool ctr (u64)
+    u32 ext_cap = std::max<u32>(1u << 16, NI * 8);
+    for (int attempt = 0;; attempt++) {
+        if (w->scratch_words == 0) { w->scratch_words = 1u << 15; w->scratch_zeroed = false; }
+        const u32 want_warps = std::min<u32>((u32)w->n_sms * 32, std::max<u32>(NI, 4));
+        if (want_warps != w->sub_warps) { w->sub_warps = want_warps; w->scratch_zeroed = false; }
+        const u64 sbytes = (u64)w->sub_warps * w->scratch_words * 4;
+        void* prevp = w->b[B_SCRATCH].p;
+        u32* scratch = (u32*)w->b[B_SCRATCH].ensure(sbytes);
+        if (scratch != prevp) w->scratch_zeroed = false;
+        if (!w->scratch_zeroed) { VGA_CUDA(cudaMemsetAsync(scratch, 0, sbytes, st)); w->scratch_zeroed = true; }
+        sub.ext_pool = w->b[B_EXT].get<u32>(ext_cap); sub.ext_cap = ext_cap;
+        sub.ext_ctr = ctr; sub.overflow = ctr + 1;
+        sub.scratch = scratch; sub.scratch_per_warp = w->scratch_words; sub.n_warps = w->sub_warps;
+        VGA_CUDA(cudaMemsetAsync(ctr, 0, 64, st));
+        c.launches += launch_sub_count(dv, sub, st);
+        u32 h[2];
+        VGA_CUDA(cudaMemcpyAsync(h, ctr, 8, cudaMemcpyDeviceToHost, st));
+        VGA_CUDA(cudaStreamSynchronize(st));
+        if (!h[1]) break;
+        if (attempt >= 12) { set_error("subgraph extension exceeded the scratch limits"); throw CudaFail{VGA_ERR_NOMEM}; }
+        if (h[0] > ext_cap) ext_cap = h[0] + h[0] / 4 + 1024;      // the counter kept counting: exact need is known
+        else { w->scratch_words *= 2; w->scratch_zeroed = false; }
+    }
+    u64* sz = w->b[B_SZ].get<u64>(4ull * NI);
+    u64* szo = w->b[B_SZOFF].get<u64>(4ull * (NI + 1));
+    item_sizes_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, sz, sz + NI, sz + 2ull * NI, sz + 3ull * NI);
+    c.launches++;
+    u64 tot[4];
+    for (int q = 0; q < 4; q++) {
+        scan_to_offsets(c, sz + (u64)q * NI, szo + (u64)q * (NI + 1), NI);
+        tot[q] = d2h_one(szo + (u64)q * (NI + 1) + NI, st);
+    }
+    for (int q = 0; q < 4; q++)
+        if (tot[q] >= (1ull << 32)) { set_error("alignment batch exceeds 32-bit offsets; use smaller batches"); throw CudaFail{VGA_ERR_UNSUPPORTED}; }
+    u32* d_nrows = w->b[B_RCNT].get<u32>(3ull * NI);
+    item_bases_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, szo, szo + (NI + 1), szo + 2ull * (NI + 1), szo + 3ull * (NI + 1),
+                                                        d_nrows, d_nrows + NI, d_nrows + 2ull * NI);
+    c.launches++;
+    sub.nd_handle = w->b[B_NDH].get<u32>(tot[0]); sub.nd_row_start = w->b[B_NDRS].get<u32>(tot[0]);
+    sub.nd_src = w->b[B_NDSRC].get<u32>(tot[0]); sub.nd_pred_off = w->b[B_NDPO].get<u32>(tot[0]);
+    sub.nd_pred = w->b[B_NDPRED].get<u32>(tot[1]); sub.nd_first_succ = w->b[B_NDFS].get<i32>(tot[0]);
+    sub.nd_remain_last = w->b[B_NDRL].get<i32>(tot[0]);
+    c.launches += launch_sub_fill(dv, sub, st);
+    std::vector<u32> h_meta(3ull * NI);
+    VGA_CUDA(cudaMemcpyAsync(h_meta.data(), d_nrows, 12ull * NI, cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaEventRecord(w->ev[4], st));
+    VGA_CUDA(cudaStreamSynchronize(st));
+    // ---- K5 POA in waves
+    PoaBuffers pb;
+    memset(&pb, 0, sizeof(pb));
+    pb.items = items; pb.seqs = d_seqs;
+    pb.nd_row_start = sub.nd_row_start; pb.nd_src = sub.nd_src; pb.nd_pred_off = sub.nd_pred_off; pb.nd_pred = sub.nd_pred;
+    pb.nd_first_succ = sub.nd_first_succ; pb.nd_remain_last = sub.nd_remain_last;
+    pb.nd_beg = w->b[B_NDBEG].get<i32>(tot[0]); pb.nd_end = w->b[B_NDEND].get<i32>(tot[0]);
+    pb.nd_lpos = w->b[B_NDL].get<i32>(tot[0]); pb.nd_rpos = w->b[B_NDR].get<i32>(tot[0]);
+    pb.nd_store = w->b[B_NDST].get<u32>(tot[0]); pb.nd_ptoff = w->b[B_NDPT].get<u32>(tot[0]);
+    pb.row_beg = w->b[B_ROWBEG].get<i32>(tot[2]); pb.row_toff = w->b[B_ROWTOFF].get<u32>(tot[2]);
+    pb.match = P.match; pb.mismatch = P.mismatch; pb.o1 = P.o1; pb.e1 = P.e1; pb.o2 = P.o2; pb.e2 = P.e2; pb.wb = P.wb; pb.wf = P.wf;
+    pb.work_ctr = ctr + 2; pb.pool_ctr = (unsigned long long*)(ctr + 4);
+    TraceBuffers tbuf;
+    memset(&tbuf, 0, sizeof(tbuf));
+    tbuf.items = items; tbuf.nd_row_start = sub.nd_row_start; tbuf.nd_pred_off = sub.nd_pred_off; tbuf.nd_pred = sub.nd_pred;
+    tbuf.row_beg = pb.row_beg; tbuf.row_toff = pb.row_toff; tbuf.nd_ptoff = pb.nd_ptoff;
+    tbuf.out_runs = w->b[B_OUTRUNS].get<u32>(tot[3]); tbuf.out_path = w->b[B_OUTPATH].get<u32>(tot[0]);
+    // estimated cells per item and its column class
+    std::vector<u64> est(NI);
+    std::vector<std::vector<u32>> cls(6);     // C = 1,2,4,8,16,32
+    u64 est_total = 0;
+    for (u32 i = 0; i < NI; i++) {
+        const i64 nrows = h_meta[i], qlen = h_meta[NI + i], S = h_meta[2ull * NI + i];
+        const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
+        const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
+        est[i] = (u64)((nrows + 9 * S) * (west + 4));
+        est_total += est[i];
+        int C = class_for_width(west), ci = 0;
+        while ((1 << ci) < C) ci++;
+        cls[ci].push_back(i);
+    }
+    size_t free_b = 0, total_b = 0;
+    VGA_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    const u64 warp_slack = (u64)w->n_sms * 64 * 16384;
+    u64 want_cells = est_total + est_total / 4 + warp_slack;
+    u64 max_cells = (u64)((free_b + w->b[B_POOL].cap) * 0.6) / 2;
+    if (want_cells > max_cells) want_cells = max_cells;
+    if (want_cells < (1ull << 24)) want_cells = 1ull << 24;
+    pb.pool = w->b[B_POOL].get<u16>(want_cells);
+    pb.pool_cells = w->b[B_POOL].cap / 2;
+    tbuf.pool = pb.pool;
+    u32* d_work = w->b[B_WORK].get<u32>(NI);
+    u32* d_status = w->b[B_STATUS].get<u32>(NI);
+    std::vector<u32> h_status(NI);
+    float ms_fill = 0, ms_trace = 0;
+    for (int ci = 0; ci < 6; ci++) {
+        std::vector<u32>& list = cls[ci];
+        size_t pos = 0;
+        int stall = 0;
+        while (pos < list.size()) {
+            // take a wave whose estimate fits the pool
+            u64 acc = warp_slack;
+            size_t end = pos;
+            while (end < list.size() && (end == pos || acc + est[list[end]] + est[list[end]] / 4 <= pb.pool_cells)) {
+                acc += est[list[end]] + est[list[end]] / 4;
+                end++;
+            }
+            const u32 nw = (u32)(end - pos);
+            VGA_CUDA(cudaMemcpyAsync(d_work, list.data() + pos, 4ull * nw, cudaMemcpyHostToDevice, st));
+            VGA_CUDA(cudaMemsetAsync(ctr + 2, 0, 24, st));
+            pb.n_items = nw; pb.work = d_work;
+            tbuf.n_items = nw; tbuf.work = d_work;
+            VGA_CUDA(cudaEventRecord(w->ev[8], st));
+            c.launches += launch_poa_fill(dv, pb, 1 << ci, w->n_sms, st);
+            VGA_CUDA(cudaEventRecord(w->ev[9], st));
+            c.launches += launch_poa_trace(tbuf, st);
+            VGA_CUDA(cudaEventRecord(w->ev[10], st));
+            item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
+            c.launches++;
+            VGA_CUDA(cudaMemcpyAsync(h_status.data(), d_status, 4ull * nw, cudaMemcpyDeviceToHost, st));
+            VGA_CUDA(cudaStreamSynchronize(st));
+            float a = 0, bms = 0;
+            cudaEventElapsedTime(&a, w->ev[8], w->ev[9]); cudaEventElapsedTime(&bms, w->ev[9], w->ev[10]);
+            ms_fill += a; ms_trace += bms;
+            std::vector<u32> again;
+            u32 done = 0;
+            for (u32 x = 0; x < nw; x++) {
+                const u32 it = list[pos + x];
+                if (h_status[x] == IT_RETRY_WIDER) { if (ci < 5) cls[ci + 1].push_back(it); else done++; }
+                else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
+                else done++;
+            }
+            pos = end;
+            if (!again.empty()) {
+                if (done == 0 && again.size() == nw) {
+                    // nothing fitted: the pool is too small for even one alignment of this wave
+                    if (++stall > 2) { set_error("POA trace pool too small for a single alignment"); throw CudaFail{VGA_ERR_NOMEM}; }
+                    for (u32 it : again) est[it] *= 4;
+                }
+                list.insert(list.end(), again.begin(), again.end());
+            }
+        }
+    }
+    VGA_CUDA(cudaEventRecord(w->ev[5], st));
+    // ---- selection + compaction
+    i32* sel = w->b[B_SEL].get<i32>(n);
+    u8* d_st8 = (u8*)w->b[B_STATUS].ensure(std::max<size_t>(4ull * NI, n));
+    ReadScalars* d_sc = w->b[B_SCAL].get<ReadScalars>(n);
+    u64* d_cells = w->b[B_CELLS].get<u64>(n);
+    u64* cnts = w->b[B_PCNT].get<u64>(4ull * n);
+    u64* offs = w->b[B_POFF2].get<u64>(4ull * (n + 1));
+    select_kernel<<<(n + 255) / 256, 256, 0, st>>>(items, item_cnt, item_off, n, 6u, sel, d_st8, d_sc, d_cells, cnts, cnts + n,
+                                                   dbg ? cnts + 2ull * n : nullptr, cnts + 3ull * n);
+    c.launches++;
+    const int nscan = dbg ? 4 : 2;
+    u64 tots[4] = {0, 0, 0, 0};
+    for (int q = 0; q < nscan; q++) {
+        scan_to_offsets(c, cnts + (u64)q * n, offs + (u64)q * (n + 1), n);
+        tots[q] = d2h_one(offs + (u64)q * (n + 1) + n, st);
+    }
+    u32* d_runs = w->b[B_RUNS].get<u32>(tots[0]);
+    u64* d_path = w->b[B_PATH].get<u64>(tots[1]);
+    gather_kernel<<<std::min<u32>((n + 7) / 8, 148 * 16), 256, 0, st>>>(items, sel, n, offs, offs + (n + 1), tbuf.out_runs,
+                                                                         tbuf.out_path, sub.nd_handle, d_runs, d_path);
+    c.launches++;
+    VGA_CUDA(cudaEventRecord(w->ev[6], st));
+    // ---- D2H of the alignment results
+    std::vector<ReadScalars> h_sc(n);
+    std::vector<u64> h_roff(n + 1), h_poff(n + 1);
+    VGA_CUDA(cudaMemcpyAsync(h_sc.data(), d_sc, n * sizeof(ReadScalars), cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaMemcpyAsync(h_roff.data(), offs, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaMemcpyAsync(h_poff.data(), offs + (n + 1), (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    const u64 run_base = R.aln_runs.size(), path_base = R.aln_path.size();
+    d2h_append(R.aln_status, d_st8, n, st);
+    d2h_append(R.aln_cells, d_cells, n, st);
+    d2h_append(R.aln_runs, d_runs, tots[0], st);
+    d2h_append(R.aln_path, d_path, tots[1], st);
+    std::vector<u64> h_soff, h_eoff;
+    if (dbg) {
+        u64* d_sub = w->b[B_DBGSUB].get<u64>(tots[2]);
+        u32* d_edges = w->b[B_DBGEDGE].get<u32>(2 * tots[3]);
+        dbg_sub_kernel<<<std::min<u32>((n + 7) / 8, 148 * 16), 256, 0, st>>>(items, sel, n, offs + 2ull * (n + 1), offs + 3ull * (n + 1),
+                                                                              sub.nd_handle, sub.nd_pred_off, sub.nd_pred, d_sub, d_edges);
+        c.launches++;
+        h_soff.resize(n + 1); h_eoff.resize(n + 1);
+        VGA_CUDA(cudaMemcpyAsync(h_soff.data(), offs + 2ull * (n + 1), (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+        VGA_CUDA(cudaMemcpyAsync(h_eoff.data(), offs + 3ull * (n + 1), (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+        const u64 sbase = R.dbg_sub_handles.size(), ebase = R.dbg_edges.size() / 2;
+        d2h_append(R.dbg_sub_handles, d_sub, tots[2], st);
+        d2h_append(R.dbg_edges, d_edges, 2 * tots[3], st);
+        VGA_CUDA(cudaStreamSynchronize(st));
+        for (u32 i = 1; i <= n; i++) { R.dbg_sub_off.push_back(sbase + h_soff[i]); R.dbg_edge_off.push_back(ebase + h_eoff[i]); }
+    }
+    // total cells over all items (GCUPS numerator)
+    {
+        std::vector<u64> h_cells(NI);
+        VGA_CUDA(cudaMemcpy2DAsync(h_cells.data(), 8, (const char*)items + offsetof(AlignItem, cells), sizeof(AlignItem), 8, NI,
+                                   cudaMemcpyDeviceToHost, st));
+        VGA_CUDA(cudaStreamSynchronize(st));
+        for (u64 v : h_cells) R.stats.poa_cells += v;
+    }
+    VGA_CUDA(cudaEventRecord(w->ev[7], st));
+    VGA_CUDA(cudaStreamSynchronize(st));
+    for (u32 i = 0; i < n; i++) {
+        R.aln_chain.push_back(h_sc[i].chain); R.aln_path_len.push_back(h_sc[i].path_len);
+        R.aln_start_off.push_back(h_sc[i].start_off); R.aln_end_off.push_back(h_sc[i].end_off);
+        R.aln_n_aligned.push_back(h_sc[i].n_aligned); R.aln_score.push_back(h_sc[i].score);
+        R.aln_run_off.push_back(run_base + h_roff[i + 1]); R.aln_path_off.push_back(path_base + h_poff[i + 1]);
+    }
+    R.stats.n_alignments += NI;
+    R.stats.ms_poa += ms_fill; R.stats.ms_trace += ms_trace;
+    return true;
+}
+
+static void add_stage_times(Ctx& c) {
+    vga_workspace* w = c.ws;
+    float t;
+    VgaStats& s = c.R->stats;
+    if (cudaEventElapsedTime(&t, w->ev[0], w->ev[1]) == cudaSuccess) s.ms_seed += t;
+    if (cudaEventElapsedTime(&t, w->ev[1], w->ev[2]) == cudaSuccess) s.ms_sort += t;
+    if (cudaEventElapsedTime(&t, w->ev[2], w->ev[3]) == cudaSuccess) s.ms_chain += t;
+    if (cudaEventElapsedTime(&t, w->ev[3], w->ev[4]) == cudaSuccess) s.ms_subgraph += t;
+    if (cudaEventElapsedTime(&t, w->ev[6], w->ev[7]) == cudaSuccess) s.ms_d2h += t;
+    cudaGetLastError();
+}
+
+// chunk driver: reads [b,e) whose bytes are resident at d_seqs (offsets absolute into d_seqs)
+static void run_range(Ctx& c, const char* d_seqs, const u64* d_seq_off, const u64* h_seq_off, u32 b, u32 e) {
+    if (b >= e) return;
+    const u64 bases = h_seq_off[e] - h_seq_off[b];
+    const u64 MAX_BASES = 96ull << 20;
+    const u32 MAX_READS = 1u << 20;
+    bool split = (e - b > 1) && (bases > MAX_BASES || e - b > MAX_READS);
+    if (!split) {
+        if (process_chunk(c, d_seqs, d_seq_off + b, e - b, bases)) { add_stage_times(c); return; }
+        if (e - b == 1) { set_error("a single read produced more than 2^31 anchors"); throw CudaFail{VGA_ERR_UNSUPPORTED}; }
+    }
+    const u32 mid = b + (e - b) / 2;
+    run_range(c, d_seqs, d_seq_off, h_seq_off, b, mid);
+    run_range(c, d_seqs, d_seq_off, h_seq_off, mid, e);
+}
+
+static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, const char* d_seqs_in, const u64* d_off_in,
+                      u32 n_reads, u64 n_bases_in, const VgaParams* params, vga_results_t** out) {
+    if (!ix || !out || !params || (n_reads && (!seq_off && !d_off_in))) { set_error("vga_map_batch: null argument"); return VGA_ERR_INVALID; }
+    *out = nullptr;
+    if (params->bandwidth == 0 || params->bandwidth > 96) { set_error("chaining bandwidth must be in 1..96"); return VGA_ERR_UNSUPPORTED; }
+    if (params->best_n == 0 || params->min_anchors == 0) { set_error("best_n and min_anchors must be >= 1"); return VGA_ERR_INVALID; }
+    if (params->max_gap > (1u << 24)) { set_error("max_gap too large"); return VGA_ERR_UNSUPPORTED; }
+    vga_results* R = new vga_results();
+    try {
+        VGA_CUDA(cudaSetDevice(ix->device));
+        Ctx c;
+        c.ix = ix; c.ws = workspace(ix); c.st = c.ws->st; c.P = params; c.R = R;
+        R->n = n_reads;
+        R->begin(params->flags & VGA_FLAG_KEEP_DEBUG);
+        cudaEvent_t t0 = c.ws->ev[11];
+        std::vector<u64> h_off;
+        const char* d_seqs = d_seqs_in;
+        const u64* d_off = d_off_in;
+        VGA_CUDA(cudaEventRecord(t0, c.st));
+        auto wall0 = std::chrono::steady_clock::now();
+        if (n_reads > 0) {
+            if (!d_seqs_in) {
+                for (u32 i = 0; i < n_reads; i++)
+                    if (seq_off[i + 1] < seq_off[i]) { set_error("seq_off not monotone"); delete R; return VGA_ERR_INVALID; }
+                const u64 nb = seq_off[n_reads] - seq_off[0];
+                char* ds = c.ws->b[B_SEQS].get<char>(nb + 16);
+                u64* doff = c.ws->b[B_SEQOFF].get<u64>(n_reads + 1);
+                h_off.resize(n_reads + 1);
+                for (u32 i = 0; i <= n_reads; i++) h_off[i] = seq_off[i] - seq_off[0];
+                VGA_CUDA(cudaMemcpyAsync(ds, seqs + seq_off[0], nb, cudaMemcpyHostToDevice, c.st));
+                VGA_CUDA(cudaMemcpyAsync(doff, h_off.data(), (n_reads + 1) * 8, cudaMemcpyHostToDevice, c.st));
+                d_seqs = ds; d_off = doff;
+            } else {
+                h_off.resize(n_reads + 1);
+                VGA_CUDA(cudaMemcpyAsync(h_off.data(), d_off_in, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, c.st));
+                VGA_CUDA(cudaStreamSynchronize(c.st));
+                (void)n_bases_in;
+            }
+            VGA_CUDA(cudaEventRecord(c.ws->ev[0], c.st));
+            float th2d = 0;
+            VGA_CUDA(cudaStreamSynchronize(c.st));
+            cudaEventElapsedTime(&th2d, t0, c.ws->ev[0]);
+            R->stats.ms_h2d = th2d;
+            run_range(c, d_seqs, d_off, h_off.data(), 0, n_reads);
+        }
+        VGA_CUDA(cudaStreamSynchronize(c.st));
+        R->stats.ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+        R->stats.n_reads = n_reads;
+        R->stats.kernel_launches = c.launches;
+    } catch (CudaFail& f) {
+        delete R;
+        return f.code;
+    } catch (std::bad_alloc&) {
+        delete R;
+        set_error("host allocation failed");
+        return VGA_ERR_NOMEM;
+    }
+    *out = R;
+    return VGA_OK;
+}
+
+extern "C" {
+
+int vga_map_batch(vga_index_t* ix, const char* seqs, const uint64_t* seq_off, uint32_t n_reads, const VgaParams* params,
+                  vga_results_t** out) {
+    if (n_reads && !seqs) { set_error("vga_map_batch: seqs is null"); return VGA_ERR_INVALID; }
+    return map_common(ix, seqs, seq_off, nullptr, nullptr, n_reads, 0, params, out);
+}
+
+int vga_map_batch_device(vga_index_t* ix, const char* dev_seqs, const uint64_t* dev_seq_off, uint32_t n_reads, uint64_t n_bases,
+                         const VgaParams* params, vga_results_t** out) {
+    if (n_reads && (!dev_seqs || !dev_seq_off)) { set_error("vga_map_batch_device: null device pointer"); return VGA_ERR_INVALID; }
+    return map_common(ix, nullptr, nullptr, dev_seqs, dev_seq_off, n_reads, n_bases, params, out);
+}
+
+int vga_results_view(const vga_results_t* r, VgaResultsView* v) {
+    if (!r || !v) { set_error("null argument"); return VGA_ERR_INVALID; }
+    memset(v, 0, sizeof(*v));
+    v->n_reads = r->n;
+    v->n_anchors = r->n_anchors.data(); v->chain_off = r->chain_off.data();
+    v->n_chains = r->chain_anchor_off.size() - 1; v->chain_anchor_off = r->chain_anchor_off.data();
+    v->n_chain_anchors = r->ca_id.size();
+    v->ca_id = r->ca_id.data(); v->ca_qb = r->ca_qb.data(); v->ca_tb = r->ca_tb.data(); v->ca_te = r->ca_te.data();
+    v->ca_score = r->ca_score.data();
+    v->aln_status = r->aln_status.data(); v->aln_chain = r->aln_chain.data(); v->aln_path_off = r->aln_path_off.data();
+    v->aln_path = r->aln_path.data(); v->aln_run_off = r->aln_run_off.data(); v->aln_runs = r->aln_runs.data();
+    v->aln_path_len = r->aln_path_len.data(); v->aln_start_off = r->aln_start_off.data(); v->aln_end_off = r->aln_end_off.data();
+    v->aln_n_aligned = r->aln_n_aligned.data(); v->aln_score = r->aln_score.data(); v->aln_cells = r->aln_cells.data();
+    if (r->debug) {
+        v->dbg_anchor_off = r->dbg_anchor_off.data(); v->dbg_qb = r->dbg_qb.data(); v->dbg_tb = r->dbg_tb.data();
+        v->dbg_te = r->dbg_te.data(); v->dbg_sorted = r->dbg_sorted.data(); v->dbg_f = r->dbg_f.data();
+        v->dbg_pred = r->dbg_pred.data(); v->dbg_sub_off = r->dbg_sub_off.data(); v->dbg_sub_handles = r->dbg_sub_handles.data();
+        v->dbg_edge_off = r->dbg_edge_off.data(); v->dbg_edges = r->dbg_edges.data();
+    }
+    return VGA_OK;
+}
+
+int vga_results_stats(const vga_results_t* r, VgaStats* s) {
+    if (!r || !s) { set_error("null argument"); return VGA_ERR_INVALID; }
+    *s = r->stats;
+    return VGA_OK;
+}
+
+int vga_results_free(vga_results_t* r) {
+    delete r;
+    return VGA_OK;
+}
+
+int vga_measure_int32_peak(double* ops_per_s) {
+    if (!ops_per_s) { set_error("null argument"); return VGA_ERR_INVALID; }
+    try {
+        if (g_device < 0) { int rc = vga_init(0); if (rc != VGA_OK) return rc; }
+        VGA_CUDA(cudaSetDevice(g_device));
+        *ops_per_s = measure_int32_peak();
+    } catch (CudaFail& f) { return f.code; }
+    return VGA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,54 @@
+/* C API of libvga_host.so: the host-side pieces the Rust front end owns in the real deployment
+ * (index build, FASTA/FASTQ reading, GAF writing), restated in C++ because this image has no cargo.
+ * Pure CPU code, no CUDA, never touches oracle/.  Used by the vga_map harness, bench.py and tests. */
+#ifndef VGA_HOST_H
+#define VGA_HOST_H
+#include <stdint.h>
+
+#include "../../include/vga.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vgah_index vgah_index_t;
+typedef struct vgah_reads vgah_reads_t;
+
+const char* vgah_last_error(void);
+
+/* `vgaligner index` (reference src/subcommands/index_main.rs:11-87, src/index.rs:109-281) */
+vgah_index_t* vgah_index_build_file(const char* gfa_path, uint32_t k, uint64_t max_furcations, uint64_t max_degree);
+vgah_index_t* vgah_index_build_text(const char* gfa_text, uint32_t k, uint64_t max_furcations, uint64_t max_degree);
+vgah_index_t* vgah_index_load(const char* path);
+int vgah_index_save(const vgah_index_t*, const char* path);
+void vgah_index_free(vgah_index_t*);
+int vgah_index_view(const vgah_index_t*, VgaIndexView* view);       /* borrowed pointers into the index */
+const char* vgah_index_keys(const vgah_index_t*, uint64_t* n_keys); /* n_keys*k bytes: the k-mer strings */
+const char* vgah_index_seq_rev(const vgah_index_t*);                /* Index.seq_rev */
+
+/* read_seqs_from_file (reference src/io.rs:74-131): extension decides FASTA/FASTQ */
+vgah_reads_t* vgah_reads_from_file(const char* path);
+/* seeded read simulator: forward random walks over the graph, substitutions / insertions /
+ * deletions, a fraction reverse-complemented (SURVEY.md §8d inputs) */
+vgah_reads_t* vgah_reads_simulate(const vgah_index_t*, uint32_t n, uint32_t len, double sub, double ins, double del,
+                                  double rev_frac, uint64_t seed);
+void vgah_reads_free(vgah_reads_t*);
+uint32_t vgah_reads_count(const vgah_reads_t*);
+const char* vgah_reads_seqs(const vgah_reads_t*);        /* concatenated */
+const uint64_t* vgah_reads_offsets(const vgah_reads_t*); /* n+1 */
+const char* vgah_reads_names(const vgah_reads_t*);       /* '\n' separated */
+int vgah_reads_write_fasta(const vgah_reads_t*, const char* path);
+
+/* synthetic variation graph (config C4): random backbone, ~1 variant site per `site_every` bp,
+ * 80% SNP bubbles, 10% insertions, 10% deletions; GFA text, ids topologically ordered */
+char* vgah_synth_gfa(uint64_t backbone_len, uint32_t site_every, uint64_t seed, uint64_t* len);
+void vgah_free_str(char*);
+
+/* GAF text from the C ABI's result arrays: GAFAlignment::{from_chain, from_placeholder_chain,
+ * to_string} (src/align.rs:762-1027) and generate_alignment (src/align.rs:1096-1168).
+ * which: 0 = chains file, 1 = alignments file. */
+char* vgah_gaf(const vgah_index_t*, const VgaResultsView* res, const vgah_reads_t* reads, int which, uint64_t* len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
