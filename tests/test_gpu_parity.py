@@ -1,0 +1,220 @@
+"""Parity tests proper: the CUDA path through the C ABI (vga_map_batch) against the oracle on the
+same seeded inputs, stage by stage.  Integer / index work is compared bit-exact; the f64 chain
+scores are compared bit-exact as well (DESIGN.md explains why that is achievable).
+
+Run on the B200 box: python -m pytest tests -m gpu
+"""
+import numpy as np
+import pytest
+
+import vgaligner_b200 as vg
+from conftest import fixture_path, gfa_text
+from oracle import binding as orc
+
+pytestmark = pytest.mark.gpu
+
+
+class FakeReads:
+    """Reads assembled in Python (duck-types vgaligner_b200.Reads for both sides)."""
+
+    def __init__(self, seqs, names=None):
+        self.n = len(seqs)
+        self.names = names or ["r%d" % i for i in range(len(seqs))]
+        self.offsets = np.zeros(self.n + 1, dtype=np.uint64)
+        if self.n:
+            self.offsets[1:] = np.cumsum([len(s) for s in seqs])
+        self.seqs = np.frombuffer("".join(seqs).encode(), dtype=np.uint8).copy() if self.n else np.zeros(0, np.uint8)
+        self._h = None
+
+    def seq(self, i):
+        return self.seqs[int(self.offsets[i]):int(self.offsets[i + 1])].tobytes().decode()
+
+
+def both(ix, reads, **kw):
+    flags = vg.VGA_FLAG_KEEP_DEBUG | kw.pop("flags", 0)
+    gp = vg.default_params(flags=flags, **kw)
+    op = orc.default_params(flags=orc.FLAG_KEEP_DEBUG | (orc.FLAG_NO_ALIGN if flags & vg.VGA_FLAG_NO_ALIGN else 0), **kw)
+    g = vg.map_reads(ix, reads, params=gp)
+    o = orc.OracleIndex(ix).map_reads(reads, op, n_threads=8)
+    return g, o
+
+
+def assert_same(g, o, what):
+    for name in what:
+        a, b = getattr(g, name), getattr(o, name)
+        assert a.shape == b.shape, "%s: shape %s vs %s" % (name, a.shape, b.shape)
+        if not np.array_equal(a, b):
+            bad = np.flatnonzero((a != b).reshape(a.shape[0], -1).any(axis=1))
+            raise AssertionError("%s differs at %d entries, first %d: gpu=%s oracle=%s" %
+                                 (name, bad.size, bad[0], a[bad[0]], b[bad[0]]))
+
+
+SEED = ["n_anchors", "dbg_anchor_off", "dbg_qb", "dbg_tb", "dbg_te"]
+SORT = ["dbg_sorted"]
+CHAIN = ["dbg_f", "dbg_pred", "chain_off", "chain_anchor_off", "ca_id", "ca_qb", "ca_tb", "ca_te", "ca_score"]
+SUB = ["dbg_sub_off", "dbg_sub_handles", "dbg_edge_off"]
+ALN = ["aln_status", "aln_chain", "aln_score", "aln_cells", "aln_path_len", "aln_start_off", "aln_end_off", "aln_n_aligned",
+       "aln_path_off", "aln_path", "aln_run_off", "aln_runs"]
+
+
+def check_all(g, o):
+    assert_same(g, o, SEED)
+    assert_same(g, o, SORT)
+    assert_same(g, o, CHAIN)
+    assert_same(g, o, SUB)
+    # edge lists: the oracle keeps find_nodes_edges_for_abpoa's emission order, the device a per-target
+    # predecessor list; both orders are the same relation (compared as sorted pairs per read)
+    for r in range(len(g.dbg_edge_off) - 1):
+        a = g.dbg_edges[int(g.dbg_edge_off[r]):int(g.dbg_edge_off[r + 1])]
+        b = o.dbg_edges[int(o.dbg_edge_off[r]):int(o.dbg_edge_off[r + 1])]
+        assert sorted(map(tuple, a.tolist())) == sorted(map(tuple, b.tolist())), "edges of read %d" % r
+    assert_same(g, o, ALN)
+
+
+@pytest.mark.parametrize("k", [3, 4, 5, 6, 11])
+@pytest.mark.parametrize("fa", ["single-read-test.fa", "multiple-read-test.fa"])
+def test_c1_test_gfa(k, fa):
+    """BASELINE config 1: test/test.gfa + the reference's FASTA fixtures, several k."""
+    ix = vg.Index.build(fixture_path("test.gfa"), k)
+    reads = vg.read_seqs_from_file(fixture_path(fa))
+    g, o = both(ix, reads)
+    check_all(g, o)
+    oi = orc.OracleIndex(ix)
+    assert g.gaf(0) == o.gaf(oi, reads, 0)
+    assert g.gaf(1) == o.gaf(oi, reads, 1)
+    if k == 11:
+        assert g.gaf(1).split("\t")[2] == "*"       # placeholder record
+
+
+def test_c1_whole_linearisation_chain():
+    ix = vg.Index.build(fixture_path("test.gfa"), 11)
+    reads = FakeReads([ix.seq_fwd, ix.seq_fwd[5:50]])
+    g, o = both(ix, reads, min_anchors=2)
+    check_all(g, o)
+    assert g.ca_score[int(g.chain_anchor_off[1]) - 1] == 35.0
+
+
+@pytest.mark.parametrize("graph,k,n,length", [
+    ("graphs/2-DRB1-3123.gfa", 11, 3000, 150),
+    ("graphs/19-MICB-4227-smooth.gfa", 11, 2000, 150),
+    ("graphs/17-DRB1-3123-smooth.gfa", 11, 2000, 150),
+])
+def test_hla_graphs_short_reads(graph, k, n, length):
+    """BASELINE configs 2 and 3 (scaled down): simulated 150 bp reads, 1% sub + 0.1% indel, 10% revcomp."""
+    ix = vg.Index.build(fixture_path(graph), k)
+    reads = vg.simulate_reads(ix, n, length, 0.01, 0.0005, 0.0005, 0.1, 77)
+    g, o = both(ix, reads)
+    check_all(g, o)
+    oi = orc.OracleIndex(ix)
+    assert g.gaf(0) == o.gaf(oi, reads, 0)
+    assert g.gaf(1) == o.gaf(oi, reads, 1)
+    assert (g.aln_status == vg.ALN_OK).mean() > 0.5
+
+
+def test_cyclic_inverting_graph():
+    """5-B3106 has back links and '-' orientations (reverse handles in the extension)."""
+    ix = vg.Index.build(fixture_path("graphs/5-B3106.gfa"), 11)
+    reads = vg.simulate_reads(ix, 500, 120, 0.01, 0.0005, 0.0005, 0.1, 3)
+    g, o = both(ix, reads)
+    check_all(g, o)
+
+
+@pytest.fixture(scope="module")
+def synth():
+    return vg.Index.build_from_text(vg.synth_gfa(200000, 100, 1), 15)
+
+
+def test_synthetic_short_reads(synth):
+    """BASELINE config 4 (scaled down): synthetic bubbles, k=15, 150 bp reads."""
+    reads = vg.simulate_reads(synth, 4000, 150, 0.01, 0.0005, 0.0005, 0.1, 2)
+    g, o = both(synth, reads)
+    check_all(g, o)
+    assert (g.aln_status == vg.ALN_OK).mean() > 0.7
+
+
+def test_synthetic_long_reads(synth):
+    """BASELINE config 5 (scaled down): 10 kb reads at 10% error (wide-band POA)."""
+    reads = vg.simulate_reads(synth, 24, 10000, 0.04, 0.03, 0.03, 0.1, 3)
+    g, o = both(synth, reads)
+    check_all(g, o)
+    assert (g.aln_status == vg.ALN_OK).sum() >= 12
+
+
+def test_medium_reads_and_best_n(synth):
+    reads = vg.simulate_reads(synth, 300, 1000, 0.03, 0.01, 0.01, 0.0, 9)
+    g, o = both(synth, reads, best_n=3, min_anchors=2)
+    check_all(g, o)
+
+
+def test_chains_only(synth):
+    reads = vg.simulate_reads(synth, 500, 150, 0.01, 0.0005, 0.0005, 0.1, 4)
+    g, o = both(synth, reads, flags=vg.VGA_FLAG_NO_ALIGN)
+    assert_same(g, o, SEED + SORT + CHAIN + ["aln_status"])
+    assert (g.aln_status == vg.ALN_PLACEHOLDER).all()
+
+
+def test_edge_cases(synth):
+    """Empty and ragged inputs, reads shorter than k, non-ACGT bytes, lowercase."""
+    fwd = synth.seq_fwd
+    seqs = ["", "A", fwd[100:114], fwd[100:115], fwd[200:350], "N" * 150, fwd[400:450] + "N" + fwd[451:550],
+            fwd[600:750].lower(), fwd[800:950], "ACGT" * 40, fwd[1000:1400]]
+    reads = FakeReads(seqs)
+    g, o = both(synth, reads)
+    check_all(g, o)
+    assert g.n_anchors[0] == 0 and g.n_anchors[1] == 0 and g.n_anchors[2] == 0 and g.n_anchors[5] == 0
+    assert g.n_anchors[7] == 0      # lowercase never matches (raw byte comparison, src/index.rs:314-321)
+
+
+def test_empty_batch(synth):
+    g = vg.map_reads(synth, FakeReads([]))
+    assert g.n_anchors.size == 0 and g.chain_off.tolist() == [0]
+
+
+def test_repeats_many_anchors():
+    """Low-complexity graph: k-mers with many occurrences, anchors per read in the thousands."""
+    unit = "ACGTTGCA"
+    nodes = [unit * 40, "A", "C", unit * 40, "G", "T", unit * 30]
+    edges = [(1, 2), (1, 3), (2, 4), (3, 4), (4, 5), (4, 6), (5, 7), (6, 7)]
+    ix = vg.Index.build_from_text(gfa_text(nodes, edges), 7)
+    reads = FakeReads([unit * 12, (unit * 20)[3:], unit * 3 + "A" + unit * 5])
+    g, o = both(ix, reads)
+    check_all(g, o)
+    assert g.n_anchors.max() > 1000
+
+
+def test_batch_independence(synth):
+    """Results do not depend on how reads are batched (reads are independent units)."""
+    reads = vg.simulate_reads(synth, 600, 150, 0.01, 0.0005, 0.0005, 0.1, 11)
+    whole = vg.map_reads(synth, reads)
+    half = FakeReads([reads.seq(i) for i in range(300, 600)], reads.names[300:])
+    part = vg.map_reads(synth, half)
+    assert np.array_equal(whole.aln_score[300:], part.aln_score)
+    assert np.array_equal(whole.aln_status[300:], part.aln_status)
+    b = int(whole.aln_run_off[300])
+    assert np.array_equal(whole.aln_runs[b:], part.aln_runs)
+
+
+def test_size_independent_properties(synth):
+    """Properties that hold at any size: every aligned read's ops consume the whole read, path
+    handles are valid node ids, runs alternate, scores are bounded by 2*len."""
+    reads = vg.simulate_reads(synth, 20000, 150, 0.01, 0.0005, 0.0005, 0.1, 21)
+    g = vg.map_reads(synth, reads)
+    ok = g.aln_status == vg.ALN_OK
+    assert ok.mean() > 0.7
+    ops = g.aln_runs >> 28
+    lens = (g.aln_runs & 0x0fffffff).astype(np.int64)
+    read_of_run = np.repeat(np.arange(reads.n), np.diff(g.aln_run_off).astype(np.int64))
+    consumed = np.bincount(read_of_run, weights=np.where(ops != 2, lens, 0), minlength=reads.n)
+    assert np.array_equal(consumed[ok], np.full(ok.sum(), 150.0))
+    graph_ops = np.bincount(read_of_run, weights=np.where(ops != 3, lens, 0), minlength=reads.n)
+    assert np.array_equal(graph_ops[ok].astype(np.uint32), g.aln_path_len[ok])
+    same_read = read_of_run[1:] == read_of_run[:-1]
+    assert not (same_read & (ops[1:] == ops[:-1])).any()
+    assert (g.aln_score[ok] <= 300).all()
+    assert ((g.aln_path >> 1) >= 1).all() and ((g.aln_path >> 1) <= synth.view.n_nodes).all()
+    st = g.stats
+    assert st["kernel_launches"] > 0 and st["poa_cells"] >= int(g.aln_cells.sum())
+
+
+def test_int32_peak_is_measurable():
+    assert vg.measure_int32_peak() > 1e12

@@ -1,0 +1,101 @@
+"""Host-side logic: FASTA/FASTQ parsing (reference src/io.rs tests), GFA handling, the index
+container, the simulators.  CPU only."""
+import os
+
+import numpy as np
+import pytest
+
+import vgaligner_b200 as vg
+from conftest import fixture_path, gfa_text
+
+
+def test_read_fasta_single_and_multiple():
+    """src/io.rs:266-300: names and sequences of the FASTA fixtures."""
+    r = vg.read_seqs_from_file(fixture_path("single-read-test.fa"))
+    assert r.n == 1 and r.names == ["seq0"] and r.seq(0) == "AAAAACGTTAAATTTGGCATCGTAGCAAAAA"
+    r = vg.read_seqs_from_file(fixture_path("multiple-read-test.fa"))
+    assert r.n == 2 and r.names == ["seq0", "seq1"]
+    assert r.seq(1) == "TTTCGTTAAATTTGGCATCGTAGCTTT"
+
+
+def test_read_fastq():
+    """src/io.rs:302-320."""
+    r = vg.read_seqs_from_file(fixture_path("test.fq"))
+    assert r.n >= 1 and r.names[0].startswith("ERR059938.60")
+    assert r.seq(0).startswith("GTCTCCGGGGGCTGGGGGAACCAGGGG") and len(r.seq(0)) == 100
+
+
+def test_fasta_one_read_per_sequence_line(tmp_path):
+    """src/io.rs:100-121: every non-empty sequence line is a read; repeated names get a counter suffix."""
+    p = tmp_path / "x.fa"
+    p.write_text(">a\nACGT\nTTTT\n\nGG\n>b\nCC\n")
+    r = vg.read_seqs_from_file(str(p))
+    assert r.names == ["a", "a1", "a2", "b"] and [r.seq(i) for i in range(4)] == ["ACGT", "TTTT", "GG", "CC"]
+
+
+def test_unknown_extension_is_an_error(tmp_path):
+    p = tmp_path / "x.txt"
+    p.write_text(">a\nACGT\n")
+    with pytest.raises(vg.VgaError):
+        vg.read_seqs_from_file(str(p))
+
+
+def test_gfa_errors():
+    with pytest.raises(vg.VgaError):
+        vg.Index.build_from_text("S\t1\tACGT\nS\t3\tAC\n", 3)          # ids not contiguous
+    with pytest.raises(vg.VgaError):
+        vg.Index.build_from_text("S\tx\tACGT\n", 3)                    # non-integer name
+    with pytest.raises(vg.VgaError):
+        vg.Index.build_from_text(gfa_text(["ACGT"], [(1, 2)]), 3)      # link to a missing segment
+    with pytest.raises(vg.VgaError):
+        vg.Index.build_from_text(gfa_text(["ACGT"], []), 33)           # k > 32 cannot be packed
+
+
+def test_duplicate_links_are_stored_once():
+    ix = vg.Index.build_from_text(gfa_text(["AC", "GT"], [(1, 2), (1, 2)]), 3)
+    assert ix.edges.tolist() == [4, 2]
+
+
+def test_n_bases_drop_the_handle():
+    """src/kmer.rs:401-403,459-461: a k-mer reaching an N discards everything from that handle orientation."""
+    ix = vg.Index.build_from_text(gfa_text(["ACGTAC", "NN", "GTACGT"], [(1, 2), (2, 3)]), 3)
+    keys, n = ix.keys_bytes()
+    kmers = {keys[i * 3:(i + 1) * 3].decode() for i in range(n)}
+    assert all("N" not in k for k in kmers)
+    ts, _, _ = ix.table()
+    fwd_starts = sorted(int(x) for x in ts if x != np.uint64(2 ** 64 - 1) and not (int(x) >> 63))
+    assert fwd_starts == [8, 9, 10, 11]       # node 1 reaches the N (dropped), node 3 forward survives
+
+
+def test_index_roundtrip(tmp_path):
+    ix = vg.Index.build(fixture_path("graphs/19-MICB-4227-smooth.gfa"), 11)
+    p = str(tmp_path / "g.vgidx")
+    ix.store_in_file(p)
+    iy = vg.Index.load_from_file(p)
+    assert iy.seq_fwd == ix.seq_fwd and iy.n_kmers == ix.n_kmers
+    assert np.array_equal(ix.table()[0], iy.table()[0]) and np.array_equal(ix.edges, iy.edges)
+    assert ix.keys_bytes() == iy.keys_bytes()
+
+
+def test_survey_graph_statistics():
+    """2-DRB1-3123 at k=11 has 99 951 distinct k-mers and 110 949 positions, 55 506 fwd/fwd."""
+    ix = vg.Index.build(fixture_path("graphs/2-DRB1-3123.gfa"), 11)
+    assert ix.view.n_nodes == 4792 and ix.view.seq_len == 22595
+    assert ix.n_kmers == 99951 and ix.n_kmer_pos - ix.n_kmers == 110949
+    ts, te, _ = ix.table()
+    real = ts != np.uint64(2 ** 64 - 1)
+    ff = real & ((ts >> np.uint64(63)) == 0) & ((te >> np.uint64(63)) == 0)
+    assert int(ff.sum()) == 55506
+
+
+def test_simulators_are_seeded():
+    ix = vg.Index.build(fixture_path("graphs/19-MICB-4227-smooth.gfa"), 11)
+    a = vg.simulate_reads(ix, 50, 150, 0.01, 0.001, 0.001, 0.1, 7)
+    b = vg.simulate_reads(ix, 50, 150, 0.01, 0.001, 0.001, 0.1, 7)
+    c = vg.simulate_reads(ix, 50, 150, 0.01, 0.001, 0.001, 0.1, 8)
+    assert np.array_equal(a.seqs, b.seqs) and not np.array_equal(a.seqs, c.seqs)
+    assert all(len(a.seq(i)) == 150 for i in range(a.n))
+    g1, g2 = vg.synth_gfa(50000, 100, 1), vg.synth_gfa(50000, 100, 1)
+    assert g1 == g2 and g1 != vg.synth_gfa(50000, 100, 2)
+    sx = vg.Index.build_from_text(g1, 15)
+    assert 49000 < sx.view.seq_len < 53000 and sx.view.n_nodes > 1000
