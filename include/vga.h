@@ -120,8 +120,12 @@ typedef struct {
     uint64_t n_reads, n_bases, n_probes, n_positions_read, n_anchors, n_chains, n_alignments;
     uint64_t poa_cells;                     /* all aligned (read,chain) pairs */
     uint64_t lookup_bytes;                  /* algorithmic bytes of the lookup stage */
-    float ms_h2d, ms_seed, ms_sort, ms_chain, ms_subgraph, ms_poa, ms_trace, ms_d2h, ms_total;
+    float ms_h2d, ms_seed, ms_sort, ms_chain, ms_subgraph, ms_poa, ms_trace, ms_d2h;
+    float ms_total;                         /* CUDA-event time of the whole call on the library's stream */
+    float ms_wall;                          /* host wall clock of the call */
     uint32_t kernel_launches;               /* kernels of this library launched by the call */
+    uint32_t poa_launches;                  /* launches of the POA fill kernel among them */
+    uint64_t h2d_bytes, d2h_bytes;          /* bytes copied host->device / device->host by the call */
 } VgaStats;
 
 typedef struct vga_index vga_index_t;

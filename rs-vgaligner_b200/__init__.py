@@ -52,7 +52,9 @@ class VgaStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("n_reads", "n_bases", "n_probes", "n_positions_read", "n_anchors",
                                           "n_chains", "n_alignments", "poa_cells", "lookup_bytes")] + \
                [(n, C.c_float) for n in ("ms_h2d", "ms_seed", "ms_sort", "ms_chain", "ms_subgraph", "ms_poa",
-                                         "ms_trace", "ms_d2h", "ms_total")] + [("kernel_launches", C.c_uint32)]
+                                         "ms_trace", "ms_d2h", "ms_total", "ms_wall")] + \
+               [("kernel_launches", C.c_uint32), ("poa_launches", C.c_uint32), ("h2d_bytes", C.c_uint64),
+                ("d2h_bytes", C.c_uint64)]
 
 
 VGA_FLAG_NO_ALIGN, VGA_FLAG_KEEP_DEBUG = 1, 2

@@ -234,7 +234,9 @@ template <class T> static T d2h_one(const T* dptr, cudaStream_t st) {
     return v;
 }
 
+static thread_local u64 g_d2h_bytes = 0;
 template <class T> static void d2h_append(std::vector<T>& dst, const T* dptr, size_t n, cudaStream_t st) {
+    g_d2h_bytes += n * sizeof(T);
     size_t o = dst.size();
     dst.resize(o + n);
     if (n) VGA_CUDA(cudaMemcpyAsync(dst.data() + o, dptr, n * sizeof(T), cudaMemcpyDeviceToHost, st));
@@ -373,6 +375,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     std::vector<u64> h_chain_off(n + 1), h_caoff(NC + 1);
     VGA_CUDA(cudaMemcpyAsync(h_chain_off.data(), chain_off, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
     VGA_CUDA(cudaMemcpyAsync(h_caoff.data(), cg.chain_anchor_off, (NC + 1) * 8, cudaMemcpyDeviceToHost, st));
+    g_d2h_bytes += (n + 1) * 8ull + (NC + 1) * 8ull;
     d2h_append(R.ca_id, cg.ca_id, NM, st); d2h_append(R.ca_qb, cg.ca_qb, NM, st); d2h_append(R.ca_tb, cg.ca_tb, NM, st);
     d2h_append(R.ca_te, cg.ca_te, NM, st); d2h_append(R.ca_score, cg.ca_score, NM, st);
     if (dbg) {
@@ -534,6 +537,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             tbuf.n_items = nw; tbuf.work = d_work;
             VGA_CUDA(cudaEventRecord(w->ev[8], st));
             c.launches += launch_poa_fill(dv, pb, 1 << ci, w->n_sms, st);
+            R.stats.poa_launches++;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
             c.launches += launch_poa_trace(tbuf, st);
             VGA_CUDA(cudaEventRecord(w->ev[10], st));
@@ -592,6 +596,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     VGA_CUDA(cudaMemcpyAsync(h_sc.data(), d_sc, n * sizeof(ReadScalars), cudaMemcpyDeviceToHost, st));
     VGA_CUDA(cudaMemcpyAsync(h_roff.data(), offs, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
     VGA_CUDA(cudaMemcpyAsync(h_poff.data(), offs + (n + 1), (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    g_d2h_bytes += n * sizeof(ReadScalars) + 2ull * (n + 1) * 8;
     const u64 run_base = R.aln_runs.size(), path_base = R.aln_path.size();
     d2h_append(R.aln_status, d_st8, n, st);
     d2h_append(R.aln_cells, d_cells, n, st);
@@ -677,6 +682,7 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
         R->n = n_reads;
         R->begin(params->flags & VGA_FLAG_KEEP_DEBUG);
         cudaEvent_t t0 = c.ws->ev[11];
+        g_d2h_bytes = 0;
         std::vector<u64> h_off;
         const char* d_seqs = d_seqs_in;
         const u64* d_off = d_off_in;
@@ -694,6 +700,7 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
                 VGA_CUDA(cudaMemcpyAsync(ds, seqs + seq_off[0], nb, cudaMemcpyHostToDevice, c.st));
                 VGA_CUDA(cudaMemcpyAsync(doff, h_off.data(), (n_reads + 1) * 8, cudaMemcpyHostToDevice, c.st));
                 d_seqs = ds; d_off = doff;
+                R->stats.h2d_bytes += nb + (n_reads + 1) * 8ull;
             } else {
                 h_off.resize(n_reads + 1);
                 VGA_CUDA(cudaMemcpyAsync(h_off.data(), d_off_in, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, c.st));
@@ -707,8 +714,11 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
             R->stats.ms_h2d = th2d;
             run_range(c, d_seqs, d_off, h_off.data(), 0, n_reads);
         }
+        VGA_CUDA(cudaEventRecord(c.ws->ev[9], c.st));
         VGA_CUDA(cudaStreamSynchronize(c.st));
-        R->stats.ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+        VGA_CUDA(cudaEventElapsedTime(&R->stats.ms_total, t0, c.ws->ev[9]));
+        R->stats.ms_wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+        R->stats.d2h_bytes = g_d2h_bytes;
         R->stats.n_reads = n_reads;
         R->stats.kernel_launches = c.launches;
     } catch (CudaFail& f) {
