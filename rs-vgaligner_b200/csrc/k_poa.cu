@@ -112,7 +112,8 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 end = imin(end, max_pe + 1);
                 if (beg > end) status = VGA_ALN_BAND_ERR;
                 const i32 W = end - beg + 1;
-                if (status == VGA_ALN_OK && W > 32 * C) status = IT_RETRY_WIDER;
+                // the 32 lanes cover columns [cbb*C, (cbb+32)*C): the band must fit from its block-aligned start
+                if (status == VGA_ALN_OK && end - (beg / C) * C + 1 > 32 * C) status = IT_RETRY_WIDER;
                 // ---- pool space: W trace cells (+2W for the per-predecessor bytes of a first row)
                 const u64 Wr = (u64)((W + 3) & ~3);
                 const u64 need = first ? 3 * Wr : Wr;
@@ -437,11 +438,13 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(TraceBuffers b) {
             } else {
                 const u32 pt = ((const u32*)(b.pool + (u64)b.nd_ptoff[nb + s] * 4))[jc - rb];
                 u32 k = kind == 1 ? (pt & 0xff) : fresh ? ((pt >> 8) & 0xff) : which == 1 ? ((pt >> 16) & 0xff) : ((pt >> 24) & 0xff);
+                if (k >= pn) { err = true; break; }      // inconsistent trace word: report, never fault
                 s = pl[po + k];
                 o = rs[s + 1] - rs[s] - 1;
             }
             if (kind == 2 && !at_source) {
                 const u32 rowp = it.row_base + rs[s] + o;
+                if (jc < b.row_beg[rowp]) { err = true; break; }
                 const u32 cellp = b.pool[(u64)b.row_toff[rowp] * 4 + (u32)(jc - b.row_beg[rowp])];
                 const bool opened = cellp & (which == 1 ? TB_E1OPEN : TB_E2OPEN);
                 cur = opened ? (M_OP | F1_OP | F2_OP) : (which == 1 ? E1_OP : E2_OP);

@@ -9,6 +9,8 @@
 #include <chrono>
 #include <cmath>
 #include <cstddef>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -227,6 +229,16 @@ struct Ctx {
     u32 launches = 0;
 };
 
+// VGA_DEBUG_SYNC=1: synchronise and check after every stage so a device fault names its stage
+static bool debug_sync() { static int v = -1; if (v < 0) { const char* e = getenv("VGA_DEBUG_SYNC"); v = e && *e == '1'; } return v; }
+static void stage_check(cudaStream_t st, const char* name) {
+    if (!debug_sync()) return;
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) { set_error(std::string("stage ") + name + ": " + cudaGetErrorString(e)); throw CudaFail{VGA_ERR_CUDA}; }
+    fprintf(stderr, "[vga] stage %s ok\n", name);
+}
+
 template <class T> static T d2h_one(const T* dptr, cudaStream_t st) {
     T v;
     VGA_CUDA(cudaMemcpyAsync(&v, dptr, sizeof(T), cudaMemcpyDeviceToHost, st));
@@ -305,6 +317,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     sb.seqs = d_seqs; sb.seq_off = d_seq_off; sb.n_reads = n;
     sb.read_koff = w->b[B_KOFF].get<u64>(n + 1);
     c.launches += launch_read_prep(dv, sb, st);
+    stage_check(st, "read_prep");
     {
         size_t tb = 0;
         cub::DeviceScan::InclusiveSum(nullptr, tb, sb.read_koff + 1, sb.read_koff + 1, (int)n, st);
@@ -318,6 +331,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     sb.read_acnt = w->b[B_ACNT].get<u32>(n);
     sb.read_aoff = w->b[B_AOFF].get<u32>(n + 1);
     c.launches += launch_seed_count(dv, sb, st);
+    stage_check(st, "seed_count");
     {   // anchors may not exceed 2^31 per chunk (CUB segmented sort takes int counts)
         u64* tmp64 = w->b[B_SZOFF].get<u64>(n + 1);
         scan_to_offsets(c, sb.read_acnt, tmp64, n);
@@ -331,6 +345,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u32* key_out = w->b[B_KEYOUT].get<u32>(A);
     u32* val_out = w->b[B_VALOUT].get<u32>(A);
     c.launches += launch_seed_emit(dv, sb, st);
+    stage_check(st, "seed_emit");
     VGA_CUDA(cudaEventRecord(w->ev[1], st));
     // ---- K2 per-read stable sort by target_end.position (src/chain.rs:386-389)
     if (A > 0) {
@@ -354,6 +369,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     cb.clen = w->b[B_CLEN].get<u32>((u64)A + n); cb.cmem = w->b[B_CMEM].get<u32>(2ull * A + 2ull * n);
     cb.k = dv.k; cb.bandwidth = P.bandwidth; cb.max_gap = P.max_gap; cb.min_anchors = P.min_anchors;
     c.launches += launch_chain(cb, st);
+    stage_check(st, "chain");
     u64* chain_off = w->b[B_CHOFF].get<u64>(n + 1);
     u64* member_off = w->b[B_MEMOFF].get<u64>(n + 1);
     scan_to_offsets(c, cb.n_chains, chain_off, n);
@@ -367,6 +383,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     cg.ca_id = w->b[B_CAID].get<u32>(NM); cg.ca_qb = w->b[B_CAQB].get<u32>(NM); cg.ca_tb = w->b[B_CATB].get<u32>(NM);
     cg.ca_te = w->b[B_CATE].get<u32>(NM); cg.ca_score = w->b[B_CASC].get<double>(NM);
     c.launches += launch_chain_gather(cg, st);
+    stage_check(st, "chain_gather");
     VGA_CUDA(cudaEventRecord(w->ev[3], st));
 
     // ---- per-chunk result bookkeeping (chains)
@@ -441,6 +458,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         sub.scratch = scratch; sub.scratch_per_warp = w->scratch_words; sub.n_warps = w->sub_warps;
         VGA_CUDA(cudaMemsetAsync(ctr, 0, 64, st));
         c.launches += launch_sub_count(dv, sub, st);
+    stage_check(st, "sub_count");
         u32 h[2];
         VGA_CUDA(cudaMemcpyAsync(h, ctr, 8, cudaMemcpyDeviceToHost, st));
         VGA_CUDA(cudaStreamSynchronize(st));
@@ -469,6 +487,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     sub.nd_pred = w->b[B_NDPRED].get<u32>(tot[1]); sub.nd_first_succ = w->b[B_NDFS].get<i32>(tot[0]);
     sub.nd_remain_last = w->b[B_NDRL].get<i32>(tot[0]);
     c.launches += launch_sub_fill(dv, sub, st);
+    stage_check(st, "sub_fill");
     std::vector<u32> h_meta(3ull * NI);
     VGA_CUDA(cudaMemcpyAsync(h_meta.data(), d_nrows, 12ull * NI, cudaMemcpyDeviceToHost, st));
     VGA_CUDA(cudaEventRecord(w->ev[4], st));
@@ -537,9 +556,11 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             tbuf.n_items = nw; tbuf.work = d_work;
             VGA_CUDA(cudaEventRecord(w->ev[8], st));
             c.launches += launch_poa_fill(dv, pb, 1 << ci, w->n_sms, st);
+    stage_check(st, "poa_fill");
             R.stats.poa_launches++;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
             c.launches += launch_poa_trace(tbuf, st);
+    stage_check(st, "poa_trace");
             VGA_CUDA(cudaEventRecord(w->ev[10], st));
             item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
             c.launches++;

@@ -218,3 +218,16 @@ def test_size_independent_properties(synth):
 
 def test_int32_peak_is_measurable():
     assert vg.measure_int32_peak() > 1e12
+
+
+def test_c2_full_size_parity_and_repeatability():
+    """BASELINE config 2 at its full size (100k x 150 bp on DRB1-3123): every alignment array bit-exact
+    against the oracle, and a second call on the reused workspace returns the same bytes."""
+    ix = vg.Index.build(fixture_path("graphs/2-DRB1-3123.gfa"), 11)
+    reads = vg.simulate_reads(ix, 100000, 150, 0.01, 0.0005, 0.0005, 0.1, 77)
+    g = vg.map_reads(ix, reads)
+    o = orc.OracleIndex(ix).map_reads(reads, orc.default_params(), n_threads=32)
+    assert_same(g, o, ["n_anchors", "chain_off", "chain_anchor_off", "ca_id", "ca_qb", "ca_tb", "ca_te", "ca_score"] + ALN)
+    g2 = vg.map_reads(ix, reads)
+    assert_same(g2, g, ["ca_id", "ca_score"] + ALN)
+    assert (g.aln_status == vg.ALN_OK).mean() > 0.9
