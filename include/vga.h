@@ -63,6 +63,7 @@ typedef struct {
 
 #define VGA_FLAG_NO_ALIGN 1u     /* `map` without --also-align: chains only (src/map.rs:154) */
 #define VGA_FLAG_KEEP_DEBUG 2u   /* also return anchors / sorted order / f / pred / subgraphs (tests) */
+#define VGA_FLAG_CHAIN_SCORES 4u /* also return ca_id / ca_score (not needed by the GAF writers) */
 
 /* per-read alignment status (aln_status) */
 #define VGA_ALN_PLACEHOLDER 0    /* no chain: GAFAlignment::from_placeholder_chain (src/align.rs:913-930) */
@@ -86,11 +87,11 @@ typedef struct {
     const uint64_t* chain_anchor_off; /* n_chains+1 */
     /* per chain anchor, in chain (query) order (Chain.anchors, src/chain.rs:176-187) */
     uint64_t n_chain_anchors;
-    const uint32_t* ca_id;            /* Anchor.id */
+    const uint32_t* ca_id;            /* Anchor.id (VGA_FLAG_CHAIN_SCORES or KEEP_DEBUG, else NULL) */
     const uint32_t* ca_qb;            /* Anchor.query_begin (query_end = +k) */
     const uint32_t* ca_tb;            /* Anchor.target_begin.position */
     const uint32_t* ca_te;            /* Anchor.target_end.position */
-    const double* ca_score;           /* Anchor.max_chain_score */
+    const double* ca_score;           /* Anchor.max_chain_score (same flags, else NULL) */
     /* best alignment per read (best_alignment_for_query, src/align.rs:34-55) */
     const uint8_t* aln_status;        /* n: VGA_ALN_* */
     const uint32_t* aln_chain;        /* n: index (within the read) of the chain that was kept */

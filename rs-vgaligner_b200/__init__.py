@@ -57,7 +57,7 @@ class VgaStats(C.Structure):
                 ("d2h_bytes", C.c_uint64)]
 
 
-VGA_FLAG_NO_ALIGN, VGA_FLAG_KEEP_DEBUG = 1, 2
+VGA_FLAG_NO_ALIGN, VGA_FLAG_KEEP_DEBUG, VGA_FLAG_CHAIN_SCORES = 1, 2, 4
 ALN_PLACEHOLDER, ALN_OK, ALN_EMPTY, ALN_TRACE_ERR, ALN_BAND_ERR, ALN_UNSUPPORTED, ALN_TOO_WIDE = range(7)
 
 GPU_SYMBOLS = ["vga_init", "vga_device_count", "vga_index_upload", "vga_index_free", "vga_index_image_size",
@@ -377,7 +377,7 @@ class MapResults:
 
 
 def map_reads(index, inputs, bandwidth=50, max_gap=1000, chain_min_n_anchors=3, also_align=True, align_best_n=1,
-              out_prefix=None, keep_debug=False, params=None):
+              out_prefix=None, keep_debug=False, chain_scores=False, params=None):
     """map_reads (reference src/map.rs:27-216) on the GPU.
 
     Returns :class:`MapResults`; when ``out_prefix`` is given also writes ``<prefix>-chains.gaf`` and
@@ -388,7 +388,8 @@ def map_reads(index, inputs, bandwidth=50, max_gap=1000, chain_min_n_anchors=3, 
     p = params or default_params()
     if params is None:
         p.bandwidth, p.max_gap, p.min_anchors, p.best_n = bandwidth, max_gap, chain_min_n_anchors, align_best_n
-        p.flags = (0 if also_align else VGA_FLAG_NO_ALIGN) | (VGA_FLAG_KEEP_DEBUG if keep_debug else 0)
+        p.flags = ((0 if also_align else VGA_FLAG_NO_ALIGN) | (VGA_FLAG_KEEP_DEBUG if keep_debug else 0) |
+                   (VGA_FLAG_CHAIN_SCORES if chain_scores else 0))
     gix = index.upload()
     out = C.c_void_p()
     seqs = np.ascontiguousarray(inputs.seqs)

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -49,8 +50,9 @@ enum {
 };
 
 struct vga_workspace {
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, st2 = nullptr;   // st2: result copies overlapped with the POA stage
     cudaEvent_t ev[12];
+    cudaEvent_t ev_copy = nullptr;
     DBuf b[B_COUNT];
     int n_sms = 148;
     u32 scratch_words = 0;      // BFS scratch per warp currently allocated
@@ -64,6 +66,8 @@ void free_workspace(vga_index* ix) {
     if (!ix->ws) return;
     for (auto& d : ix->ws->b) d.release();
     for (auto& e : ix->ws->ev) cudaEventDestroy(e);
+    if (ix->ws->ev_copy) cudaEventDestroy(ix->ws->ev_copy);
+    if (ix->ws->st2) cudaStreamDestroy(ix->ws->st2);
     if (ix->ws->st) cudaStreamDestroy(ix->ws->st);
     delete ix->ws;
     ix->ws = nullptr;
@@ -74,6 +78,8 @@ static vga_workspace* workspace(vga_index* ix) {
     if (ix->ws) return ix->ws;
     vga_workspace* w = new vga_workspace();
     VGA_CUDA(cudaStreamCreate(&w->st));
+    VGA_CUDA(cudaStreamCreateWithFlags(&w->st2, cudaStreamNonBlocking));
+    VGA_CUDA(cudaEventCreateWithFlags(&w->ev_copy, cudaEventDisableTiming));
     for (auto& e : w->ev) VGA_CUDA(cudaEventCreate(&e));
     cudaDeviceProp prop;
     VGA_CUDA(cudaGetDeviceProperties(&prop, ix->device));
@@ -83,27 +89,75 @@ static vga_workspace* workspace(vga_index* ix) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// results
+// results: pinned host arrays (process-wide cache of pinned blocks, so repeated calls do not pay
+// cudaHostAlloc again); one OutSet per chunk, merged when a call needed several chunks
 // ---------------------------------------------------------------------------------------------
+struct HBlock { void* p; size_t cap; };
+static std::mutex g_pin_mu;
+static std::vector<HBlock> g_pin_free;
+
+static HBlock pin_get(size_t bytes) {
+    if (bytes < 256) bytes = 256;
+    {
+        std::lock_guard<std::mutex> lk(g_pin_mu);
+        int best = -1;
+        for (int i = 0; i < (int)g_pin_free.size(); i++)
+            if (g_pin_free[i].cap >= bytes && g_pin_free[i].cap <= 2 * bytes + (1u << 20) &&
+                (best < 0 || g_pin_free[i].cap < g_pin_free[best].cap)) best = i;
+        if (best >= 0) { HBlock b = g_pin_free[best]; g_pin_free.erase(g_pin_free.begin() + best); return b; }
+    }
+    HBlock b{nullptr, bytes + bytes / 8};
+    VGA_CUDA(cudaHostAlloc(&b.p, b.cap, cudaHostAllocDefault));
+    return b;
+}
+static void pin_put(HBlock b) {
+    if (!b.p) return;
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    if (g_pin_free.size() >= 256) { cudaFreeHost(b.p); return; }
+    g_pin_free.push_back(b);
+}
+
+template <class T> struct HArr {
+    HBlock blk{nullptr, 0};
+    size_t n = 0;
+    T* data() const { return (T*)blk.p; }
+    void alloc(size_t count) { release(); blk = pin_get(std::max<size_t>(count, 1) * sizeof(T)); n = count; }
+    void release() { pin_put(blk); blk = HBlock{nullptr, 0}; n = 0; }
+    T& operator[](size_t i) { return data()[i]; }
+};
+
+struct OutSet {
+    u32 n = 0;
+    u64 NC = 0, NM = 0;
+    HArr<u32> n_anchors, aln_chain, aln_path_len, aln_start_off, aln_end_off, aln_n_aligned;
+    HArr<u64> chain_off, chain_anchor_off, aln_path_off, aln_path, aln_run_off, aln_cells;
+    HArr<u32> ca_id, ca_qb, ca_tb, ca_te, aln_runs;
+    HArr<double> ca_score;
+    HArr<u8> aln_status;
+    HArr<i32> aln_score;
+    HArr<u64> dbg_anchor_off, dbg_sub_off, dbg_sub_handles, dbg_edge_off;
+    HArr<u32> dbg_qb, dbg_tb, dbg_te, dbg_sorted, dbg_edges;
+    HArr<double> dbg_f;
+    HArr<i32> dbg_pred;
+    void release_all() {
+        n_anchors.release(); aln_chain.release(); aln_path_len.release(); aln_start_off.release(); aln_end_off.release();
+        aln_n_aligned.release(); chain_off.release(); chain_anchor_off.release(); aln_path_off.release(); aln_path.release();
+        aln_run_off.release(); aln_cells.release(); ca_id.release(); ca_qb.release(); ca_tb.release(); ca_te.release();
+        aln_runs.release(); ca_score.release(); aln_status.release(); aln_score.release(); dbg_anchor_off.release();
+        dbg_sub_off.release(); dbg_sub_handles.release(); dbg_edge_off.release(); dbg_qb.release(); dbg_tb.release();
+        dbg_te.release(); dbg_sorted.release(); dbg_edges.release(); dbg_f.release(); dbg_pred.release();
+    }
+};
+
 struct vga_results {
     u32 n = 0;
-    std::vector<u32> n_anchors, aln_chain, aln_path_len, aln_start_off, aln_end_off, aln_n_aligned;
-    std::vector<u64> chain_off, chain_anchor_off, aln_path_off, aln_path, aln_run_off, aln_cells;
-    std::vector<u32> ca_id, ca_qb, ca_tb, ca_te, aln_runs;
-    std::vector<double> ca_score;
-    std::vector<u8> aln_status;
-    std::vector<i32> aln_score;
-    bool debug = false;
-    std::vector<u64> dbg_anchor_off, dbg_sub_off, dbg_sub_handles, dbg_edge_off;
-    std::vector<u32> dbg_qb, dbg_tb, dbg_te, dbg_sorted, dbg_edges;
-    std::vector<double> dbg_f;
-    std::vector<i32> dbg_pred;
+    bool debug = false, scores = false;
+    OutSet o;
+    std::vector<OutSet*> parts;
     VgaStats stats;
-    void begin(bool dbg) {
-        debug = dbg;
-        chain_off.assign(1, 0); chain_anchor_off.assign(1, 0); aln_path_off.assign(1, 0); aln_run_off.assign(1, 0);
-        dbg_anchor_off.assign(1, 0); dbg_sub_off.assign(1, 0); dbg_edge_off.assign(1, 0);
-        memset(&stats, 0, sizeof(stats));
+    ~vga_results() {
+        o.release_all();
+        for (OutSet* p : parts) { p->release_all(); delete p; }
     }
 };
 
@@ -150,11 +204,10 @@ __global__ void item_status_kernel(const AlignItem* items, const u32* work, u32 
     if (i < n) status[i] = items[work[i]].status;
 }
 
-struct ReadScalars { u32 chain, path_len, start_off, end_off, n_aligned; i32 score; };
-
-// best_alignment_for_query (src/align.rs:34-55): stable sort by path_length descending, first wins
+// best_alignment_for_query (src/align.rs:34-55): stable sort by path_length descending, first wins.
+// sc: SoA block of 6 arrays of n (chain, path_len, start_off, end_off, n_aligned, score)
 __global__ void select_kernel(const AlignItem* items, const u32* cnt, const u64* item_off, u32 n, u32 max_c_status,
-                              i32* sel, u8* status, ReadScalars* sc, u64* cells, u64* run_cnt, u64* path_cnt,
+                              i32* sel, u8* status, u32* sc, u64* cells, u64* run_cnt, u64* path_cnt,
                               u64* sub_cnt, u64* edge_cnt) {
     u32 r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
@@ -166,20 +219,22 @@ __global__ void select_kernel(const AlignItem* items, const u32* cnt, const u64*
         if (best < 0 || pl > best_len) { best = (i32)(item_off[r] + c); best_len = pl; }
     }
     sel[r] = best;
-    ReadScalars s = {0, 0, 0, 0, 0, 0};
+    u32 v[6] = {0, 0, 0, 0, 0, 0};
     u8 st = VGA_ALN_PLACEHOLDER;
     u64 rc = 0, pc = 0, ce = 0, sn = 0, en = 0;
     if (best >= 0) {
         const AlignItem& it = items[best];
         st = (u8)(it.status >= IT_PENDING ? max_c_status : it.status);
-        s.chain = (u32)(best - (i32)item_off[r]);
+        v[0] = (u32)(best - (i32)item_off[r]);
         if (it.status == VGA_ALN_OK) {
-            s.path_len = it.path_len; s.start_off = it.start_off; s.end_off = it.end_off; s.n_aligned = it.n_aligned;
-            s.score = it.score; rc = it.n_runs; pc = it.n_path;
+            v[1] = it.path_len; v[2] = it.start_off; v[3] = it.end_off; v[4] = it.n_aligned; v[5] = (u32)it.score;
+            rc = it.n_runs; pc = it.n_path;
         }
         ce = it.cells; sn = it.S; en = it.E;
     }
-    status[r] = st; sc[r] = s; cells[r] = ce; run_cnt[r] = rc; path_cnt[r] = pc;
+    status[r] = st; cells[r] = ce; run_cnt[r] = rc; path_cnt[r] = pc;
+#pragma unroll
+    for (int q = 0; q < 6; q++) sc[(u64)q * n + r] = v[q];
     if (sub_cnt) { sub_cnt[r] = sn; edge_cnt[r] = en; }
 }
 
@@ -247,11 +302,11 @@ template <class T> static T d2h_one(const T* dptr, cudaStream_t st) {
 }
 
 static thread_local u64 g_d2h_bytes = 0;
-template <class T> static void d2h_append(std::vector<T>& dst, const T* dptr, size_t n, cudaStream_t st) {
+// device -> pinned result array (async on `st`)
+template <class T> static void d2h_into(HArr<T>& dst, const T* dptr, size_t n, cudaStream_t st) {
+    dst.alloc(n);
     g_d2h_bytes += n * sizeof(T);
-    size_t o = dst.size();
-    dst.resize(o + n);
-    if (n) VGA_CUDA(cudaMemcpyAsync(dst.data() + o, dptr, n * sizeof(T), cudaMemcpyDeviceToHost, st));
+    if (n) VGA_CUDA(cudaMemcpyAsync(dst.data(), dptr, n * sizeof(T), cudaMemcpyDeviceToHost, st));
 }
 
 // inclusive scan of in[0..n) into out[1..n], out[0]=0  (u64 output)
@@ -304,13 +359,15 @@ static int class_for_width(i64 w) {
 // one chunk of reads already resident on the device
 // returns false when the chunk must be split (too many anchors for 32-bit offsets)
 // ---------------------------------------------------------------------------------------------
-static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 n, u64 n_bases) {
+static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 n, u64 n_bases, OutSet& O) {
     vga_workspace* w = c.ws;
     cudaStream_t st = c.st;
     const DevIndex& dv = c.ix->dv;
     const VgaParams& P = *c.P;
     vga_results& R = *c.R;
     const bool dbg = P.flags & VGA_FLAG_KEEP_DEBUG;
+    const bool want_scores = dbg || (P.flags & VGA_FLAG_CHAIN_SCORES);
+    cudaStream_t st2 = w->st2;
     VGA_CUDA(cudaEventRecord(w->ev[0], st));
     // ---- K1 seeding
     SeedBuffers sb;
@@ -386,27 +443,26 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     stage_check(st, "chain_gather");
     VGA_CUDA(cudaEventRecord(w->ev[3], st));
 
-    // ---- per-chunk result bookkeeping (chains)
-    const u64 chain_base = R.chain_anchor_off.size() - 1, member_base = R.ca_id.size();
-    d2h_append(R.n_anchors, sb.read_acnt, n, st);
-    std::vector<u64> h_chain_off(n + 1), h_caoff(NC + 1);
-    VGA_CUDA(cudaMemcpyAsync(h_chain_off.data(), chain_off, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
-    VGA_CUDA(cudaMemcpyAsync(h_caoff.data(), cg.chain_anchor_off, (NC + 1) * 8, cudaMemcpyDeviceToHost, st));
-    g_d2h_bytes += (n + 1) * 8ull + (NC + 1) * 8ull;
-    d2h_append(R.ca_id, cg.ca_id, NM, st); d2h_append(R.ca_qb, cg.ca_qb, NM, st); d2h_append(R.ca_tb, cg.ca_tb, NM, st);
-    d2h_append(R.ca_te, cg.ca_te, NM, st); d2h_append(R.ca_score, cg.ca_score, NM, st);
+    // ---- chain results leave on the copy stream while the alignment stages run
+    O.n = n; O.NC = NC; O.NM = NM;
+    VGA_CUDA(cudaEventRecord(w->ev_copy, st));
+    VGA_CUDA(cudaStreamWaitEvent(st2, w->ev_copy, 0));
+    d2h_into(O.n_anchors, (const u32*)sb.read_acnt, n, st2);
+    d2h_into(O.chain_off, (const u64*)chain_off, (size_t)n + 1, st2);
+    d2h_into(O.chain_anchor_off, (const u64*)cg.chain_anchor_off, NC + 1, st2);
+    d2h_into(O.ca_qb, (const u32*)cg.ca_qb, NM, st2); d2h_into(O.ca_tb, (const u32*)cg.ca_tb, NM, st2);
+    d2h_into(O.ca_te, (const u32*)cg.ca_te, NM, st2);
+    if (want_scores) { d2h_into(O.ca_id, (const u32*)cg.ca_id, NM, st2); d2h_into(O.ca_score, (const double*)cg.ca_score, NM, st2); }
     if (dbg) {
-        std::vector<u32> h_aoff(n + 1);
-        VGA_CUDA(cudaMemcpyAsync(h_aoff.data(), sb.read_aoff, (n + 1) * 4, cudaMemcpyDeviceToHost, st));
-        const u64 abase = R.dbg_qb.size();
-        d2h_append(R.dbg_qb, sb.a_qb, A, st); d2h_append(R.dbg_tb, sb.a_tb, A, st); d2h_append(R.dbg_te, sb.a_te, A, st);
-        d2h_append(R.dbg_sorted, val_out, A, st); d2h_append(R.dbg_f, cb.f, A, st); d2h_append(R.dbg_pred, cb.pred_dbg, A, st);
-        VGA_CUDA(cudaStreamSynchronize(st));
-        for (u32 i = 1; i <= n; i++) R.dbg_anchor_off.push_back(abase + h_aoff[i]);
+        u64* aoff64 = w->b[B_DBGSUBCNT].get<u64>(n + 1);
+        scan_to_offsets(c, sb.read_acnt, aoff64, n);
+        VGA_CUDA(cudaEventRecord(w->ev_copy, st));
+        VGA_CUDA(cudaStreamWaitEvent(st2, w->ev_copy, 0));
+        d2h_into(O.dbg_anchor_off, (const u64*)aoff64, (size_t)n + 1, st2);
+        d2h_into(O.dbg_qb, (const u32*)sb.a_qb, A, st2); d2h_into(O.dbg_tb, (const u32*)sb.a_tb, A, st2);
+        d2h_into(O.dbg_te, (const u32*)sb.a_te, A, st2); d2h_into(O.dbg_sorted, (const u32*)val_out, A, st2);
+        d2h_into(O.dbg_f, (const double*)cb.f, A, st2); d2h_into(O.dbg_pred, (const i32*)cb.pred_dbg, A, st2);
     }
-    VGA_CUDA(cudaStreamSynchronize(st));
-    for (u32 i = 1; i <= n; i++) R.chain_off.push_back(chain_base + h_chain_off[i]);
-    for (u64 i = 1; i <= NC; i++) R.chain_anchor_off.push_back(member_base + h_caoff[i]);
     R.stats.n_probes += total_k; R.stats.n_anchors += A; R.stats.n_positions_read += A; R.stats.n_chains += NC;
     R.stats.n_bases += n_bases;
     R.stats.lookup_bytes += n_bases + 32ull * total_k + 8ull * A + 16ull * A;
@@ -422,16 +478,24 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         scan_to_offsets(c, item_cnt, item_off, n);
         NI = (u32)d2h_one(item_off + n, st);
     }
-    const size_t rbase = R.aln_status.size();
     if (NI == 0) {
         // every read is a placeholder (or alignment was not requested)
-        R.aln_status.resize(rbase + n, VGA_ALN_PLACEHOLDER); R.aln_chain.resize(rbase + n, 0);
-        R.aln_path_len.resize(rbase + n, 0); R.aln_start_off.resize(rbase + n, 0); R.aln_end_off.resize(rbase + n, 0);
-        R.aln_n_aligned.resize(rbase + n, 0); R.aln_score.resize(rbase + n, 0); R.aln_cells.resize(rbase + n, 0);
-        for (u32 i = 0; i < n; i++) { R.aln_path_off.push_back(R.aln_path.size()); R.aln_run_off.push_back(R.aln_runs.size()); }
-        if (dbg) for (u32 i = 0; i < n; i++) { R.dbg_sub_off.push_back(R.dbg_sub_handles.size()); R.dbg_edge_off.push_back(R.dbg_edges.size() / 2); }
+        O.aln_status.alloc(n); O.aln_chain.alloc(n); O.aln_path_len.alloc(n); O.aln_start_off.alloc(n); O.aln_end_off.alloc(n);
+        O.aln_n_aligned.alloc(n); O.aln_score.alloc(n); O.aln_cells.alloc(n); O.aln_path_off.alloc((size_t)n + 1);
+        O.aln_run_off.alloc((size_t)n + 1); O.aln_path.alloc(0); O.aln_runs.alloc(0);
+        memset(O.aln_status.data(), VGA_ALN_PLACEHOLDER, n); memset(O.aln_chain.data(), 0, 4ull * n);
+        memset(O.aln_path_len.data(), 0, 4ull * n); memset(O.aln_start_off.data(), 0, 4ull * n);
+        memset(O.aln_end_off.data(), 0, 4ull * n); memset(O.aln_n_aligned.data(), 0, 4ull * n);
+        memset(O.aln_score.data(), 0, 4ull * n); memset(O.aln_cells.data(), 0, 8ull * n);
+        memset(O.aln_path_off.data(), 0, 8ull * (n + 1)); memset(O.aln_run_off.data(), 0, 8ull * (n + 1));
+        if (dbg) {
+            O.dbg_sub_off.alloc((size_t)n + 1); O.dbg_edge_off.alloc((size_t)n + 1); O.dbg_sub_handles.alloc(0); O.dbg_edges.alloc(0);
+            memset(O.dbg_sub_off.data(), 0, 8ull * (n + 1)); memset(O.dbg_edge_off.data(), 0, 8ull * (n + 1));
+        }
         VGA_CUDA(cudaEventRecord(w->ev[4], st)); VGA_CUDA(cudaEventRecord(w->ev[5], st)); VGA_CUDA(cudaEventRecord(w->ev[6], st));
         VGA_CUDA(cudaEventRecord(w->ev[7], st));
+        VGA_CUDA(cudaStreamSynchronize(st2));
+        VGA_CUDA(cudaStreamSynchronize(st));
         return true;
     }
     items = w->b[B_ITEMS].get<AlignItem>(NI);
@@ -529,9 +593,10 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u64 want_cells = est_total + est_total / 4 + warp_slack;
     u64 max_cells = (u64)((free_b + w->b[B_POOL].cap) * 0.6) / 2;
     if (want_cells > max_cells) want_cells = max_cells;
+    if (want_cells > (1ull << 34) - (1u << 20)) want_cells = (1ull << 34) - (1u << 20);   // row_toff: u32 in 4-cell units
     if (want_cells < (1ull << 24)) want_cells = 1ull << 24;
     pb.pool = w->b[B_POOL].get<u16>(want_cells);
-    pb.pool_cells = w->b[B_POOL].cap / 2;
+    pb.pool_cells = std::min<u64>(w->b[B_POOL].cap / 2, (1ull << 34) - 16);
     tbuf.pool = pb.pool;
     u32* d_work = w->b[B_WORK].get<u32>(NI);
     u32* d_status = w->b[B_STATUS].get<u32>(NI);
@@ -592,12 +657,12 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     // ---- selection + compaction
     i32* sel = w->b[B_SEL].get<i32>(n);
     u8* d_st8 = (u8*)w->b[B_STATUS].ensure(std::max<size_t>(4ull * NI, n));
-    ReadScalars* d_sc = w->b[B_SCAL].get<ReadScalars>(n);
+    u32* d_sc = w->b[B_SCAL].get<u32>(6ull * n);
     u64* d_cells = w->b[B_CELLS].get<u64>(n);
     u64* cnts = w->b[B_PCNT].get<u64>(4ull * n);
     u64* offs = w->b[B_POFF2].get<u64>(4ull * (n + 1));
-    select_kernel<<<(n + 255) / 256, 256, 0, st>>>(items, item_cnt, item_off, n, 6u, sel, d_st8, d_sc, d_cells, cnts, cnts + n,
-                                                   dbg ? cnts + 2ull * n : nullptr, cnts + 3ull * n);
+    select_kernel<<<(n + 255) / 256, 256, 0, st>>>(items, item_cnt, item_off, n, (u32)VGA_ALN_TOO_WIDE, sel, d_st8, d_sc, d_cells, cnts,
+                                                   cnts + n, dbg ? cnts + 2ull * n : nullptr, cnts + 3ull * n);
     c.launches++;
     const int nscan = dbg ? 4 : 2;
     u64 tots[4] = {0, 0, 0, 0};
@@ -612,32 +677,24 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     c.launches++;
     VGA_CUDA(cudaEventRecord(w->ev[6], st));
     // ---- D2H of the alignment results
-    std::vector<ReadScalars> h_sc(n);
-    std::vector<u64> h_roff(n + 1), h_poff(n + 1);
-    VGA_CUDA(cudaMemcpyAsync(h_sc.data(), d_sc, n * sizeof(ReadScalars), cudaMemcpyDeviceToHost, st));
-    VGA_CUDA(cudaMemcpyAsync(h_roff.data(), offs, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
-    VGA_CUDA(cudaMemcpyAsync(h_poff.data(), offs + (n + 1), (n + 1) * 8, cudaMemcpyDeviceToHost, st));
-    g_d2h_bytes += n * sizeof(ReadScalars) + 2ull * (n + 1) * 8;
-    const u64 run_base = R.aln_runs.size(), path_base = R.aln_path.size();
-    d2h_append(R.aln_status, d_st8, n, st);
-    d2h_append(R.aln_cells, d_cells, n, st);
-    d2h_append(R.aln_runs, d_runs, tots[0], st);
-    d2h_append(R.aln_path, d_path, tots[1], st);
-    std::vector<u64> h_soff, h_eoff;
+    d2h_into(O.aln_status, (const u8*)d_st8, n, st);
+    d2h_into(O.aln_cells, (const u64*)d_cells, n, st);
+    d2h_into(O.aln_chain, (const u32*)d_sc, n, st); d2h_into(O.aln_path_len, (const u32*)(d_sc + n), n, st);
+    d2h_into(O.aln_start_off, (const u32*)(d_sc + 2ull * n), n, st); d2h_into(O.aln_end_off, (const u32*)(d_sc + 3ull * n), n, st);
+    d2h_into(O.aln_n_aligned, (const u32*)(d_sc + 4ull * n), n, st); d2h_into(O.aln_score, (const i32*)(d_sc + 5ull * n), n, st);
+    d2h_into(O.aln_run_off, (const u64*)offs, (size_t)n + 1, st); d2h_into(O.aln_path_off, (const u64*)(offs + (n + 1)), (size_t)n + 1, st);
+    d2h_into(O.aln_runs, (const u32*)d_runs, tots[0], st);
+    d2h_into(O.aln_path, (const u64*)d_path, tots[1], st);
     if (dbg) {
         u64* d_sub = w->b[B_DBGSUB].get<u64>(tots[2]);
         u32* d_edges = w->b[B_DBGEDGE].get<u32>(2 * tots[3]);
         dbg_sub_kernel<<<std::min<u32>((n + 7) / 8, 148 * 16), 256, 0, st>>>(items, sel, n, offs + 2ull * (n + 1), offs + 3ull * (n + 1),
                                                                               sub.nd_handle, sub.nd_pred_off, sub.nd_pred, d_sub, d_edges);
         c.launches++;
-        h_soff.resize(n + 1); h_eoff.resize(n + 1);
-        VGA_CUDA(cudaMemcpyAsync(h_soff.data(), offs + 2ull * (n + 1), (n + 1) * 8, cudaMemcpyDeviceToHost, st));
-        VGA_CUDA(cudaMemcpyAsync(h_eoff.data(), offs + 3ull * (n + 1), (n + 1) * 8, cudaMemcpyDeviceToHost, st));
-        const u64 sbase = R.dbg_sub_handles.size(), ebase = R.dbg_edges.size() / 2;
-        d2h_append(R.dbg_sub_handles, d_sub, tots[2], st);
-        d2h_append(R.dbg_edges, d_edges, 2 * tots[3], st);
-        VGA_CUDA(cudaStreamSynchronize(st));
-        for (u32 i = 1; i <= n; i++) { R.dbg_sub_off.push_back(sbase + h_soff[i]); R.dbg_edge_off.push_back(ebase + h_eoff[i]); }
+        d2h_into(O.dbg_sub_off, (const u64*)(offs + 2ull * (n + 1)), (size_t)n + 1, st);
+        d2h_into(O.dbg_edge_off, (const u64*)(offs + 3ull * (n + 1)), (size_t)n + 1, st);
+        d2h_into(O.dbg_sub_handles, (const u64*)d_sub, tots[2], st);
+        d2h_into(O.dbg_edges, (const u32*)d_edges, 2 * tots[3], st);
     }
     // total cells over all items (GCUPS numerator)
     {
@@ -648,13 +705,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         for (u64 v : h_cells) R.stats.poa_cells += v;
     }
     VGA_CUDA(cudaEventRecord(w->ev[7], st));
+    VGA_CUDA(cudaStreamSynchronize(st2));
     VGA_CUDA(cudaStreamSynchronize(st));
-    for (u32 i = 0; i < n; i++) {
-        R.aln_chain.push_back(h_sc[i].chain); R.aln_path_len.push_back(h_sc[i].path_len);
-        R.aln_start_off.push_back(h_sc[i].start_off); R.aln_end_off.push_back(h_sc[i].end_off);
-        R.aln_n_aligned.push_back(h_sc[i].n_aligned); R.aln_score.push_back(h_sc[i].score);
-        R.aln_run_off.push_back(run_base + h_roff[i + 1]); R.aln_path_off.push_back(path_base + h_poff[i + 1]);
-    }
     R.stats.n_alignments += NI;
     R.stats.ms_poa += ms_fill; R.stats.ms_trace += ms_trace;
     return true;
@@ -676,16 +728,77 @@ static void add_stage_times(Ctx& c) {
 static void run_range(Ctx& c, const char* d_seqs, const u64* d_seq_off, const u64* h_seq_off, u32 b, u32 e) {
     if (b >= e) return;
     const u64 bases = h_seq_off[e] - h_seq_off[b];
-    const u64 MAX_BASES = 96ull << 20;
-    const u32 MAX_READS = 1u << 20;
+    const u64 MAX_BASES = 320ull << 20;
+    const u32 MAX_READS = 1u << 21;
     bool split = (e - b > 1) && (bases > MAX_BASES || e - b > MAX_READS);
     if (!split) {
-        if (process_chunk(c, d_seqs, d_seq_off + b, e - b, bases)) { add_stage_times(c); return; }
+        OutSet* O = new OutSet();
+        c.R->parts.push_back(O);
+        if (process_chunk(c, d_seqs, d_seq_off + b, e - b, bases, *O)) { add_stage_times(c); return; }
+        c.R->parts.pop_back();
+        O->release_all();
+        delete O;
         if (e - b == 1) { set_error("a single read produced more than 2^31 anchors"); throw CudaFail{VGA_ERR_UNSUPPORTED}; }
     }
     const u32 mid = b + (e - b) / 2;
     run_range(c, d_seqs, d_seq_off, h_seq_off, b, mid);
     run_range(c, d_seqs, d_seq_off, h_seq_off, mid, e);
+}
+
+// concatenate per-chunk outputs (only when a call needed more than one chunk)
+template <class T> static void cat_plain(HArr<T>& dst, std::vector<OutSet*>& parts, HArr<T> OutSet::*f) {
+    size_t tot = 0;
+    for (OutSet* p : parts) tot += (p->*f).n;
+    dst.alloc(tot);
+    size_t o = 0;
+    for (OutSet* p : parts) { memcpy(dst.data() + o, (p->*f).data(), (p->*f).n * sizeof(T)); o += (p->*f).n; }
+}
+// offsets arrays: each part has count+1 entries starting at 0; rebase by the running total of `payload`
+static void cat_offsets(HArr<u64>& dst, std::vector<OutSet*>& parts, HArr<u64> OutSet::*f) {
+    size_t tot = 1;
+    for (OutSet* p : parts) tot += (p->*f).n ? (p->*f).n - 1 : 0;
+    dst.alloc(tot);
+    dst[0] = 0;
+    size_t o = 1;
+    u64 base = 0;
+    for (OutSet* p : parts) {
+        const HArr<u64>& a = p->*f;
+        if (a.n == 0) continue;
+        for (size_t i = 1; i < a.n; i++) dst[o++] = base + a.data()[i];
+        base += a.data()[a.n - 1];
+    }
+}
+
+static void merge_parts(vga_results* R) {
+    if (R->parts.size() == 1) {
+        R->o = *R->parts[0];           // move the blocks (shallow copy, then forget the part)
+        delete R->parts[0];
+        R->parts.clear();
+        return;
+    }
+    OutSet& o = R->o;
+    auto& ps = R->parts;
+    for (OutSet* p : ps) { o.n += p->n; o.NC += p->NC; o.NM += p->NM; }
+    cat_plain(o.n_anchors, ps, &OutSet::n_anchors); cat_offsets(o.chain_off, ps, &OutSet::chain_off);
+    cat_offsets(o.chain_anchor_off, ps, &OutSet::chain_anchor_off);
+    cat_plain(o.ca_qb, ps, &OutSet::ca_qb); cat_plain(o.ca_tb, ps, &OutSet::ca_tb); cat_plain(o.ca_te, ps, &OutSet::ca_te);
+    if (R->scores) { cat_plain(o.ca_id, ps, &OutSet::ca_id); cat_plain(o.ca_score, ps, &OutSet::ca_score); }
+    cat_plain(o.aln_status, ps, &OutSet::aln_status); cat_plain(o.aln_chain, ps, &OutSet::aln_chain);
+    cat_plain(o.aln_path_len, ps, &OutSet::aln_path_len); cat_plain(o.aln_start_off, ps, &OutSet::aln_start_off);
+    cat_plain(o.aln_end_off, ps, &OutSet::aln_end_off); cat_plain(o.aln_n_aligned, ps, &OutSet::aln_n_aligned);
+    cat_plain(o.aln_score, ps, &OutSet::aln_score); cat_plain(o.aln_cells, ps, &OutSet::aln_cells);
+    cat_offsets(o.aln_path_off, ps, &OutSet::aln_path_off); cat_offsets(o.aln_run_off, ps, &OutSet::aln_run_off);
+    cat_plain(o.aln_path, ps, &OutSet::aln_path); cat_plain(o.aln_runs, ps, &OutSet::aln_runs);
+    if (R->debug) {
+        cat_offsets(o.dbg_anchor_off, ps, &OutSet::dbg_anchor_off); cat_plain(o.dbg_qb, ps, &OutSet::dbg_qb);
+        cat_plain(o.dbg_tb, ps, &OutSet::dbg_tb); cat_plain(o.dbg_te, ps, &OutSet::dbg_te);
+        cat_plain(o.dbg_sorted, ps, &OutSet::dbg_sorted); cat_plain(o.dbg_f, ps, &OutSet::dbg_f);
+        cat_plain(o.dbg_pred, ps, &OutSet::dbg_pred); cat_offsets(o.dbg_sub_off, ps, &OutSet::dbg_sub_off);
+        cat_plain(o.dbg_sub_handles, ps, &OutSet::dbg_sub_handles); cat_offsets(o.dbg_edge_off, ps, &OutSet::dbg_edge_off);
+        cat_plain(o.dbg_edges, ps, &OutSet::dbg_edges);
+    }
+    for (OutSet* p : ps) { p->release_all(); delete p; }
+    ps.clear();
 }
 
 static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, const char* d_seqs_in, const u64* d_off_in,
@@ -701,7 +814,9 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
         Ctx c;
         c.ix = ix; c.ws = workspace(ix); c.st = c.ws->st; c.P = params; c.R = R;
         R->n = n_reads;
-        R->begin(params->flags & VGA_FLAG_KEEP_DEBUG);
+        R->debug = params->flags & VGA_FLAG_KEEP_DEBUG;
+        R->scores = R->debug || (params->flags & VGA_FLAG_CHAIN_SCORES);
+        memset(&R->stats, 0, sizeof(R->stats));
         cudaEvent_t t0 = c.ws->ev[11];
         g_d2h_bytes = 0;
         std::vector<u64> h_off;
@@ -734,6 +849,14 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
             cudaEventElapsedTime(&th2d, t0, c.ws->ev[0]);
             R->stats.ms_h2d = th2d;
             run_range(c, d_seqs, d_off, h_off.data(), 0, n_reads);
+            merge_parts(R);
+        } else {
+            R->o.chain_off.alloc(1); R->o.chain_off[0] = 0; R->o.chain_anchor_off.alloc(1); R->o.chain_anchor_off[0] = 0;
+            R->o.aln_path_off.alloc(1); R->o.aln_path_off[0] = 0; R->o.aln_run_off.alloc(1); R->o.aln_run_off[0] = 0;
+            if (R->debug) {
+                R->o.dbg_anchor_off.alloc(1); R->o.dbg_anchor_off[0] = 0; R->o.dbg_sub_off.alloc(1); R->o.dbg_sub_off[0] = 0;
+                R->o.dbg_edge_off.alloc(1); R->o.dbg_edge_off[0] = 0;
+            }
         }
         VGA_CUDA(cudaEventRecord(c.ws->ev[9], c.st));
         VGA_CUDA(cudaStreamSynchronize(c.st));
@@ -771,21 +894,22 @@ int vga_map_batch_device(vga_index_t* ix, const char* dev_seqs, const uint64_t* 
 int vga_results_view(const vga_results_t* r, VgaResultsView* v) {
     if (!r || !v) { set_error("null argument"); return VGA_ERR_INVALID; }
     memset(v, 0, sizeof(*v));
+    const OutSet& o = r->o;
     v->n_reads = r->n;
-    v->n_anchors = r->n_anchors.data(); v->chain_off = r->chain_off.data();
-    v->n_chains = r->chain_anchor_off.size() - 1; v->chain_anchor_off = r->chain_anchor_off.data();
-    v->n_chain_anchors = r->ca_id.size();
-    v->ca_id = r->ca_id.data(); v->ca_qb = r->ca_qb.data(); v->ca_tb = r->ca_tb.data(); v->ca_te = r->ca_te.data();
-    v->ca_score = r->ca_score.data();
-    v->aln_status = r->aln_status.data(); v->aln_chain = r->aln_chain.data(); v->aln_path_off = r->aln_path_off.data();
-    v->aln_path = r->aln_path.data(); v->aln_run_off = r->aln_run_off.data(); v->aln_runs = r->aln_runs.data();
-    v->aln_path_len = r->aln_path_len.data(); v->aln_start_off = r->aln_start_off.data(); v->aln_end_off = r->aln_end_off.data();
-    v->aln_n_aligned = r->aln_n_aligned.data(); v->aln_score = r->aln_score.data(); v->aln_cells = r->aln_cells.data();
+    v->n_anchors = o.n_anchors.data(); v->chain_off = o.chain_off.data();
+    v->n_chains = o.chain_anchor_off.n ? o.chain_anchor_off.n - 1 : 0; v->chain_anchor_off = o.chain_anchor_off.data();
+    v->n_chain_anchors = o.ca_qb.n;
+    v->ca_qb = o.ca_qb.data(); v->ca_tb = o.ca_tb.data(); v->ca_te = o.ca_te.data();
+    if (r->scores) { v->ca_id = o.ca_id.data(); v->ca_score = o.ca_score.data(); }
+    v->aln_status = o.aln_status.data(); v->aln_chain = o.aln_chain.data(); v->aln_path_off = o.aln_path_off.data();
+    v->aln_path = o.aln_path.data(); v->aln_run_off = o.aln_run_off.data(); v->aln_runs = o.aln_runs.data();
+    v->aln_path_len = o.aln_path_len.data(); v->aln_start_off = o.aln_start_off.data(); v->aln_end_off = o.aln_end_off.data();
+    v->aln_n_aligned = o.aln_n_aligned.data(); v->aln_score = o.aln_score.data(); v->aln_cells = o.aln_cells.data();
     if (r->debug) {
-        v->dbg_anchor_off = r->dbg_anchor_off.data(); v->dbg_qb = r->dbg_qb.data(); v->dbg_tb = r->dbg_tb.data();
-        v->dbg_te = r->dbg_te.data(); v->dbg_sorted = r->dbg_sorted.data(); v->dbg_f = r->dbg_f.data();
-        v->dbg_pred = r->dbg_pred.data(); v->dbg_sub_off = r->dbg_sub_off.data(); v->dbg_sub_handles = r->dbg_sub_handles.data();
-        v->dbg_edge_off = r->dbg_edge_off.data(); v->dbg_edges = r->dbg_edges.data();
+        v->dbg_anchor_off = o.dbg_anchor_off.data(); v->dbg_qb = o.dbg_qb.data(); v->dbg_tb = o.dbg_tb.data();
+        v->dbg_te = o.dbg_te.data(); v->dbg_sorted = o.dbg_sorted.data(); v->dbg_f = o.dbg_f.data();
+        v->dbg_pred = o.dbg_pred.data(); v->dbg_sub_off = o.dbg_sub_off.data(); v->dbg_sub_handles = o.dbg_sub_handles.data();
+        v->dbg_edge_off = o.dbg_edge_off.data(); v->dbg_edges = o.dbg_edges.data();
     }
     return VGA_OK;
 }

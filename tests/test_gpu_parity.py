@@ -225,9 +225,12 @@ def test_c2_full_size_parity_and_repeatability():
     against the oracle, and a second call on the reused workspace returns the same bytes."""
     ix = vg.Index.build(fixture_path("graphs/2-DRB1-3123.gfa"), 11)
     reads = vg.simulate_reads(ix, 100000, 150, 0.01, 0.0005, 0.0005, 0.1, 77)
-    g = vg.map_reads(ix, reads)
+    g = vg.map_reads(ix, reads, chain_scores=True)
     o = orc.OracleIndex(ix).map_reads(reads, orc.default_params(), n_threads=32)
     assert_same(g, o, ["n_anchors", "chain_off", "chain_anchor_off", "ca_id", "ca_qb", "ca_tb", "ca_te", "ca_score"] + ALN)
-    g2 = vg.map_reads(ix, reads)
+    g2 = vg.map_reads(ix, reads, chain_scores=True)
     assert_same(g2, g, ["ca_id", "ca_score"] + ALN)
+    g3 = vg.map_reads(ix, reads)           # default: no ids / scores cross the bus
+    assert g3.ca_id.size == 0 and g3.ca_score.size == 0
+    assert_same(g3, g, ["ca_qb", "ca_tb", "ca_te"] + ALN)
     assert (g.aln_status == vg.ALN_OK).mean() > 0.9
