@@ -40,7 +40,7 @@ $(PKG)/vga_map: $(HOST)/vga_map_main.cpp $(PKG)/libvga_host.so $(PKG)/libvgalign
 oracle: oracle/_build/liboracle.so
 oracle/_build/liboracle.so: oracle/oracle.cpp oracle/oracle.h
 	mkdir -p oracle/_build
-	$(CXX) -O2 -std=c++17 -ffp-contract=off -fopenmp -fPIC -Wall -Wextra -shared -o $@ oracle/oracle.cpp
+	$(CXX) -O2 -std=c++17 -ffp-contract=off -pthread -fPIC -Wall -Wextra -shared -o $@ oracle/oracle.cpp
 
 clean:
 	rm -rf $(BUILD) $(PKG)/*.so $(PKG)/vga_map oracle/_build

@@ -10,7 +10,7 @@ through the reference-facing C-ABI call vga_map_batch with pinned HOST buffers, 
 copies inside the timed region.  Reads shard across ranks with no data-path collective; the index
 is replicated by ONE NCCL broadcast (weak scaling: fixed reads per GPU).
 
-`--impl reference` times the CPU implementation of the same path (the oracle port, OpenMP over
+`--impl reference` times the CPU implementation of the same path (the oracle port, worker threads over
 reads on all host cores; the Rust binary cannot be built in this image) on a bounded
 sample of the same workload.
 """
@@ -161,7 +161,7 @@ def main():
         line = dict(base)
         line.update({"impl": "reference", "value": rate, "ms_per_step": sec * 1e3,
                      "cpu_baseline": {"value": rate, "unit": "reads/s", "cores": threads, "kind": "port",
-                                      "sample": "%d reads of the workload per step, oracle port, OpenMP over reads" % n_sample},
+                                      "sample": "%d reads of the workload per step, oracle port, threads over reads" % n_sample},
                      "e2e": {"value": rate, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                      "gpu_launches": 0, "aligned_fraction": aligned / n_sample, "cpu_gcups": cells / sec / 1e9})
         print(json.dumps(line))
@@ -379,7 +379,7 @@ def main():
             n_sample = pick_cpu_sample(vg, orc, ix, reads, threads, args.cpu_seconds)
             rate, sec, _, cells = cpu_run(vg, orc, ix, reads, n_sample, threads, 1)
             line["cpu_baseline"] = {"value": rate, "unit": "reads/s", "cores": threads, "kind": "port",
-                                    "sample": "first %d reads of rank 0's shard, oracle port with OpenMP over reads, %.1f s" % (n_sample, sec),
+                                    "sample": "first %d reads of rank 0's shard, oracle port with threads over reads, %.1f s" % (n_sample, sec),
                                     "cpu_gcups": cells / sec / 1e9}
         print(json.dumps(line))
     if world > 1:

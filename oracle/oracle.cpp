@@ -5,7 +5,7 @@
 // the reference's O(N) scans (hash map for `kmer_pos_ref.contains`, binary search for rank/select,
 // no sequence clones) are marked "sane:".
 //
-// Build: g++ -O2 -std=c++17 -ffp-contract=off -fopenmp -shared -fPIC  (Rust never contracts a*b+c
+// Build: g++ -O2 -std=c++17 -ffp-contract=off -pthread -shared -fPIC  (Rust never contracts a*b+c
 // into an FMA, so neither may this file).
 #include "oracle.h"
 
@@ -18,9 +18,8 @@
 #include <string>
 #include <unordered_map>
 #include <vector>
-#ifdef _OPENMP
-#include <omp.h>
-#endif
+#include <atomic>
+#include <thread>
 
 namespace {
 
@@ -766,14 +765,23 @@ orc_results_t* orc_map_reads(const orc_index_t* o, const char* seqs, const uint6
     for (u32 b = 0; b < n_reads; b += CH) {
         u32 e = std::min(n_reads, b + CH);
         buf.assign(e - b, ReadResult());
-#ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic, 16) num_threads(n_threads > 0 ? n_threads : 1)
-#endif
-        for (int64_t r = b; r < (int64_t)e; r++)
-            map_one(o->ix, seqs + seq_off[r], seq_off[r + 1] - seq_off[r], *P, buf[r - b]);
+        // reads are independent: worker threads pull blocks of 16 reads from a shared counter
+        std::atomic<u32> next(b);
+        auto worker = [&]() {
+            for (;;) {
+                u32 r0 = next.fetch_add(16);
+                if (r0 >= e) break;
+                for (u32 r = r0; r < std::min(e, r0 + 16); r++)
+                    map_one(o->ix, seqs + seq_off[r], seq_off[r + 1] - seq_off[r], *P, buf[r - b]);
+            }
+        };
+        const int nt = n_threads > 1 ? n_threads : 1;
+        std::vector<std::thread> pool;
+        for (int t = 1; t < nt; t++) pool.emplace_back(worker);
+        worker();
+        for (auto& t : pool) t.join();
         for (u32 r = b; r < e; r++) R->append(buf[r - b], dbg);
     }
-    (void)n_threads;
     R->finish();
     return R;
 }

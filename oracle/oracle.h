@@ -71,7 +71,7 @@ double orc_score_anchor(uint64_t a_qb, uint64_t a_qe, uint64_t a_tb, uint64_t a_
                         uint64_t b_qe, uint64_t b_tb, uint64_t b_te, uint64_t seed_length, uint64_t max_gap);
 
 /* map_reads (src/map.rs:27-216) over reads given as concatenated bytes + n+1 offsets.
- * n_threads > 1 parallelises over reads (OpenMP) for the CPU baseline; results are identical. */
+ * n_threads > 1 parallelises over reads (std::thread workers) for the CPU baseline; results are identical. */
 orc_results_t* orc_map_reads(const orc_index_t*, const char* seqs, const uint64_t* seq_off, uint32_t n_reads,
                              const orc_params_t*, int n_threads);
 void orc_results_free(orc_results_t*);

@@ -1,0 +1,98 @@
+"""Multi-GPU plumbing for the map path: one process per GPU, reads sharded, index replicated.
+
+Reads are independent units (the reference's per-read closures share only the immutable `&Index`,
+reference src/map.rs:56-111 and 162-167), so the path shards with NO data-path collective:
+
+* the index image is ONE allocation, replicated by a single broadcast (NCCL over NVLink on the GPU
+  box; the same code runs over gloo with host tensors in the CPU tests);
+* rank r maps the contiguous read range [r*n/W, (r+1)*n/W) — output order must equal input order
+  (src/map.rs:123-133), so rank-ordered concatenation of the per-rank GAF text is the whole output;
+* the only other traffic is start-up scatter of the read shards from the rank that parsed the
+  FASTA/FASTQ file and the final gather of GAF text to it.
+
+torch.distributed is plumbing only; nothing here touches oracle/.
+"""
+import numpy as np
+
+
+def shard_bounds(n_reads, world):
+    """Contiguous read ranges: shard g is [g*n/W, (g+1)*n/W)."""
+    return [(g * n_reads) // world for g in range(world + 1)]
+
+
+class ReadShard:
+    """A slice of a read batch (duck-types vgaligner_b200.Reads for map_reads)."""
+
+    def __init__(self, seqs, offsets, names=None):
+        self.seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        self.n = len(self.offsets) - 1
+        self.names = names if names is not None else ["read%d" % i for i in range(self.n)]
+        self._h = None
+
+    def seq(self, i):
+        return self.seqs[int(self.offsets[i]):int(self.offsets[i + 1])].tobytes().decode()
+
+
+def shard_reads(reads, rank, world):
+    """The reads rank `rank` of `world` maps, rebased to offset 0."""
+    b = shard_bounds(reads.n, world)
+    lo, hi = b[rank], b[rank + 1]
+    o = np.asarray(reads.offsets[lo:hi + 1], dtype=np.uint64)
+    base = int(o[0]) if len(o) else 0
+    seqs = np.asarray(reads.seqs[base:int(o[-1])] if len(o) else np.zeros(0, np.uint8))
+    return ReadShard(seqs, o - np.uint64(base), list(reads.names[lo:hi]) if reads.names else None)
+
+
+def scatter_reads(reads, rank, world, dist, device=None, src=0):
+    """Rank `src` holds `reads` (others pass None); every rank returns its shard.
+
+    Point-to-point sends, two tensors per shard (bytes, offsets); names stay on `src` (only the GAF
+    writer needs them and it runs where the names are)."""
+    import torch
+    dev = device if device is not None else torch.device("cpu")
+    if world == 1:
+        return shard_reads(reads, 0, 1)
+    mine = None
+    meta = torch.zeros(2, dtype=torch.int64, device=dev)
+    for r in range(world):
+        if rank == src:
+            s = shard_reads(reads, r, world)
+            if r == src:
+                mine = s
+                continue
+            meta[0], meta[1] = s.n, int(s.offsets[-1]) if s.n else 0
+            dist.send(meta, r)
+            dist.send(torch.from_numpy(s.seqs.copy()).to(dev) if s.seqs.size else torch.zeros(1, dtype=torch.uint8, device=dev), r)
+            dist.send(torch.from_numpy(s.offsets.astype(np.int64)).to(dev), r)
+        elif rank == r:
+            dist.recv(meta, src)
+            n, nb = int(meta[0]), int(meta[1])
+            seqs_t = torch.empty(max(nb, 1), dtype=torch.uint8, device=dev)
+            offs_t = torch.empty(n + 1, dtype=torch.int64, device=dev)
+            dist.recv(seqs_t, src)
+            dist.recv(offs_t, src)
+            mine = ReadShard(seqs_t.cpu().numpy()[:nb], offs_t.cpu().numpy().astype(np.uint64))
+    return mine
+
+
+def broadcast_image(image, rank, dist, device=None, src=0):
+    """Replicate the index image (a uint8 tensor on `src`, None elsewhere) with ONE broadcast
+    (plus an 8-byte size broadcast so the receivers can allocate)."""
+    import torch
+    dev = device if device is not None else torch.device("cpu")
+    sz = torch.tensor([image.numel() if rank == src else 0], dtype=torch.int64, device=dev)
+    dist.broadcast(sz, src)
+    if rank != src:
+        image = torch.empty(int(sz.item()), dtype=torch.uint8, device=dev)
+    dist.broadcast(image, src)
+    return image
+
+
+def gather_text(text, rank, world, dist, dst=0):
+    """Rank-ordered concatenation of per-rank GAF text on `dst` (None elsewhere)."""
+    if world == 1:
+        return text
+    parts = [None] * world if rank == dst else None
+    dist.gather_object(text, parts, dst=dst)
+    return "".join(parts) if rank == dst else None
