@@ -87,26 +87,15 @@ __host__ __device__ static inline u64 kmer_slot_hash(u64 key) {
 static const i32 POA_NEG_INF = -(1 << 29);   // same sentinel as the oracle
 static const i32 POA_DEEP = -(1 << 30);      // generator value of masked cells (never wins a max)
 
-// trace cell bits (u16 per DP cell)
-enum : u16 {
-    TB_M = 1u << 0,        // some predecessor p: in band at j-1 and H(p,j-1)+s == H(i,j)
-    TB_E1 = 1u << 1,       // fresh deletion hit through E1'
-    TB_E2 = 1u << 2,       // fresh deletion hit through E2'
-    TB_HF1 = 1u << 3,      // H(i,j) == F1(i,j)
-    TB_HF2 = 1u << 4,      // H(i,j) == F2(i,j)
-    TB_E1OPEN = 1u << 5,   // H(i,j)-oe1 == E1'(i,j)
-    TB_E2OPEN = 1u << 6,
-    TB_F1OPEN = 1u << 7,   // H(i,j-1)-oe1 == F1(i,j)
-    TB_F2OPEN = 1u << 8,
-    TB_MATCH = 1u << 9,    // query base == graph base
-    TB_E1EXT = 1u << 10,   // in-node rows: E1'(i,j) == E1'(i-1,j)-e1 with (i-1,j) in band
-    TB_E2EXT = 1u << 11,
-};
+// per DP row: band, trace location and the reference score the row's trace words are relative to
+struct RowInfo { i32 beg, end; u32 toff; i32 ref; };        // toff: pool offset in 4-word (16 B) units
+// per subgraph node: band, row-maximum span and maximum of the node's LAST row
+struct NodeState { i32 beg, end, lpos, rpos, mx, pad0, pad1, pad2; };
 
 // per-item status while in flight (device side); final values are VGA_ALN_*
 enum : u32 {
     IT_PENDING = 100,
-    IT_RETRY_WIDER = 101,   // band wider than 32*C columns
+    IT_RETRY_WIDER = 101,   // does not fit this kernel instance (band wider than 32*C columns, or too many rows for FIXED)
     IT_RETRY_POOL = 102,    // trace pool exhausted in this wave
 };
 

@@ -90,25 +90,29 @@ struct PoaBuffers {
     const char* seqs;
     const u32* nd_row_start; const u32* nd_src; const u32* nd_pred_off; const u32* nd_pred;
     const i32* nd_first_succ; const i32* nd_remain_last;
-    // per node, written by the fill kernel for later rows / traceback
-    i32* nd_beg; i32* nd_end; i32* nd_lpos; i32* nd_rpos; u32* nd_store; u32* nd_ptoff;   // nd_store: pool offset (8-byte units) of the saved last row
-    // per row
-    i32* row_beg; u32* row_toff;
-    // trace pool
-    u16* pool; u64 pool_cells; unsigned long long* pool_ctr;
+    NodeState* nd_state;     // per node, written by the fill kernel for later nodes
+    RowInfo* rows;           // per row, written by the fill kernel for later rows / traceback
+    // trace pool: one 32-bit word per band cell
+    u32* pool; u64 pool_words; unsigned long long* pool_ctr;
     u32* work_ctr;
     i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
 };
-int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int C, int n_sms, cudaStream_t st);
+// kernel instances: classes 0..7 FIXED C=1..8 (qlen < 32*C), 8..10 SLIDE C=8,16,32
+int poa_class_count();
+int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P);
+int poa_class_wider(int cls);    // -1: none
+int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 
 struct TraceBuffers {
     u32 n_items; const u32* work; AlignItem* items;
-    const u32* nd_row_start; const u32* nd_pred_off; const u32* nd_pred;
-    const i32* row_beg; const u32* row_toff; const u16* pool; const u32* nd_ptoff;
+    const char* seqs;
+    const u32* nd_row_start; const u32* nd_src; const u32* nd_pred_off; const u32* nd_pred; const i32* nd_remain_last;
+    const RowInfo* rows; const u32* pool;
     u32* out_runs;           // per item region at out_base, capacity nrows+qlen+2, written back to front
     u32* out_path;           // per item region at node_base, capacity S, written back to front
+    i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
 };
-int launch_poa_trace(const TraceBuffers& b, cudaStream_t st);
+int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st);
 
 double measure_int32_peak();
 

@@ -5,14 +5,25 @@
 //
 // Fill kernel: one warp per (read, chain).  Rows (graph bases) are visited in subgraph node order,
 // which is a topological order because only edges s<e are kept (src/align.rs:717-718).  Each lane
-// owns C consecutive query columns of a cyclic block layout (column j -> block j/C -> lane
-// block%32), so the adaptive band can slide without moving data: the previous row's H/E1/E2 stay
-// in registers for all rows inside a node label; only the last row of every node is saved to the
-// pool, because only those rows can be predecessors of another node's first row.
+// owns C consecutive query columns.  FIXED instances (32*C > qlen) pin column j to lane j/C for the
+// whole alignment; SLIDE instances (long reads) use a cyclic block layout (column j -> block j/C ->
+// lane block%32) so the adaptive band can slide without moving data.  The previous row's H/E1'/E2'
+// stay in registers for all rows inside a node label.  The first row of a node rebuilds them from
+// the trace words of its predecessors' last rows.
+//
+// Trace: one 32-bit word per DP cell that holds the cell's complete state relative to H:
+//   bits  0..15  H(i,j) - ref(i), clamped to int16; ref(i) is 0 in the FIXED instances (scores are
+//                bounded by 6*(rows+qlen) there) and the previous row's maximum in the SLIDE instances,
+//                which also verify that no reachable cell was clamped
+//   bits 16..18  E1'(i,j) - (H(i,j) - o1 - e1)            in [0, o1]
+//   bits 19..23  E2'(i,j) - (H(i,j) - o2 - e2)            in [0, o2]
+//   bits 24..26  max(F1(i,j) - (H(i,j-1) - o1 - e1), -1) + 1   in [0, o1+1]
+//   bits 27..31  max(F2(i,j) - (H(i,j-1) - o2 - e2), -1) + 1   in [0, o2+1]
+// (bounds: E <= H, F(i,j) <= H(i,j-1) - e; proofs in DESIGN.md).  The traceback kernel re-derives
+// H/E1'/E2'/F1/F2 from these words and runs abPOA's value-driven backtrack exactly as the oracle
+// does, so no per-cell decision flags have to be computed in the fill loop.
 // The horizontal gap recurrences (F1,F2) are prefix-max scans: serial inside a lane, Kogge-Stone
-// across lanes with the constant decay e*C per lane.  Row maxima use REDUX.  Traceback state is a
-// 12-bit flag word per cell (u16) computed from the same equalities abPOA's value-driven
-// backtrack evaluates, so the traceback kernel reproduces its decisions without the H/E/F matrices.
+// across lanes with the constant decay e*C per lane.  Row maxima use REDUX.
 // Roofline: INT32 ALU (no tensor cores: nothing here is a contraction).  Algorithmic work =
 // band cells; see DESIGN.md for ops/cell.
 #include <climits>
@@ -24,18 +35,20 @@ namespace vga {
 
 static const int POA_WARPS = 4;
 static const u32 FULL = 0xffffffffu;
-static const u64 POOL_CHUNK = 16384;   // cells taken from the pool per refill
+static const u64 POOL_CHUNK = 8192;   // trace words taken from the pool per refill
 
 enum { M_OP = 1, E1_OP = 2, E2_OP = 4, F1_OP = 8, F2_OP = 16, ALL_OP = 31 };
 
 __device__ __forceinline__ i32 imax(i32 a, i32 b) { return a > b ? a : b; }
 __device__ __forceinline__ i32 imin(i32 a, i32 b) { return a < b ? a : b; }
+__device__ __forceinline__ i32 sext16(u32 w) { return (i32)(short)(w & 0xffffu); }
 
-template <int C>
+template <int C, bool SLIDE>
 __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, PoaBuffers b) {
     const u32 lane = threadIdx.x & 31;
     const i32 e1 = b.e1, e2 = b.e2, oe1 = b.o1 + b.e1, oe2 = b.o2 + b.e2;
-    u64 pool_cur = 0, pool_end = 0;      // this warp's current chunk of the trace pool (cells)
+    const i32 smatch = b.match, smis = -b.mismatch;
+    u64 pool_cur = 0, pool_end = 0;      // this warp's current chunk of the trace pool (words)
     for (;;) {
         u32 wi = 0;
         if (lane == 0) wi = atomicAdd(b.work_ctr, 1u);
@@ -50,61 +63,66 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
         const u32* __restrict__ rs = b.nd_row_start + nb;
         const u32* __restrict__ poff = b.nd_pred_off + nb;
         const u32* __restrict__ pl = b.nd_pred + it.pred_base;
+        NodeState* __restrict__ nst = b.nd_state + nb;
+        RowInfo* __restrict__ rows = b.rows + it.row_base;
         const i32 remain_src = b.nd_remain_last[nb] + (i32)(rs[1] - rs[0]) - 1 + 1;
         const i32 end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
         u32 status = VGA_ALN_OK;
+        // FIXED instances keep absolute H as int16: every DP step loses at most max(mismatch, o1+e1), so
+        // reachable scores are >= -that*(rows+qlen); longer alignments go to a SLIDE instance
+        if (!SLIDE && (qlen >= 32 * C || (i64)imax(b.mismatch, oe1) * ((i64)it.nrows + qlen) > 32000)) status = IT_RETRY_WIDER;
+        i32 mxrow = 0;                       // maximum of the previous row
         u64 cells = 0;
         i32 Hp[C], E1p[C], E2p[C];
         u32 qv[C];
         i32 qblk = INT_MIN, pbb = 0, ppb = 0, ppe = -1, lpos = 0, rpos = 0;
 #pragma unroll
-        for (int t = 0; t < C; t++) { Hp[t] = E1p[t] = E2p[t] = POA_NEG_INF; qv[t] = 0; }
-
-        // value of the combined predecessor row of node s at column j (first rows only)
-        auto pred_vals = [&](u32 po, u32 pn, i32 j, i32& hv, i32& x1, i32& x2) {
-            hv = POA_NEG_INF; x1 = POA_NEG_INF; x2 = POA_NEG_INF;
-            if (pn == 0) {                       // virtual source row
-                if (j >= 0 && j <= end0) {
-                    hv = j == 0 ? 0 : imax(-(b.o1 + b.e1 * j), -(b.o2 + b.e2 * j));
-                    if (j == 0) { x1 = -oe1; x2 = -oe2; }
-                }
-                return;
-            }
-            for (u32 x = 0; x < pn; x++) {
-                const u32 p = nb + pl[po + x];
-                const i32 pb = b.nd_beg[p], pe = b.nd_end[p];
-                if (j >= pb && j <= pe) {
-                    const i32* base = (const i32*)(b.pool + (u64)b.nd_store[p] * 4);
-                    const i32 Wp = pe - pb + 1;
-                    hv = imax(hv, base[j - pb]);
-                    x1 = imax(x1, base[Wp + j - pb]);
-                    x2 = imax(x2, base[2 * Wp + j - pb]);
-                }
-            }
-        };
+        for (int t = 0; t < C; t++) {
+            Hp[t] = E1p[t] = E2p[t] = POA_NEG_INF;
+            qv[t] = 0;
+            if (!SLIDE) { const i32 j = (i32)lane * C + t; if (j >= 1 && j <= qlen) qv[t] = q[j - 1]; }
+        }
 
         for (u32 s = 0; s < S && status == VGA_ALN_OK; s++) {
             const u32 len = rs[s + 1] - rs[s];
             const u32 src = b.nd_src[nb + s];
             const u32 po = poff[s], pn = poff[s + 1] - po;
             const i32 remain_last = b.nd_remain_last[nb + s];
+            // ---- predecessor summary (lane x holds predecessor x of the current chunk of 32)
+            i32 my_pb = INT_MAX, my_pe = -1, my_l = INT_MAX - 1, my_r = -1, my_mx = INT_MIN, my_ref = 0;
+            u32 my_toff = 0;
+            auto load_preds = [&](u32 x0) {
+                my_pb = INT_MAX; my_pe = -1; my_l = INT_MAX - 1; my_r = -1; my_mx = INT_MIN; my_ref = 0; my_toff = 0;
+                if (x0 + lane < pn) {
+                    const u32 p = pl[po + x0 + lane];
+                    const NodeState ns = nst[p];
+                    my_pb = ns.beg; my_pe = ns.end; my_l = ns.lpos; my_r = ns.rpos; my_mx = ns.mx;
+                    const RowInfo pr = rows[rs[p + 1] - 1];
+                    my_toff = pr.toff; my_ref = pr.ref;
+                }
+            };
+            i32 f_mpl = 1, f_mpr = 1, f_min_pb = 0, f_max_pe = end0, f_mx = 0;   // virtual source row
+            if (pn > 0) {
+                f_mpl = INT_MAX; f_mpr = 0; f_min_pb = INT_MAX; f_max_pe = -1; f_mx = INT_MIN;
+                for (u32 x0 = 0; x0 < pn; x0 += 32) {
+                    load_preds(x0);
+                    f_mpl = imin(f_mpl, __reduce_min_sync(FULL, my_l + 1));
+                    f_mpr = imax(f_mpr, __reduce_max_sync(FULL, my_r + 1));
+                    f_min_pb = imin(f_min_pb, __reduce_min_sync(FULL, my_pb));
+                    f_max_pe = imax(f_max_pe, __reduce_max_sync(FULL, my_pe));
+                    if (SLIDE) f_mx = imax(f_mx, __reduce_max_sync(FULL, my_mx));
+                }
+            }
+            u32 bases = 0;
             i32 beg = 0, end = 0;
             for (u32 o = 0; o < len; o++) {
                 const bool first = o == 0;
-                const u32 base = ix.seq_both[src + o];
+                if ((o & 31) == 0) bases = (o + lane < len) ? (u32)ix.seq_both[src + o + lane] : 0u;
+                const u32 base = __shfl_sync(FULL, bases, o & 31);
                 // ---- adaptive band (abPOA GET_AD_DP_BEGIN/END + clipping to the predecessors' bands)
                 i32 mpl, mpr, min_pb, max_pe;
                 if (!first) { mpl = lpos + 1; mpr = rpos + 1; min_pb = ppb; max_pe = ppe; }
-                else if (pn == 0) { mpl = 1; mpr = 1; min_pb = 0; max_pe = end0; }
-                else {
-                    mpl = INT_MAX; mpr = 0; min_pb = INT_MAX; max_pe = -1;
-                    for (u32 x = 0; x < pn; x++) {
-                        const u32 p = nb + pl[po + x];
-                        mpl = imin(mpl, b.nd_lpos[p] + 1); mpr = imax(mpr, b.nd_rpos[p] + 1);
-                        min_pb = imin(min_pb, b.nd_beg[p]); max_pe = imax(max_pe, b.nd_end[p]);
-                    }
-                    if (pn > 254) status = VGA_ALN_UNSUPPORTED;
-                }
+                else { mpl = f_mpl; mpr = f_mpr; min_pb = f_min_pb; max_pe = f_max_pe; }
                 const i32 r = qlen - (remain_last + (i32)(len - 1 - o));
                 beg = imax(0, imin(mpl, r) - wband);
                 end = imin(qlen, imax(mpr, r) + wband);
@@ -112,35 +130,34 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 end = imin(end, max_pe + 1);
                 if (beg > end) status = VGA_ALN_BAND_ERR;
                 const i32 W = end - beg + 1;
+                const i32 cbb = SLIDE ? beg / C : 0;
                 // the 32 lanes cover columns [cbb*C, (cbb+32)*C): the band must fit from its block-aligned start
-                if (status == VGA_ALN_OK && end - (beg / C) * C + 1 > 32 * C) status = IT_RETRY_WIDER;
-                // ---- pool space: W trace cells (+2W for the per-predecessor bytes of a first row)
-                const u64 Wr = (u64)((W + 3) & ~3);
-                const u64 need = first ? 3 * Wr : Wr;
+                if (SLIDE && status == VGA_ALN_OK && end - cbb * C + 1 > 32 * C) status = IT_RETRY_WIDER;
+                // ---- pool space: one trace word per band cell, rows start on 16-byte boundaries
+                const u64 need = (u64)((W + 3) & ~3);
                 if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
                     unsigned long long got = 0;
                     const u64 take = need > POOL_CHUNK ? need : POOL_CHUNK;
                     if (lane == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
                     got = __shfl_sync(FULL, got, 0);
-                    if (got + take > b.pool_cells) status = IT_RETRY_POOL;
+                    if (got + take > b.pool_words) status = IT_RETRY_POOL;
                     else { pool_cur = got; pool_end = got + take; }
                 }
                 if (status != VGA_ALN_OK) break;
-                u16* __restrict__ tr = b.pool + pool_cur;
-                u32* __restrict__ ptr = (u32*)(b.pool + pool_cur + Wr);
+                u32* __restrict__ tr = b.pool + pool_cur;
+                const i32 ref = SLIDE ? (first ? f_mx : mxrow) : 0;
                 if (lane == 0) {
-                    b.row_beg[it.row_base + rs[s] + o] = beg;
-                    b.row_toff[it.row_base + rs[s] + o] = (u32)(pool_cur >> 2);
-                    if (first) b.nd_ptoff[nb + s] = (u32)((pool_cur + Wr) >> 2);
+                    RowInfo ri;
+                    ri.beg = beg; ri.end = end; ri.toff = (u32)(pool_cur >> 2); ri.ref = ref;
+                    rows[rs[s] + o] = ri;
                 }
                 pool_cur += need;
                 cells += (u64)W;
                 // ---- column mapping of this row
-                const i32 cbb = beg / C;
-                const i32 cbl = cbb + (i32)((lane - (u32)cbb) & 31u);
+                const i32 cbl = SLIDE ? cbb + (i32)((lane - (u32)cbb) & 31u) : (i32)lane;
                 const i32 ll = cbl - cbb;                 // logical lane
                 const i32 j0 = cbl * C;
-                if (cbl != qblk) {
+                if (SLIDE && cbl != qblk) {
 #pragma unroll
                     for (int t = 0; t < C; t++) { const i32 j = j0 + t; qv[t] = (j >= 1 && j <= qlen) ? q[j - 1] : 0u; }
                     qblk = cbl;
@@ -148,12 +165,54 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 i32 hleft_old;
                 const u32 src_lane = (lane + 31) & 31;
                 if (first) {
-                    i32 d1, d2;
-                    pred_vals(po, pn, j0 - 1, hleft_old, d1, d2);
+                    // combined predecessor row: H at columns j0-1..j0+C-1, E1'/E2' at j0..j0+C-1
+                    hleft_old = POA_NEG_INF;
 #pragma unroll
-                    for (int t = 0; t < C; t++) pred_vals(po, pn, j0 + t, Hp[t], E1p[t], E2p[t]);
+                    for (int t = 0; t < C; t++) { Hp[t] = E1p[t] = E2p[t] = POA_NEG_INF; }
+                    if (pn == 0) {
+#pragma unroll
+                        for (int t = -1; t < C; t++) {
+                            const i32 j = j0 + t;
+                            if (j >= 0 && j <= end0) {
+                                const i32 hv = j == 0 ? 0 : imax(-(b.o1 + b.e1 * j), -(b.o2 + b.e2 * j));
+                                if (t < 0) hleft_old = hv;
+                                else { Hp[t < 0 ? 0 : t] = hv; if (j == 0) { E1p[t < 0 ? 0 : t] = -oe1; E2p[t < 0 ? 0 : t] = -oe2; } }
+                            }
+                        }
+                    } else {
+                        __syncwarp();       // trace words of earlier rows were written by other lanes
+                        for (u32 x0 = 0; x0 < pn; x0 += 32) {
+                            if (pn > 32) load_preds(x0);
+                            const u32 nh = imin(32, (i32)(pn - x0));
+                            for (u32 x = 0; x < nh; x++) {
+                                const i32 pb = __shfl_sync(FULL, my_pb, x), pe = __shfl_sync(FULL, my_pe, x);
+                                const i32 pref = SLIDE ? __shfl_sync(FULL, my_ref, x) : 0;
+                                const u32* __restrict__ tw = b.pool + (u64)__shfl_sync(FULL, my_toff, x) * 4;
+                                u32 wv[C + 1];
+#pragma unroll
+                                for (int t = -1; t < C; t++) {
+                                    const i32 j = j0 + t;
+                                    wv[t + 1] = (j >= pb && j <= pe) ? tw[j - pb] : 0xffff8000u;
+                                }
+#pragma unroll
+                                for (int t = -1; t < C; t++) {
+                                    const i32 j = j0 + t;
+                                    if (j >= pb && j <= pe) {
+                                        const u32 v = wv[t + 1];
+                                        const i32 hv = pref + sext16(v);
+                                        if (t < 0) hleft_old = imax(hleft_old, hv);
+                                        else {
+                                            Hp[t < 0 ? 0 : t] = imax(Hp[t < 0 ? 0 : t], hv);
+                                            E1p[t < 0 ? 0 : t] = imax(E1p[t < 0 ? 0 : t], hv - oe1 + (i32)((v >> 16) & 7u));
+                                            E2p[t < 0 ? 0 : t] = imax(E2p[t < 0 ? 0 : t], hv - oe2 + (i32)((v >> 19) & 31u));
+                                        }
+                                    }
+                                }
+                            }
+                        }
+                    }
                     ppb = min_pb; ppe = max_pe;
-                } else {
+                } else if (SLIDE) {
                     const i32 lv = __shfl_sync(FULL, Hp[C - 1], src_lane);
                     const i32 src_pblk = pbb + (i32)((src_lane - (u32)pbb) & 31u);
                     hleft_old = src_pblk == cbl - 1 ? lv : POA_NEG_INF;
@@ -162,21 +221,23 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
 #pragma unroll
                         for (int t = 0; t < C; t++) { Hp[t] = E1p[t] = E2p[t] = POA_NEG_INF; }
                     }
+                } else {
+                    hleft_old = __shfl_sync(FULL, Hp[C - 1], src_lane);
                 }
+                if (j0 == 0) hleft_old = POA_DEEP;       // column -1: M(i,0) does not exist
+                const i32 tlo = beg - j0, thi = end - j0;     // in band iff tlo <= t <= thi
                 // ---- sweep 1: Hhat = max(M, E1, E2) and the lane-local part of the F scans
                 i32 hh[C], f1l[C], f2l[C];
                 i32 run1 = POA_DEEP, run2 = POA_DEEP;
 #pragma unroll
                 for (int t = 0; t < C; t++) {
-                    const i32 j = j0 + t;
                     const i32 hd = t == 0 ? hleft_old : Hp[t - 1];
-                    const i32 sc = qv[t] == base ? b.match : -b.mismatch;
-                    const i32 m = j >= 1 ? hd + sc : POA_NEG_INF;
-                    hh[t] = imax(m, imax(E1p[t], E2p[t]));
-                    const i32 hg = (j >= beg && j <= end) ? hh[t] : POA_DEEP;
+                    const i32 sc = qv[t] == base ? smatch : smis;
+                    hh[t] = imax(imax(hd + sc, E1p[t]), E2p[t]);
+                    const i32 hg = (t >= tlo && t <= thi) ? hh[t] : POA_DEEP;
                     f1l[t] = run1; f2l[t] = run2;
-                    run1 = imax(hg - oe1, run1 - e1);
-                    run2 = imax(hg - oe2, run2 - e2);
+                    run1 = imax(run1 - e1, hg - oe1);
+                    run2 = imax(run2 - e2, hg - oe2);
                 }
                 // ---- cross-lane carry of F1/F2 (Kogge-Stone in logical lane order)
                 i32 v1 = run1, v2 = run2;
@@ -188,147 +249,69 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 }
                 i32 cin1 = __shfl_sync(FULL, v1, src_lane), cin2 = __shfl_sync(FULL, v2, src_lane);
                 if (ll == 0) { cin1 = POA_DEEP; cin2 = POA_DEEP; }
-                // ---- sweep 2: H, E', flags, masking, row maximum
-                u32 fl[C];
-                i32 oldh_prev = hleft_old, newh_prev = POA_NEG_INF, f1_0 = 0, f2_0 = 0;
-                i32 lmax = INT_MIN, lfirst = INT_MAX, llast = -1;
+                // ---- sweep 2: H, E', trace words, masking, row maximum
+                u32 wd[C];
+                i32 b1p = 0, b2p = 0, f1_0 = 0, f2_0 = 0;
+                i32 lmax = INT_MIN, lfirst = INT_MAX, llast = -1, lmin = INT_MAX;
 #pragma unroll
                 for (int t = 0; t < C; t++) {
                     const i32 j = j0 + t;
-                    const bool inb = j >= beg && j <= end;
+                    const bool inb = t >= tlo && t <= thi;
                     i32 f1 = imax(f1l[t], cin1 - e1 * t), f2 = imax(f2l[t], cin2 - e2 * t);
-                    if (j == beg) { f1 = POA_NEG_INF; f2 = POA_NEG_INF; }
+                    if (t == tlo) { f1 = POA_NEG_INF; f2 = POA_NEG_INF; }       // F(i,beg) does not exist
                     const i32 h = imax(hh[t], imax(f1, f2));
-                    const i32 x1 = E1p[t], x2 = E2p[t];
-                    const i32 n1 = imax(x1 - e1, h - oe1), n2 = imax(x2 - e2, h - oe2);
-                    const bool ismatch = qv[t] == base;
-                    const i32 m = j >= 1 ? oldh_prev + (ismatch ? b.match : -b.mismatch) : POA_NEG_INF;
-                    const bool pin_m = j - 1 >= ppb && j - 1 <= ppe && j >= 1;
-                    const bool pin_e = j >= ppb && j <= ppe;
-                    u32 f = 0;
-                    if (pin_m && m == h) f |= TB_M;
-                    if (pin_e && x1 == h) f |= TB_E1;
-                    if (pin_e && x2 == h) f |= TB_E2;
-                    if (h == f1) f |= TB_HF1;
-                    if (h == f2) f |= TB_HF2;
-                    if (h - oe1 == n1) f |= TB_E1OPEN;
-                    if (h - oe2 == n2) f |= TB_E2OPEN;
-                    if (ismatch) f |= TB_MATCH;
-                    if (pin_e && n1 == x1 - e1) f |= TB_E1EXT;
-                    if (pin_e && n2 == x2 - e2) f |= TB_E2EXT;
-                    if (t > 0) {
-                        if (newh_prev - oe1 == f1) f |= TB_F1OPEN;
-                        if (newh_prev - oe2 == f2) f |= TB_F2OPEN;
-                    } else { f1_0 = f1; f2_0 = f2; }
-                    fl[t] = f;
-                    oldh_prev = Hp[t];
+                    const i32 b1 = h - oe1, b2 = h - oe2;
+                    const i32 n1 = imax(E1p[t] - e1, b1), n2 = imax(E2p[t] - e2, b2);
+                    u32 wv = ((u32)imax(h - ref, -32768) & 0xffffu) + ((u32)(n1 - b1) << 16) + ((u32)(n2 - b2) << 19);
+                    if (SLIDE && inb && h > -(1 << 27)) lmin = imin(lmin, h);   // reachable cells only
+                    if (t > 0) wv += ((u32)imax(f1 - b1p + 1, 0) << 24) + ((u32)imax(f2 - b2p + 1, 0) << 27);
+                    else { f1_0 = f1; f2_0 = f2; }
+                    wd[t] = wv;
+                    b1p = b1; b2p = b2;
                     Hp[t] = inb ? h : POA_NEG_INF;
                     E1p[t] = inb ? n1 : POA_NEG_INF;
                     E2p[t] = inb ? n2 : POA_NEG_INF;
-                    newh_prev = Hp[t];
                     if (inb) {
                         if (h > lmax) { lmax = h; lfirst = j; }
                         if (h >= lmax) llast = j;
                     }
                 }
-                {   // F-open flags of the lane's first column need the left lane's new last H
+                {   // F fields of the lane's first column need the left lane's new last H
                     const i32 hl = __shfl_sync(FULL, Hp[C - 1], src_lane);
-                    if (ll > 0) {
-                        if (hl - oe1 == f1_0) fl[0] |= TB_F1OPEN;
-                        if (hl - oe2 == f2_0) fl[0] |= TB_F2OPEN;
-                    }
-                }
-                if (first) {
-                    // exact per-predecessor decisions in list order (backtrack tries predecessors in order)
-#pragma unroll
-                    for (int t = 0; t < C; t++) {
-                        const i32 j = j0 + t;
-                        if (j < beg || j > end) continue;
-                        const i32 h = Hp[t], n1 = E1p[t], n2 = E2p[t];
-                        const i32 sc = qv[t] == base ? b.match : -b.mismatch;
-                        u32 mp = 0xff, ep = 0xff, ex = 0, e1p = 0xff, e2p = 0xff;
-                        const u32 np = pn == 0 ? 1u : pn;
-                        for (u32 x = 0; x < np; x++) {
-                            i32 pb, pe, a1 = POA_NEG_INF, a2 = POA_NEG_INF, hm = POA_NEG_INF;
-                            if (pn == 0) {
-                                pb = 0; pe = end0;
-                                if (j - 1 >= 0 && j - 1 <= end0) hm = j - 1 == 0 ? 0 : imax(-(b.o1 + b.e1 * (j - 1)), -(b.o2 + b.e2 * (j - 1)));
-                                if (j == 0) { a1 = -oe1; a2 = -oe2; }
-                            } else {
-                                const u32 p = nb + pl[po + x];
-                                pb = b.nd_beg[p]; pe = b.nd_end[p];
-                                const i32* bs = (const i32*)(b.pool + (u64)b.nd_store[p] * 4);
-                                const i32 Wp = pe - pb + 1;
-                                if (j - 1 >= pb && j - 1 <= pe) hm = bs[j - 1 - pb];
-                                if (j >= pb && j <= pe) { a1 = bs[Wp + j - pb]; a2 = bs[2 * Wp + j - pb]; }
-                            }
-                                                        const bool in_m = j >= 1 && j - 1 >= pb && j - 1 <= pe;
-                            const bool in_e = j >= pb && j <= pe;
-                            if (mp == 0xff && in_m && hm + sc == h) mp = x;
-                            if (ep == 0xff && in_e) { if (a1 == h) { ep = x; ex = 1; } else if (a2 == h) { ep = x; ex = 2; } }
-                            if (e1p == 0xff && in_e && n1 == a1 - e1) e1p = x;
-                            if (e2p == 0xff && in_e && n2 == a2 - e2) e2p = x;
-                        }
-                        u32 f = fl[t] & ~(u32)(TB_M | TB_E1 | TB_E2 | TB_E1EXT | TB_E2EXT);
-                        if (mp != 0xff) f |= TB_M;
-                        if (ex == 1) f |= TB_E1;
-                        if (ex == 2) f |= TB_E2;
-                        if (e1p != 0xff) f |= TB_E1EXT;
-                        if (e2p != 0xff) f |= TB_E2EXT;
-                        fl[t] = f;
-                        ptr[j - beg] = mp | (ep << 8) | (e1p << 16) | (e2p << 24);
-                    }
+                    if (ll > 0) wd[0] += ((u32)imax(f1_0 - (hl - oe1) + 1, 0) << 24) + ((u32)imax(f2_0 - (hl - oe2) + 1, 0) << 27);
                 }
 #pragma unroll
                 for (int t = 0; t < C; t++) {
-                    const i32 j = j0 + t;
-                    if (j >= beg && j <= end) tr[j - beg] = (u16)fl[t];
+                    if (t >= tlo && t <= thi) tr[j0 + t - beg] = wd[t];
                 }
                 // ---- row maximum and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i)
                 const i32 mx = __reduce_max_sync(FULL, lmax);
                 lpos = __reduce_min_sync(FULL, lmax == mx ? lfirst : INT_MAX);
                 rpos = __reduce_max_sync(FULL, lmax == mx ? llast : -1);
-                pbb = cbb; ppb = beg; ppe = end;
+                pbb = cbb; ppb = beg; ppe = end; mxrow = mx;
+                // a reachable cell further than int16 below the row reference cannot be encoded
+                if (SLIDE && __any_sync(FULL, lmin != INT_MAX && lmin - ref < -32000)) status = VGA_ALN_UNSUPPORTED;
             }
             if (status != VGA_ALN_OK) break;
-            // ---- save the node's last row: it may be a predecessor of later nodes' first rows
-            {
-                const i32 W = end - beg + 1;
-                const u64 Wr = (u64)((W + 1) & ~1);
-                const u64 need = ((6 * Wr) + 3) & ~3ull;       // 3 ints per column, in u16 cells
-                if (pool_cur + need > pool_end) {
-                    unsigned long long got = 0;
-                    const u64 take = need > POOL_CHUNK ? need : POOL_CHUNK;
-                    if (lane == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
-                    got = __shfl_sync(FULL, got, 0);
-                    if (got + take > b.pool_cells) { status = IT_RETRY_POOL; break; }
-                    pool_cur = got; pool_end = got + take;
-                }
-                i32* st = (i32*)(b.pool + pool_cur);
-                const i32 cbl = pbb + (i32)((lane - (u32)pbb) & 31u);
-#pragma unroll
-                for (int t = 0; t < C; t++) {
-                    const i32 j = cbl * C + t;
-                    if (j >= beg && j <= end) { st[j - beg] = Hp[t]; st[W + j - beg] = E1p[t]; st[2 * W + j - beg] = E2p[t]; }
-                }
-                if (lane == 0) {
-                    b.nd_beg[nb + s] = beg; b.nd_end[nb + s] = end; b.nd_lpos[nb + s] = lpos; b.nd_rpos[nb + s] = rpos;
-                    b.nd_store[nb + s] = (u32)(pool_cur >> 2);
-                }
-                pool_cur += need;
-                __syncwarp();
+            // ---- the node's last row may be a predecessor of later nodes' first rows
+            if (lane == 0) {
+                NodeState ns;
+                ns.beg = beg; ns.end = end; ns.lpos = lpos; ns.rpos = rpos; ns.mx = mxrow; ns.pad0 = ns.pad1 = ns.pad2 = 0;
+                nst[s] = ns;
             }
+            __syncwarp();       // NodeState / RowInfo are read by other lanes when a later node loads its predecessors
         }
         // ---- global end: sink predecessors (nodes without successors, ascending) that reach column qlen
         i32 best = INT_MIN;
         u32 bs = 0xffffffffu;
         if (status == VGA_ALN_OK) {
+            __syncwarp();
             for (u32 s0 = 0; s0 < S; s0 += 32) {
                 const u32 s = s0 + lane;
                 i32 h = INT_MIN;
-                if (s < S && b.nd_first_succ[nb + s] < 0 && b.nd_end[nb + s] >= qlen) {
-                    const i32* st = (const i32*)(b.pool + (u64)b.nd_store[nb + s] * 4);
-                    h = st[qlen - b.nd_beg[nb + s]];
+                if (s < S && b.nd_first_succ[nb + s] < 0) {
+                    const RowInfo ri = rows[rs[s + 1] - 1];
+                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - ri.beg)]);
                 }
                 const i32 mx = __reduce_max_sync(FULL, h);
                 if (mx > best) {                             // strict: the first node wins ties
@@ -350,10 +333,13 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
 }
 
 // ---------------------------------------------------------------------------------------------
-// Traceback: one thread per alignment, abPOA's backtrack state machine driven by the flag words.
+// Traceback: one thread per alignment, abPOA's value-driven backtrack on the values re-derived
+// from the trace words (same order of tests as oracle/oracle.cpp poa_align()).
 // Runs and path nodes are written back to front, so they end up in alignment order.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) poa_trace_kernel(TraceBuffers b) {
+struct TCell { i32 h, e1, e2; bool ok; };
+
+__global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffers b) {
     const u32 idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= b.n_items) return;
     const u32 w = b.work[idx];
@@ -364,13 +350,20 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(TraceBuffers b) {
     const u32* __restrict__ rs = b.nd_row_start + nb;
     const u32* __restrict__ poff = b.nd_pred_off + nb;
     const u32* __restrict__ pl = b.nd_pred + it.pred_base;
+    const RowInfo* __restrict__ rows = b.rows + it.row_base;
+    const u8* __restrict__ q = (const u8*)b.seqs + it.q_off;
+    const i32 e1 = b.e1, e2 = b.e2, oe1 = b.o1 + b.e1, oe2 = b.o2 + b.e2;
+    const i32 qlen = (i32)it.qlen;
+    const i32 wband = b.wb + (i32)(b.wf * (float)qlen);
+    const i32 remain_src = b.nd_remain_last[nb] + (i32)(rs[1] - rs[0]) - 1 + 1;
+    const i32 end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
     const u32 cap = it.nrows + it.qlen + 2;
     u32* runs = b.out_runs + it.out_base;
     u32* path = b.out_path + nb;
     u32 wpos = cap, ppos = it.S;
     u32 cur_op = 0xffffffffu, cur_len = 0, n_aligned = 0, path_len = 0;
     u32 s = it.end_node, o = rs[s + 1] - rs[s] - 1;
-    i32 j = (i32)it.qlen;
+    i32 j = qlen;
     i32 cur = ALL_OP;
     bool at_source = false, err = false, have_row = false;
     u32 last_node = 0xffffffffu, start_off = 0, end_off = 0;
@@ -385,41 +378,84 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(TraceBuffers b) {
         if (!have_row) { end_off = o; have_row = true; }
         start_off = o;
     };
+    // state of cell (row r, column jj); ok = jj inside the row's band
+    auto cell = [&](u32 r, i32 jj) {
+        TCell c; c.h = c.e1 = c.e2 = POA_NEG_INF; c.ok = false;
+        const RowInfo ri = rows[r];
+        if (jj >= ri.beg && jj <= ri.end) {
+            const u32 v = b.pool[(u64)ri.toff * 4 + (u32)(jj - ri.beg)];
+            c.h = ri.ref + sext16(v); c.e1 = c.h - oe1 + (i32)((v >> 16) & 7u); c.e2 = c.h - oe2 + (i32)((v >> 19) & 31u);
+            c.ok = true;
+        }
+        return c;
+    };
+    auto source_cell = [&](i32 jj) {  // virtual source row
+        TCell c; c.h = c.e1 = c.e2 = POA_NEG_INF; c.ok = false;
+        if (jj >= 0 && jj <= end0) {
+            c.ok = true;
+            c.h = jj == 0 ? 0 : imax(-(b.o1 + b.e1 * jj), -(b.o2 + b.e2 * jj));
+            if (jj == 0) { c.e1 = -oe1; c.e2 = -oe2; }
+        }
+        return c;
+    };
     while (!at_source && j > 0) {
-        const u32 row = it.row_base + rs[s] + o;
-        const i32 rb = b.row_beg[row];
-        const u32 cell = b.pool[(u64)b.row_toff[row] * 4 + (u32)(j - rb)];
+        const u32 rowi = rs[s] + o;
+        const RowInfo ri = rows[rowi];
+        if (j < ri.beg || j > ri.end) { err = true; break; }
+        const u32 vij = b.pool[(u64)ri.toff * 4 + (u32)(j - ri.beg)];
+        const i32 hij = ri.ref + sext16(vij);
+        const i32 e1ij = hij - oe1 + (i32)((vij >> 16) & 7u), e2ij = hij - oe2 + (i32)((vij >> 19) & 31u);
+        const bool ismatch = q[j - 1] == ix.seq_both[b.nd_src[nb + s] + o];
+        const i32 sc = ismatch ? b.match : -b.mismatch;
+        const u32 po = poff[s], pn = poff[s + 1] - po;
+        const u32 np = (o > 0 || pn == 0) ? 1u : pn;       // predecessor rows of (s,o)
+        auto pred_cell = [&](u32 kx, i32 jj) {
+            if (o > 0) return cell(rowi - 1, jj);
+            if (pn == 0) return source_cell(jj);
+            const u32 p = pl[po + kx];
+            return cell(rs[p + 1] - 1, jj);
+        };
+        bool hit = false;
+        i32 chosen = -1;
         const i32 jc = j;
-        const bool first = o == 0;
-        bool hit = false, fresh = false;
-        int kind = 0, which = 0;      // kind 1 = M move, 2 = D move
         for (int attempt = 0; attempt < 2 && !hit; attempt++) {
-            if ((cur & M_OP) && (cell & TB_M)) {
-                push((cell & TB_MATCH) ? 0u : 1u);
-                visit_row();
-                n_aligned++;
-                j--;
-                cur = ALL_OP;
-                kind = 1; hit = true;
+            if (cur & M_OP) {
+                for (u32 kx = 0; kx < np; kx++) {
+                    const TCell c = pred_cell(kx, jc - 1);
+                    if (!c.ok) continue;
+                    if (c.h + sc == hij) {
+                        push(ismatch ? 0u : 1u);
+                        visit_row();
+                        n_aligned++;
+                        chosen = (i32)kx; j--; cur = ALL_OP; hit = true;
+                        break;
+                    }
+                }
             }
             if (!hit && (cur & (E1_OP | E2_OP))) {
-                fresh = (cur & M_OP) != 0;
-                which = 0;
-                if (cur & E1_OP) { if (fresh ? (cell & TB_E1) : (cell & TB_E1EXT)) which = 1; }
-                if (!which && (cur & E2_OP)) { if (fresh ? (cell & TB_E2) : (cell & TB_E2EXT)) which = 2; }
-                if (which) {
-                    push(2u);
-                    visit_row();
-                    cur = which == 1 ? E1_OP : E2_OP;     // refined below from the predecessor cell
-                    kind = 2; hit = true;
+                for (u32 kx = 0; kx < np && !hit; kx++) {
+                    const TCell c = pred_cell(kx, jc);
+                    if (!c.ok) continue;
+                    if (cur & E1_OP) {
+                        const bool t = (cur & M_OP) ? (hij == c.e1) : (e1ij == c.e1 - e1);
+                        if (t) { cur = (c.h - oe1 == c.e1) ? (M_OP | F1_OP | F2_OP) : E1_OP; hit = true; }
+                    }
+                    if (!hit && (cur & E2_OP)) {
+                        const bool t = (cur & M_OP) ? (hij == c.e2) : (e2ij == c.e2 - e2);
+                        if (t) { cur = (c.h - oe2 == c.e2) ? (M_OP | F1_OP | F2_OP) : E2_OP; hit = true; }
+                    }
+                    if (hit) { push(2u); visit_row(); chosen = (i32)kx; }
                 }
             }
-            if (!hit && (cur & (F1_OP | F2_OP)) && j > rb) {
+            if (!hit && (cur & (F1_OP | F2_OP)) && jc > ri.beg) {
+                const i32 hl = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(jc - 1 - ri.beg)]);
                 if (cur & F1_OP) {
-                    if (!(cur & M_OP) || (cell & TB_HF1)) { cur = (cell & TB_F1OPEN) ? (M_OP | E1_OP | E2_OP) : F1_OP; hit = true; }
+                    const i32 f = hl - oe1 + (i32)((vij >> 24) & 7u) - 1;
+                    if (!(cur & M_OP) || hij == f) { cur = (hl - oe1 == f) ? (M_OP | E1_OP | E2_OP) : F1_OP; hit = true; }
                 }
                 if (!hit && (cur & F2_OP)) {
-                    if (!(cur & M_OP) || (cell & TB_HF2)) { cur = (cell & TB_F2OPEN) ? (M_OP | E1_OP | E2_OP) : F2_OP; hit = true; }
+                    const i32 f = hl - oe2 + (i32)((vij >> 27) & 31u) - 1;
+                    if (!(cur & M_OP) || hij == f) { cur = (hl - oe2 == f) ? (M_OP | E1_OP | E2_OP) : F2_OP; hit = true; }
                 }
                 if (hit) { push(3u); j--; }
             }
@@ -429,26 +465,10 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(TraceBuffers b) {
             }
         }
         if (!hit) { err = true; break; }
-        if (kind) {
-            const u32 po = poff[s], pn = poff[s + 1] - po;
-            if (!first) {
-                o--;
-            } else if (pn == 0) {
-                at_source = true;
-            } else {
-                const u32 pt = ((const u32*)(b.pool + (u64)b.nd_ptoff[nb + s] * 4))[jc - rb];
-                u32 k = kind == 1 ? (pt & 0xff) : fresh ? ((pt >> 8) & 0xff) : which == 1 ? ((pt >> 16) & 0xff) : ((pt >> 24) & 0xff);
-                if (k >= pn) { err = true; break; }      // inconsistent trace word: report, never fault
-                s = pl[po + k];
-                o = rs[s + 1] - rs[s] - 1;
-            }
-            if (kind == 2 && !at_source) {
-                const u32 rowp = it.row_base + rs[s] + o;
-                if (jc < b.row_beg[rowp]) { err = true; break; }
-                const u32 cellp = b.pool[(u64)b.row_toff[rowp] * 4 + (u32)(jc - b.row_beg[rowp])];
-                const bool opened = cellp & (which == 1 ? TB_E1OPEN : TB_E2OPEN);
-                cur = opened ? (M_OP | F1_OP | F2_OP) : (which == 1 ? E1_OP : E2_OP);
-            }
+        if (chosen >= 0) {            // moved to a predecessor row
+            if (o > 0) o--;
+            else if (pn == 0) at_source = true;
+            else { s = pl[po + (u32)chosen]; o = rs[s + 1] - rs[s] - 1; }
         }
     }
     if (err) {
@@ -464,34 +484,56 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(TraceBuffers b) {
     itp->start_off = start_off; itp->end_off = end_off;
 }
 
-int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int C, int n_sms, cudaStream_t st) {
-    if (b.n_items == 0) return 0;
+// instances: FIXED C = 1..8 (reads up to 255 bases), SLIDE C = 8, 16, 32 (bands up to 1024 columns)
+int poa_class_count() { return 11; }
+int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
+    const i64 step = P.mismatch > P.o1 + P.e1 ? P.mismatch : P.o1 + P.e1;
+    if (qlen < 256 && step * (nrows + qlen) <= 32000) return (int)(qlen / 32);   // FIXED, C = class + 1 (32*C > qlen)
+    if (west <= 256 - 8) return 8;
+    if (west <= 512 - 16) return 9;
+    return 10;
+}
+int poa_class_wider(int cls) { return cls < 8 ? 8 : cls < 10 ? cls + 1 : -1; }
+
+template <int C, bool SLIDE>
+static void launch_fill(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
     // persistent warps pulling work from a counter; enough CTAs to fill every SM
-    int per_sm = C <= 2 ? 12 : C <= 4 ? 10 : C <= 8 ? 6 : 3;
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, poa_fill_kernel<C, SLIDE>, POA_WARPS * 32, 0);
+    if (per_sm < 1) per_sm = 1;
     long long ctas = (long long)n_sms * per_sm;
     long long need = ((long long)b.n_items + POA_WARPS - 1) / POA_WARPS;
     if (ctas > need) ctas = need;
     if (ctas < 1) ctas = 1;
-    dim3 g((unsigned)ctas), t(POA_WARPS * 32);
-    switch (C) {
-        case 1: poa_fill_kernel<1><<<g, t, 0, st>>>(ix, b); break;
-        case 2: poa_fill_kernel<2><<<g, t, 0, st>>>(ix, b); break;
-        case 4: poa_fill_kernel<4><<<g, t, 0, st>>>(ix, b); break;
-        case 8: poa_fill_kernel<8><<<g, t, 0, st>>>(ix, b); break;
-        case 16: poa_fill_kernel<16><<<g, t, 0, st>>>(ix, b); break;
-        default: poa_fill_kernel<32><<<g, t, 0, st>>>(ix, b); break;
+    poa_fill_kernel<C, SLIDE><<<(unsigned)ctas, POA_WARPS * 32, 0, st>>>(ix, b);
+}
+
+int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st) {
+    if (b.n_items == 0) return 0;
+    switch (cls) {
+        case 0: launch_fill<1, false>(ix, b, n_sms, st); break;
+        case 1: launch_fill<2, false>(ix, b, n_sms, st); break;
+        case 2: launch_fill<3, false>(ix, b, n_sms, st); break;
+        case 3: launch_fill<4, false>(ix, b, n_sms, st); break;
+        case 4: launch_fill<5, false>(ix, b, n_sms, st); break;
+        case 5: launch_fill<6, false>(ix, b, n_sms, st); break;
+        case 6: launch_fill<7, false>(ix, b, n_sms, st); break;
+        case 7: launch_fill<8, false>(ix, b, n_sms, st); break;
+        case 8: launch_fill<8, true>(ix, b, n_sms, st); break;
+        case 9: launch_fill<16, true>(ix, b, n_sms, st); break;
+        default: launch_fill<32, true>(ix, b, n_sms, st); break;
     }
     return 1;
 }
 
-int launch_poa_trace(const TraceBuffers& b, cudaStream_t st) {
+int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st) {
     if (b.n_items == 0) return 0;
-    poa_trace_kernel<<<(b.n_items + 127) / 128, 128, 0, st>>>(b);
+    poa_trace_kernel<<<(b.n_items + 127) / 128, 128, 0, st>>>(ix, b);
     return 1;
 }
 
 // ---------------------------------------------------------------------------------------------
-// INT32 ALU peak: independent IADD3 / VIMNMX streams, the instruction mix of the DP inner loop.
+// INT32 ALU peak: independent IADD / VIMNMX streams, the instruction mix of the DP inner loop.
 // ---------------------------------------------------------------------------------------------
 __global__ void int32_peak_kernel(int iters, int* out) {
     int a0 = threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -523,7 +565,7 @@ double measure_int32_peak() {
         if (ms < best) best = ms;
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
-    // per inner step: 8 adds + 8 max = 16 INT32 ops per thread
+    // per inner step: 8 adds + 8 max = 16 INT32 ops per thread (ptxas fuses each pair into one VIADDMNMX)
     double ops = (double)iters * 16.0 * 16.0 * (double)blocks * threads;
     return ops / (best * 1e-3);
 }

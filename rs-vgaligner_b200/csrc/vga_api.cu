@@ -44,7 +44,7 @@ enum {
     B_SEQS, B_SEQOFF, B_KOFF, B_KCNT, B_KSLOT, B_ACNT, B_AOFF, B_AQB, B_ATB, B_ATE, B_KEYIN, B_VALIN, B_KEYOUT, B_VALOUT,
     B_CUB, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
     B_CATE, B_CASC, B_GAP, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
-    B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDBEG, B_NDEND, B_NDL, B_NDR, B_NDST, B_NDPT, B_ROWBEG, B_ROWTOFF,
+    B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDSTATE, B_ROWS,
     B_POOL, B_WORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
     B_DBGSUBCNT, B_DBGSUBOFF, B_DBGSUB, B_DBGEDGECNT, B_DBGEDGEOFF, B_DBGEDGE, B_CELLS, B_COUNT
 };
@@ -349,12 +349,6 @@ static void upload_gapcost(Ctx& c, u32 k, u32 max_gap) {
     w->gap_k = k; w->gap_max = max_gap;
 }
 
-static int class_for_width(i64 w) {
-    int C = 1;
-    while (32 * C < w && C < 32) C <<= 1;
-    return C;
-}
-
 // ---------------------------------------------------------------------------------------------
 // one chunk of reads already resident on the device
 // returns false when the chunk must be split (too many anchors for 32-bit offsets)
@@ -562,47 +556,59 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     pb.items = items; pb.seqs = d_seqs;
     pb.nd_row_start = sub.nd_row_start; pb.nd_src = sub.nd_src; pb.nd_pred_off = sub.nd_pred_off; pb.nd_pred = sub.nd_pred;
     pb.nd_first_succ = sub.nd_first_succ; pb.nd_remain_last = sub.nd_remain_last;
-    pb.nd_beg = w->b[B_NDBEG].get<i32>(tot[0]); pb.nd_end = w->b[B_NDEND].get<i32>(tot[0]);
-    pb.nd_lpos = w->b[B_NDL].get<i32>(tot[0]); pb.nd_rpos = w->b[B_NDR].get<i32>(tot[0]);
-    pb.nd_store = w->b[B_NDST].get<u32>(tot[0]); pb.nd_ptoff = w->b[B_NDPT].get<u32>(tot[0]);
-    pb.row_beg = w->b[B_ROWBEG].get<i32>(tot[2]); pb.row_toff = w->b[B_ROWTOFF].get<u32>(tot[2]);
+    pb.nd_state = w->b[B_NDSTATE].get<NodeState>(tot[0]);
+    pb.rows = w->b[B_ROWS].get<RowInfo>(tot[2]);
     pb.match = P.match; pb.mismatch = P.mismatch; pb.o1 = P.o1; pb.e1 = P.e1; pb.o2 = P.o2; pb.e2 = P.e2; pb.wb = P.wb; pb.wf = P.wf;
     pb.work_ctr = ctr + 2; pb.pool_ctr = (unsigned long long*)(ctr + 4);
     TraceBuffers tbuf;
     memset(&tbuf, 0, sizeof(tbuf));
-    tbuf.items = items; tbuf.nd_row_start = sub.nd_row_start; tbuf.nd_pred_off = sub.nd_pred_off; tbuf.nd_pred = sub.nd_pred;
-    tbuf.row_beg = pb.row_beg; tbuf.row_toff = pb.row_toff; tbuf.nd_ptoff = pb.nd_ptoff;
+    tbuf.items = items; tbuf.seqs = d_seqs;
+    tbuf.nd_row_start = sub.nd_row_start; tbuf.nd_src = sub.nd_src; tbuf.nd_pred_off = sub.nd_pred_off; tbuf.nd_pred = sub.nd_pred;
+    tbuf.nd_remain_last = sub.nd_remain_last; tbuf.rows = pb.rows;
     tbuf.out_runs = w->b[B_OUTRUNS].get<u32>(tot[3]); tbuf.out_path = w->b[B_OUTPATH].get<u32>(tot[0]);
-    // estimated cells per item and its column class
+    tbuf.match = P.match; tbuf.mismatch = P.mismatch; tbuf.o1 = P.o1; tbuf.e1 = P.e1; tbuf.o2 = P.o2; tbuf.e2 = P.e2; tbuf.wb = P.wb; tbuf.wf = P.wf;
+    // estimated trace words per item and its kernel class; inside a class the large items go first
+    // (persistent warps pull work in list order, so the long alignments do not end up as a tail)
+    const int NCLS = poa_class_count();
     std::vector<u64> est(NI);
-    std::vector<std::vector<u32>> cls(6);     // C = 1,2,4,8,16,32
+    std::vector<std::vector<u32>> cls(NCLS);
     u64 est_total = 0;
-    for (u32 i = 0; i < NI; i++) {
-        const i64 nrows = h_meta[i], qlen = h_meta[NI + i], S = h_meta[2ull * NI + i];
-        const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
-        const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
-        est[i] = (u64)((nrows + 9 * S) * (west + 4));
-        est_total += est[i];
-        int C = class_for_width(west), ci = 0;
-        while ((1 << ci) < C) ci++;
-        cls[ci].push_back(i);
+    {
+        const int NB = 48;
+        std::vector<std::vector<u32>> bucket((size_t)NCLS * NB);
+        for (u32 i = 0; i < NI; i++) {
+            const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
+            const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
+            const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
+            est[i] = (u64)(nrows * (west + 4));
+            est_total += est[i];
+            const int ci = poa_class_for(qlen, nrows, west, P);
+            int lb = 0;
+            while (lb < NB - 1 && (est[i] >> lb) > 1) lb++;
+            bucket[(size_t)ci * NB + (NB - 1 - lb)].push_back(i);
+        }
+        for (int ci = 0; ci < NCLS; ci++)
+            for (int q = 0; q < NB; q++) {
+                std::vector<u32>& v = bucket[(size_t)ci * NB + q];
+                cls[ci].insert(cls[ci].end(), v.begin(), v.end());
+            }
     }
     size_t free_b = 0, total_b = 0;
     VGA_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    const u64 warp_slack = (u64)w->n_sms * 64 * 16384;
-    u64 want_cells = est_total + est_total / 4 + warp_slack;
-    u64 max_cells = (u64)((free_b + w->b[B_POOL].cap) * 0.6) / 2;
-    if (want_cells > max_cells) want_cells = max_cells;
-    if (want_cells > (1ull << 34) - (1u << 20)) want_cells = (1ull << 34) - (1u << 20);   // row_toff: u32 in 4-cell units
-    if (want_cells < (1ull << 24)) want_cells = 1ull << 24;
-    pb.pool = w->b[B_POOL].get<u16>(want_cells);
-    pb.pool_cells = std::min<u64>(w->b[B_POOL].cap / 2, (1ull << 34) - 16);
+    const u64 warp_slack = (u64)w->n_sms * 64 * 8192;
+    u64 want_words = est_total + est_total / 4 + warp_slack;
+    u64 max_words = (u64)((free_b + w->b[B_POOL].cap) * 0.6) / 4;
+    if (want_words > max_words) want_words = max_words;
+    if (want_words > (1ull << 34) - (1u << 20)) want_words = (1ull << 34) - (1u << 20);   // RowInfo.toff: u32 in 4-word units
+    if (want_words < (1ull << 22)) want_words = 1ull << 22;
+    pb.pool = w->b[B_POOL].get<u32>(want_words);
+    pb.pool_words = std::min<u64>(w->b[B_POOL].cap / 4, (1ull << 34) - 16);
     tbuf.pool = pb.pool;
     u32* d_work = w->b[B_WORK].get<u32>(NI);
     u32* d_status = w->b[B_STATUS].get<u32>(NI);
     std::vector<u32> h_status(NI);
     float ms_fill = 0, ms_trace = 0;
-    for (int ci = 0; ci < 6; ci++) {
+    for (int ci = 0; ci < NCLS; ci++) {
         std::vector<u32>& list = cls[ci];
         size_t pos = 0;
         int stall = 0;
@@ -610,7 +616,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             // take a wave whose estimate fits the pool
             u64 acc = warp_slack;
             size_t end = pos;
-            while (end < list.size() && (end == pos || acc + est[list[end]] + est[list[end]] / 4 <= pb.pool_cells)) {
+            while (end < list.size() && (end == pos || acc + est[list[end]] + est[list[end]] / 4 <= pb.pool_words)) {
                 acc += est[list[end]] + est[list[end]] / 4;
                 end++;
             }
@@ -620,12 +626,12 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             pb.n_items = nw; pb.work = d_work;
             tbuf.n_items = nw; tbuf.work = d_work;
             VGA_CUDA(cudaEventRecord(w->ev[8], st));
-            c.launches += launch_poa_fill(dv, pb, 1 << ci, w->n_sms, st);
-    stage_check(st, "poa_fill");
+            c.launches += launch_poa_fill(dv, pb, ci, w->n_sms, st);
+            stage_check(st, "poa_fill");
             R.stats.poa_launches++;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
-            c.launches += launch_poa_trace(tbuf, st);
-    stage_check(st, "poa_trace");
+            c.launches += launch_poa_trace(dv, tbuf, st);
+            stage_check(st, "poa_trace");
             VGA_CUDA(cudaEventRecord(w->ev[10], st));
             item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
             c.launches++;
@@ -638,7 +644,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             u32 done = 0;
             for (u32 x = 0; x < nw; x++) {
                 const u32 it = list[pos + x];
-                if (h_status[x] == IT_RETRY_WIDER) { if (ci < 5) cls[ci + 1].push_back(it); else done++; }
+                if (h_status[x] == IT_RETRY_WIDER) { const int nc = poa_class_wider(ci); if (nc >= 0) cls[nc].push_back(it); else done++; }
                 else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
                 else done++;
             }
@@ -808,6 +814,14 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
     if (params->bandwidth == 0 || params->bandwidth > 96) { set_error("chaining bandwidth must be in 1..96"); return VGA_ERR_UNSUPPORTED; }
     if (params->best_n == 0 || params->min_anchors == 0) { set_error("best_n and min_anchors must be >= 1"); return VGA_ERR_INVALID; }
     if (params->max_gap > (1u << 24)) { set_error("max_gap too large"); return VGA_ERR_UNSUPPORTED; }
+    {   // the 32-bit trace word keeps E'/F relative to H in 3 + 5 bit fields (k_poa.cu): bounds on the gap model
+        const VgaParams& q = *params;
+        if (q.match < 0 || q.mismatch < 0 || q.e1 < 0 || q.e2 < 0 || q.o1 < 0 || q.o2 < 0 || q.o1 > 6 || q.o2 > 30 ||
+            q.e2 > q.o1 + q.e1 || q.e1 > q.o2 + q.e2 || q.match > 64 || q.mismatch > 64 || q.e1 > 64 || q.e2 > 64) {
+            set_error("POA gap model outside the supported range (o1 <= 6, o2 <= 30, e2 <= o1+e1, e1 <= o2+e2)");
+            return VGA_ERR_UNSUPPORTED;
+        }
+    }
     vga_results* R = new vga_results();
     try {
         VGA_CUDA(cudaSetDevice(ix->device));
