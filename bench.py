@@ -59,32 +59,65 @@ def build_index(vg, wl):
 
 
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons DURING the timed region.  NVML in-process (cheap); falls back to
+    spawning nvidia-smi when pynvml is not importable."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, gpu):
         super().__init__(daemon=True)
         self.gpu, self.rows, self.stop_flag = gpu, [], False
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # LOCAL_RANK indexes the visible devices; honour CUDA_VISIBLE_DEVICES when it lists ordinals
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = gpu
+            if vis:
+                parts = [x.strip() for x in vis.split(",") if x.strip()]
+                if gpu < len(parts) and parts[gpu].isdigit():
+                    idx = int(parts[gpu])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def sample(self):
+        if self.nvml is not None:
+            n = self.nvml
+            sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+            mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+            pw = n.nvmlDeviceGetPowerUsage(self.handle) / 1000.0
+            r = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+                else n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+            bits = [getattr(n, "nvmlClocksThrottleReasonHwSlowdown", 0x8), getattr(n, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                    getattr(n, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20), getattr(n, "nvmlClocksThrottleReasonSwPowerCap", 0x4)]
+            return [str(sm), str(mx), "%.1f" % pw] + ["Active" if (r & b) else "Not Active" for b in bits]
+        out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        return [x.strip() for x in out.split(",")] if out else None
 
     def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                row = self.sample()
+                if row:
+                    self.rows.append(row)
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.02 if self.nvml is not None else 0.2)
 
     def summary(self):
         self.stop_flag = True
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        reasons = sorted({self.NAMES[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        pw = [float(r[2]) for r in self.rows if len(r) > 2]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(self.rows), "power_w_max": max(pw) if pw else None,
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def cpu_run(vg, orc, ix, reads, n_sample, threads, steps):
@@ -293,8 +326,11 @@ def main():
             last = out
         return acc, last
 
-    for _ in range(args.warmup):
-        L.vga_results_free(step_device())
+    # warm-up in the same pattern as the timed loop (the previous step's results stay alive while the next
+    # step runs, so both sets of pinned result blocks exist before timing starts)
+    _, wlast = timed(step_device, args.warmup)
+    if wlast is not None:
+        L.vga_results_free(wlast)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -302,7 +338,6 @@ def main():
     acc, last = timed(step_device, args.steps)
     barrier()
     t_wall = time.perf_counter() - t_wall0
-    clocks = sampler.summary()
     ms_dev = sum(s["ms_total"] for s in acc)
 
     # aligned fraction from the last step's results
@@ -314,14 +349,17 @@ def main():
 
     e2e = None
     if not args.no_e2e:
-        for _ in range(1):
-            L.vga_results_free(step_host())
+        _, wlast = timed(step_host, max(1, min(args.warmup, 2)))
+        L.vga_results_free(wlast)
         barrier()
         acc_h, last_h = timed(step_host, args.steps)
         barrier()
         L.vga_results_free(last_h)
         ms_e2e = sum(s["ms_total"] for s in acc_h)
-        e2e = (ms_e2e, acc_h[-1]["h2d_bytes"], acc_h[-1]["d2h_bytes"])
+        e2e = (ms_e2e, acc_h[-1]["h2d_bytes"], acc_h[-1]["d2h_bytes"],
+               {k: sum(x[k] for x in acc_h) / len(acc_h) for k in ("ms_h2d", "ms_seed", "ms_sort", "ms_chain", "ms_subgraph", "ms_poa", "ms_trace", "ms_d2h", "ms_total")})
+
+    clocks = sampler.summary()      # sampled over both timed legs
 
     # max over ranks
     red = torch.tensor([ms_dev, e2e[0] if e2e else 0.0], dtype=torch.float64, device=dev)
@@ -373,7 +411,7 @@ def main():
                      "counts": {k: s[k] for k in ("n_probes", "n_anchors", "n_chains", "n_alignments", "poa_cells", "lookup_bytes")}})
         if e2e:
             line["e2e"] = {"value": total_reads * K / (ms_e2e_max * 1e-3), "unit": "reads/s",
-                           "h2d_bytes_per_step": int(e2e[1]), "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": ms_e2e_max / K}
+                           "h2d_bytes_per_step": int(e2e[1]), "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": ms_e2e_max / K, "stage_ms": e2e[3]}
         if not args.no_cpu_baseline:
             from oracle import binding as orc       # CPU baseline leg: the one place bench.py executes oracle/
             n_sample = pick_cpu_sample(vg, orc, ix, reads, threads, args.cpu_seconds)

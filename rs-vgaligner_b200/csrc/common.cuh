@@ -88,7 +88,11 @@ static const i32 POA_NEG_INF = -(1 << 29);   // same sentinel as the oracle
 static const i32 POA_DEEP = -(1 << 30);      // generator value of masked cells (never wins a max)
 
 // per DP row: band, trace location and the reference score the row's trace words are relative to
-struct RowInfo { i32 beg, end; u32 toff; i32 ref; };        // toff: pool offset in 4-word (16 B) units
+// toff: pool offset in 4-word (16 B) units; prow: row of the first predecessor (relative to the item's
+// row_base); meta: number of predecessor rows (low 24 bits, 0 = virtual source) | graph base << 24;
+// node/off: subgraph node index and offset inside its label.  Everything the traceback needs for a
+// row with a single predecessor is in this one 32-byte record.
+struct RowInfo { i32 beg, end; u32 toff; i32 ref; u32 prow, meta, node, off; };
 // per subgraph node: band, row-maximum span and maximum of the node's LAST row
 struct NodeState { i32 beg, end, lpos, rpos, mx, pad0, pad1, pad2; };
 

@@ -38,11 +38,13 @@ int launch_read_prep(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
 int launch_seed_count(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
 int launch_seed_emit(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
 
+static const int CHAIN_SMAX = 512;   // anchors per read the fused sort+chain kernel keeps in shared memory
 struct ChainBuffers {
     u32 n_reads;
     const u32* read_aoff;
     const u32* a_qb; const u32* a_tb; const u32* a_te;
-    const u32* sidx;          // sorted position -> local anchor id (per read segment)
+    u32* sidx;                // sorted position -> local anchor id (per read segment); written by the fused kernel
+    const u32* big_list; u32 n_big;   // reads with more than CHAIN_SMAX anchors (sorted by CUB)
     const double* gapcost;    // [max_gap+1]: 0.01*k*g + 0.5*log2(g), host-computed (src/chain.rs:348-354)
     double* f;                // by sorted position
     i32* pred;                // sorted position of the best predecessor, -1 = None (consumed by backtracking)
@@ -53,7 +55,9 @@ struct ChainBuffers {
     u32* cmem;                // chain members (sorted positions), region at 2*read_aoff[r] + 2*r
     u32 k, bandwidth, max_gap, min_anchors;
 };
-int launch_chain(const ChainBuffers& b, cudaStream_t st);
+int launch_chain_prep(const u64* aoff64, u32 n, u32* aoff32, u32* big_ctr, u32* big_list, u32* big_beg, u32* big_end,
+                      cudaStream_t st);
+int launch_chain(const ChainBuffers& b, bool fused, cudaStream_t st);
 
 struct ChainGather {
     u32 n_reads;

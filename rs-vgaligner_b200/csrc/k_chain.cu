@@ -9,6 +9,7 @@
 // host-computed table so no device transcendental is involved.  Scores are bit-identical to the
 // CPU evaluation, not merely within a tolerance.
 #include <cfloat>
+#include <climits>
 
 #include "common.cuh"
 #include "internal.h"
@@ -17,79 +18,117 @@ namespace vga {
 
 static const int CHAIN_WARPS = 4;
 static const int RING = 128;           // supports bandwidth <= 96 (checked by the caller)
+static const u32 FULLM = 0xffffffffu;
 
-// score_anchor (src/chain.rs:274-368) for forward/forward anchors of equal length k
-__device__ __forceinline__ double score_pair(u32 qb_a, u32 tb_a, u32 te_a, double f_a, u32 qb_b, u32 tb_b,
-                                             u32 te_b, u32 k, u32 max_gap, const double* __restrict__ gapcost) {
-    if (qb_a >= qb_b || te_a >= te_b) return -DBL_MAX;               // :277-311
+// score_anchor (src/chain.rs:274-368) for forward/forward anchors of equal length k, returned as the
+// integer round(x * 1000) the reference divides by 1000.0 (:360-363); INT_MIN stands for -f64::MAX.
+// The f64 score is a strictly increasing function of that integer, so every comparison of the
+// chaining DP (`>` at :430-447, `==` at :469) can be made on the integers, and only the winning
+// score of an anchor is turned back into the f64 the reference stores (one division per anchor).
+__device__ __forceinline__ i32 score_pair(u32 qb_a, u32 tb_a, u32 te_a, double f_a, u32 qb_b, u32 tb_b, u32 te_b,
+                                          u32 k, u32 max_gap, const double* __restrict__ gapcost) {
+    if (qb_a >= qb_b || te_a >= te_b) return INT_MIN;                 // :277-311
     const u32 ql = qb_b - qb_a;                                       // :313 (both terms are equal)
     const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;          // :324-327
     const u32 ted = te_b - te_a;                                      // :328-331
     const u32 tl = min(tbd, ted);
     const u32 g = ql > tl ? ql - tl : tl - ql;                        // :338-341
-    if (g > max_gap) return -DBL_MAX;                                 // :343-344
+    if (g > max_gap) return INT_MIN;                                  // :343-344
     const double gc = __ldg(gapcost + g);                             // :348-354
     const u32 ml = min(min(ql, tl), k);                               // :357
     double x = __dadd_rn(f_a, (double)ml);
     x = __dsub_rn(x, gc);
     x = __dmul_rn(x, 1000.0);
-    x = round(x);
-    x = __ddiv_rn(x, 1000.0);
-    return __dadd_rn(x, 0.0);                                         // + query_overlap (always 0) :360-363
+    return __double2int_rn(round(x));                                 // f64::round: half away from zero
 }
 
+// One warp per read.  FUSED: reads with at most CHAIN_SMAX anchors — the stable sort by
+// target_end.position (src/chain.rs:386-389) is a bitonic sort of (te, id) keys in shared memory,
+// and the integer scores / predecessor distances of the whole read stay in shared memory for the
+// backtracking.  !FUSED: the reads of big_list (more anchors than that), already sorted by CUB.
+template <bool FUSED>
 __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b) {
     __shared__ u32 s_q[CHAIN_WARPS][RING], s_tb[CHAIN_WARPS][RING], s_te[CHAIN_WARPS][RING];
     __shared__ double s_f[CHAIN_WARPS][RING];
+    __shared__ unsigned long long s_key[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
+    __shared__ i32 s_r[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
+    __shared__ u8 s_pd[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
     const u32 lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
     const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
     u32* rq = s_q[wl]; u32* rtb = s_tb[wl]; u32* rte = s_te[wl]; double* rf = s_f[wl];
-    const double kf = (double)b.k;
-    for (u32 r = warp; r < b.n_reads; r += n_warps) {
+    unsigned long long* keys = s_key[FUSED ? wl : 0];
+    i32* rr = s_r[FUSED ? wl : 0];
+    u8* pd = s_pd[FUSED ? wl : 0];
+    const i32 rk = (i32)b.k * 1000;                                       // Anchor::new: max_chain_score = k
+    const u32 n_work = FUSED ? b.n_reads : b.n_big;
+    for (u32 x = warp; x < n_work; x += n_warps) {
+        const u32 r = FUSED ? x : b.big_list[x];
         const u32 base = b.read_aoff[r];
         const u32 n = b.read_aoff[r + 1] - base;
         if (n == 0) {
             if (lane == 0) { b.n_chains[r] = 0; b.n_members[r] = 0; }
             continue;
         }
-        double curr_max = 0.0;                                           // :398
+        if (FUSED && n > CHAIN_SMAX) continue;                               // handled by the !FUSED pass
+        if (FUSED) {
+            // ---- stable sort by te: keys (te, id) are unique, so any sort is the stable one
+            u32 np2 = 32;
+            while (np2 < n) np2 <<= 1;
+            for (u32 i = lane; i < np2; i += 32)
+                keys[i] = i < n ? (((unsigned long long)b.a_te[base + i] << 32) | i) : ~0ull;
+            __syncwarp();
+            for (u32 k2 = 2; k2 <= np2; k2 <<= 1) {
+                for (u32 j = k2 >> 1; j > 0; j >>= 1) {
+                    for (u32 t = lane; t < (np2 >> 1); t += 32) {
+                        const u32 i = ((t & ~(j - 1)) << 1) | (t & (j - 1));   // the lower index of pair t
+                        const u32 p = i | j;
+                        const unsigned long long a = keys[i], c = keys[p];
+                        const bool up = (i & k2) == 0;
+                        if ((a > c) == up) { keys[i] = c; keys[p] = a; }
+                    }
+                    __syncwarp();
+                }
+            }
+            for (u32 i = lane; i < n; i += 32) b.sidx[base + i] = (u32)keys[i];
+        }
+        i32 r_max = 0;                                                   // curr_max = 0.0 (:398)
         for (u32 i = 0; i < n; i++) {
-            if ((i & 31) == 0) {           // stage the next 32 anchors of the sorted order (:386-389)
+            if ((i & 31) == 0) {           // stage the next 32 anchors of the sorted order
                 const u32 ii = i + lane;
                 if (ii < n) {
-                    const u32 id = b.sidx[base + ii];
+                    const u32 id = FUSED ? (u32)keys[ii] : b.sidx[base + ii];
                     rq[ii % RING] = b.a_qb[base + id];
                     rtb[ii % RING] = b.a_tb[base + id];
-                    rte[ii % RING] = b.a_te[base + id];
+                    rte[ii % RING] = FUSED ? (u32)(keys[ii] >> 32) : b.a_te[base + id];
                 }
                 __syncwarp();
             }
             const u32 si = i % RING;
             const u32 qb_i = rq[si], tb_i = rtb[si], te_i = rte[si];
-            double best = -DBL_MAX;
+            i32 best = INT_MIN;
             u32 bestd = 0x7fffffffu;
             for (u32 d0 = 0; d0 < b.bandwidth; d0 += 32) {               // j = i-1 down to max(0, i-bandwidth) :404-417
                 const u32 d = d0 + lane + 1;
                 if (d <= b.bandwidth && d <= i) {
                     const u32 sj = (i - d) % RING;
-                    const double s = score_pair(rq[sj], rtb[sj], rte[sj], rf[sj], qb_i, tb_i, te_i, b.k, b.max_gap, b.gapcost);
+                    const i32 s = score_pair(rq[sj], rtb[sj], rte[sj], rf[sj], qb_i, tb_i, te_i, b.k, b.max_gap, b.gapcost);
                     if (s > best) { best = s; bestd = d; }
                 }
             }
-            double m = best;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-            const u32 dmin = __reduce_min_sync(0xffffffffu, best == m ? bestd : 0x7fffffffu);
-            double f_i = kf;                                             // Anchor::new: max_chain_score = k
+            const i32 m = __reduce_max_sync(FULLM, best);
+            const u32 dmin = __reduce_min_sync(FULLM, best == m ? bestd : 0x7fffffffu);   // ties keep the nearest j
+            i32 r_i = rk;
             i32 p = -1;
-            if (m > kf) { f_i = m; p = (i32)(i - dmin); }                // :430-443 strict >
-            if (m > curr_max) curr_max = m;                              // :445-447 (all proposals)
+            if (m > rk) { r_i = m; p = (i32)(i - dmin); }                // :430-443 strict >
+            if (m > r_max) r_max = m;                                    // :445-447 (all proposals)
+            const double f_i = __ddiv_rn((double)r_i, 1000.0);           // :360-363
             if (lane == 0) {
                 rf[si] = f_i;
                 b.f[base + i] = f_i;
-                b.pred[base + i] = p;
-                if (b.pred_dbg) b.pred_dbg[base + i] = p < 0 ? -1 : (i32)b.sidx[base + p];
+                if (FUSED) { rr[i] = r_i; pd[i] = p < 0 ? 0 : (u8)dmin; }
+                else b.pred[base + i] = p;
+                if (b.pred_dbg) b.pred_dbg[base + i] = p < 0 ? -1 : (i32)(FUSED ? (u32)keys[p] : b.sidx[base + p]);
             }
             __syncwarp();
         }
@@ -98,23 +137,27 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
             u32* creg = b.cmem + 2ull * base + 2ull * r;
             u32* cl = b.clen + base + r;
             u32 n_ch = 0, tail = 0;
+            const double curr_max = __ddiv_rn((double)r_max, 1000.0);
             for (u32 i = n; i-- > 0;) {
-                if (b.pred[base + i] >= 0 && b.f[base + i] == curr_max) {     // :469 exact f64 equality
+                const bool cand = FUSED ? (pd[i] != 0 && rr[i] == r_max)
+                                        : (b.pred[base + i] >= 0 && b.f[base + i] == curr_max);     // :469
+                if (cand) {
                     const u32 start = tail;
                     u32 cur = i;
-                    i32 p;
-                    while ((p = b.pred[base + cur]) >= 0) {
-                        b.pred[base + cur] = -1;                         // :478 consume
-                        creg[tail++] = cur;
+                    for (;;) {
+                        i32 p;
+                        if (FUSED) { p = pd[cur] ? (i32)(cur - pd[cur]) : -1; pd[cur] = 0; }
+                        else { p = b.pred[base + cur]; b.pred[base + cur] = -1; }       // :478 consume
+                        creg[tail++] = cur;                              // :498 the terminal is pushed too
+                        if (p < 0) break;
                         cur = (u32)p;
                     }
-                    creg[tail++] = cur;                                  // :498 terminal (root or already consumed)
                     const u32 len = tail - start;
                     if (len >= b.min_anchors) {                          // :545-548
-                        for (u32 x = 0; x < len / 2; x++) {
-                            u32 t = creg[start + x];
-                            creg[start + x] = creg[tail - 1 - x];
-                            creg[tail - 1 - x] = t;
+                        for (u32 y = 0; y < len / 2; y++) {
+                            u32 t = creg[start + y];
+                            creg[start + y] = creg[tail - 1 - y];
+                            creg[tail - 1 - y] = t;
                         }
                         cl[n_ch++] = len;
                     } else {
@@ -126,6 +169,20 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
             b.n_members[r] = tail;
         }
         __syncwarp();
+    }
+}
+
+// anchors per read -> u32 offsets, plus the list of reads the fused kernel leaves to the CUB path
+__global__ void chain_prep_kernel(const u64* __restrict__ aoff64, u32 n, u32* __restrict__ aoff32, u32* big_ctr,
+                                  u32* __restrict__ big_list, u32* __restrict__ big_beg, u32* __restrict__ big_end) {
+    const u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r > n) return;
+    aoff32[r] = (u32)aoff64[r];
+    if (r == n) return;
+    const u64 cnt = aoff64[r + 1] - aoff64[r];
+    if (cnt > CHAIN_SMAX) {
+        const u32 x = atomicAdd(big_ctr, 1u);
+        big_list[x] = r; big_beg[x] = (u32)aoff64[r]; big_end[x] = (u32)aoff64[r + 1];
     }
 }
 
@@ -168,8 +225,16 @@ static int grid_for_warps(u32 n_items, int warps_per_cta) {
     return (int)ctas;
 }
 
-int launch_chain(const ChainBuffers& b, cudaStream_t st) {
-    chain_kernel<<<grid_for_warps(b.n_reads, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b);
+int launch_chain_prep(const u64* aoff64, u32 n, u32* aoff32, u32* big_ctr, u32* big_list, u32* big_beg, u32* big_end,
+                      cudaStream_t st) {
+    chain_prep_kernel<<<(n + 1 + 255) / 256, 256, 0, st>>>(aoff64, n, aoff32, big_ctr, big_list, big_beg, big_end);
+    return 1;
+}
+
+int launch_chain(const ChainBuffers& b, bool fused, cudaStream_t st) {
+    if (fused) chain_kernel<true><<<grid_for_warps(b.n_reads, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b);
+    else if (b.n_big) chain_kernel<false><<<grid_for_warps(b.n_big, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b);
+    else return 0;
     return 1;
 }
 

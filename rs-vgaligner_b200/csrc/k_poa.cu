@@ -90,14 +90,15 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
             const i32 remain_last = b.nd_remain_last[nb + s];
             // ---- predecessor summary (lane x holds predecessor x of the current chunk of 32)
             i32 my_pb = INT_MAX, my_pe = -1, my_l = INT_MAX - 1, my_r = -1, my_mx = INT_MIN, my_ref = 0;
-            u32 my_toff = 0;
+            u32 my_toff = 0, my_prow = 0, prow0 = 0;
             auto load_preds = [&](u32 x0) {
                 my_pb = INT_MAX; my_pe = -1; my_l = INT_MAX - 1; my_r = -1; my_mx = INT_MIN; my_ref = 0; my_toff = 0;
                 if (x0 + lane < pn) {
                     const u32 p = pl[po + x0 + lane];
                     const NodeState ns = nst[p];
                     my_pb = ns.beg; my_pe = ns.end; my_l = ns.lpos; my_r = ns.rpos; my_mx = ns.mx;
-                    const RowInfo pr = rows[rs[p + 1] - 1];
+                    my_prow = rs[p + 1] - 1;
+                    const RowInfo pr = rows[my_prow];
                     my_toff = pr.toff; my_ref = pr.ref;
                 }
             };
@@ -106,6 +107,7 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 f_mpl = INT_MAX; f_mpr = 0; f_min_pb = INT_MAX; f_max_pe = -1; f_mx = INT_MIN;
                 for (u32 x0 = 0; x0 < pn; x0 += 32) {
                     load_preds(x0);
+                    if (x0 == 0) prow0 = my_prow;           // lane 0: row of the first predecessor
                     f_mpl = imin(f_mpl, __reduce_min_sync(FULL, my_l + 1));
                     f_mpr = imax(f_mpr, __reduce_max_sync(FULL, my_r + 1));
                     f_min_pb = imin(f_min_pb, __reduce_min_sync(FULL, my_pb));
@@ -149,6 +151,9 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 if (lane == 0) {
                     RowInfo ri;
                     ri.beg = beg; ri.end = end; ri.toff = (u32)(pool_cur >> 2); ri.ref = ref;
+                    ri.prow = first ? prow0 : rs[s] + o - 1;
+                    ri.meta = (first ? (pn < 0xffffffu ? pn : 0xffffffu) : 1u) | (base << 24);
+                    ri.node = s; ri.off = o;
                     rows[rs[s] + o] = ri;
                 }
                 pool_cur += need;
@@ -351,6 +356,7 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     const u32* __restrict__ poff = b.nd_pred_off + nb;
     const u32* __restrict__ pl = b.nd_pred + it.pred_base;
     const RowInfo* __restrict__ rows = b.rows + it.row_base;
+    const u32* __restrict__ pool = b.pool;
     const u8* __restrict__ q = (const u8*)b.seqs + it.q_off;
     const i32 e1 = b.e1, e2 = b.e2, oe1 = b.o1 + b.e1, oe2 = b.o2 + b.e2;
     const i32 qlen = (i32)it.qlen;
@@ -362,7 +368,6 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     u32* path = b.out_path + nb;
     u32 wpos = cap, ppos = it.S;
     u32 cur_op = 0xffffffffu, cur_len = 0, n_aligned = 0, path_len = 0;
-    u32 s = it.end_node, o = rs[s + 1] - rs[s] - 1;
     i32 j = qlen;
     i32 cur = ALL_OP;
     bool at_source = false, err = false, have_row = false;
@@ -372,19 +377,11 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
         if (cur_len) runs[--wpos] = (cur_op << 28) | cur_len;
         cur_op = op; cur_len = 1;
     };
-    auto visit_row = [&]() {          // an M/X/D op consumes graph row (s,o)
-        path_len++;
-        if (s != last_node) { path[--ppos] = s; last_node = s; }
-        if (!have_row) { end_off = o; have_row = true; }
-        start_off = o;
-    };
-    // state of cell (row r, column jj); ok = jj inside the row's band
-    auto cell = [&](u32 r, i32 jj) {
+    auto word_at = [&](const RowInfo& r, i32 jj) -> u32 { return pool[(u64)r.toff * 4 + (u32)(jj - r.beg)]; };
+    auto decode = [&](const RowInfo& r, i32 jj, u32 v) {
         TCell c; c.h = c.e1 = c.e2 = POA_NEG_INF; c.ok = false;
-        const RowInfo ri = rows[r];
-        if (jj >= ri.beg && jj <= ri.end) {
-            const u32 v = b.pool[(u64)ri.toff * 4 + (u32)(jj - ri.beg)];
-            c.h = ri.ref + sext16(v); c.e1 = c.h - oe1 + (i32)((v >> 16) & 7u); c.e2 = c.h - oe2 + (i32)((v >> 19) & 31u);
+        if (jj >= r.beg && jj <= r.end) {
+            c.h = r.ref + sext16(v); c.e1 = c.h - oe1 + (i32)((v >> 16) & 7u); c.e2 = c.h - oe2 + (i32)((v >> 19) & 31u);
             c.ok = true;
         }
         return c;
@@ -398,43 +395,60 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
         }
         return c;
     };
+    // current row, its word at column j, and (single-predecessor rows) the predecessor's RowInfo, which
+    // is always fetched one step ahead so that a step costs one memory round trip
+    RowInfo ri = rows[rs[it.end_node + 1] - 1];
+    if (j < ri.beg || j > ri.end) { itp->status = VGA_ALN_TRACE_ERR; itp->score = 0; return; }
+    u32 vij = word_at(ri, j);
+    RowInfo rip = ri;
+    bool have_p = false;
     while (!at_source && j > 0) {
-        const u32 rowi = rs[s] + o;
-        const RowInfo ri = rows[rowi];
-        if (j < ri.beg || j > ri.end) { err = true; break; }
-        const u32 vij = b.pool[(u64)ri.toff * 4 + (u32)(j - ri.beg)];
+        const u32 np = ri.meta & 0xffffffu;
         const i32 hij = ri.ref + sext16(vij);
         const i32 e1ij = hij - oe1 + (i32)((vij >> 16) & 7u), e2ij = hij - oe2 + (i32)((vij >> 19) & 31u);
-        const bool ismatch = q[j - 1] == ix.seq_both[b.nd_src[nb + s] + o];
+        const bool ismatch = q[j - 1] == (u8)(ri.meta >> 24);
         const i32 sc = ismatch ? b.match : -b.mismatch;
-        const u32 po = poff[s], pn = poff[s + 1] - po;
-        const u32 np = (o > 0 || pn == 0) ? 1u : pn;       // predecessor rows of (s,o)
-        auto pred_cell = [&](u32 kx, i32 jj) {
-            if (o > 0) return cell(rowi - 1, jj);
-            if (pn == 0) return source_cell(jj);
-            const u32 p = pl[po + kx];
-            return cell(rs[p + 1] - 1, jj);
-        };
-        bool hit = false;
-        i32 chosen = -1;
         const i32 jc = j;
+        // ---- issue every load of this step together
+        if (np == 1 && !have_p) { rip = rows[ri.prow]; have_p = true; }
+        u32 wl = 0, wd = 0, wv = 0;
+        if (jc > ri.beg) wl = word_at(ri, jc - 1);
+        RowInfo rpp = rip;
+        bool have_pp = false;
+        if (np == 1) {
+            if (jc - 1 >= rip.beg && jc - 1 <= rip.end) wd = word_at(rip, jc - 1);
+            if (jc >= rip.beg && jc <= rip.end) wv = word_at(rip, jc);
+            if ((rip.meta & 0xffffffu) == 1u) { rpp = rows[rip.prow]; have_pp = true; }
+        }
+        const u32 po = np > 1 ? poff[ri.node] : 0;
+        RowInfo rsel = rip;               // row moved to by an M / D op
+        u32 wsel = 0;
+        auto pred_cell = [&](u32 kx, i32 jj, bool diag) {
+            if (np == 0) return source_cell(jj);
+            if (np == 1) { wsel = diag ? wd : wv; return decode(rip, jj, wsel); }
+            const u32 p = pl[po + kx];
+            rsel = rows[rs[p + 1] - 1];
+            wsel = (jj >= rsel.beg && jj <= rsel.end) ? word_at(rsel, jj) : 0u;
+            return decode(rsel, jj, wsel);
+        };
+        const u32 npl = np == 0 ? 1u : np;
+        bool hit = false, moved = false;
         for (int attempt = 0; attempt < 2 && !hit; attempt++) {
             if (cur & M_OP) {
-                for (u32 kx = 0; kx < np; kx++) {
-                    const TCell c = pred_cell(kx, jc - 1);
+                for (u32 kx = 0; kx < npl; kx++) {
+                    const TCell c = pred_cell(kx, jc - 1, true);
                     if (!c.ok) continue;
                     if (c.h + sc == hij) {
                         push(ismatch ? 0u : 1u);
-                        visit_row();
                         n_aligned++;
-                        chosen = (i32)kx; j--; cur = ALL_OP; hit = true;
+                        moved = true; j--; cur = ALL_OP; hit = true;
                         break;
                     }
                 }
             }
             if (!hit && (cur & (E1_OP | E2_OP))) {
-                for (u32 kx = 0; kx < np && !hit; kx++) {
-                    const TCell c = pred_cell(kx, jc);
+                for (u32 kx = 0; kx < npl && !hit; kx++) {
+                    const TCell c = pred_cell(kx, jc, false);
                     if (!c.ok) continue;
                     if (cur & E1_OP) {
                         const bool t = (cur & M_OP) ? (hij == c.e1) : (e1ij == c.e1 - e1);
@@ -444,11 +458,11 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
                         const bool t = (cur & M_OP) ? (hij == c.e2) : (e2ij == c.e2 - e2);
                         if (t) { cur = (c.h - oe2 == c.e2) ? (M_OP | F1_OP | F2_OP) : E2_OP; hit = true; }
                     }
-                    if (hit) { push(2u); visit_row(); chosen = (i32)kx; }
+                    if (hit) { push(2u); moved = true; }
                 }
             }
             if (!hit && (cur & (F1_OP | F2_OP)) && jc > ri.beg) {
-                const i32 hl = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(jc - 1 - ri.beg)]);
+                const i32 hl = ri.ref + sext16(wl);
                 if (cur & F1_OP) {
                     const i32 f = hl - oe1 + (i32)((vij >> 24) & 7u) - 1;
                     if (!(cur & M_OP) || hij == f) { cur = (hl - oe1 == f) ? (M_OP | E1_OP | E2_OP) : F1_OP; hit = true; }
@@ -457,7 +471,7 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
                     const i32 f = hl - oe2 + (i32)((vij >> 27) & 31u) - 1;
                     if (!(cur & M_OP) || hij == f) { cur = (hl - oe2 == f) ? (M_OP | E1_OP | E2_OP) : F2_OP; hit = true; }
                 }
-                if (hit) { push(3u); j--; }
+                if (hit) { push(3u); j--; vij = wl; }
             }
             if (!hit) {
                 if (cur == ALL_OP) break;
@@ -465,10 +479,14 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
             }
         }
         if (!hit) { err = true; break; }
-        if (chosen >= 0) {            // moved to a predecessor row
-            if (o > 0) o--;
-            else if (pn == 0) at_source = true;
-            else { s = pl[po + (u32)chosen]; o = rs[s + 1] - rs[s] - 1; }
+        if (moved) {                  // an M/X/D op consumed graph row ri and moves to a predecessor row
+            path_len++;
+            if (ri.node != last_node) { path[--ppos] = ri.node; last_node = ri.node; }
+            if (!have_row) { end_off = ri.off; have_row = true; }
+            start_off = ri.off;
+            if (np == 0) at_source = true;
+            else if (np == 1) { ri = rip; rip = rpp; have_p = have_pp; vij = wsel; }
+            else { ri = rsel; have_p = false; vij = wsel; }
         }
     }
     if (err) {

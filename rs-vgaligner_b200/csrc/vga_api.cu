@@ -42,7 +42,7 @@ struct DBuf {
 
 enum {
     B_SEQS, B_SEQOFF, B_KOFF, B_KCNT, B_KSLOT, B_ACNT, B_AOFF, B_AQB, B_ATB, B_ATE, B_KEYIN, B_VALIN, B_KEYOUT, B_VALOUT,
-    B_CUB, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
+    B_CUB, B_BIG, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
     B_CATE, B_CASC, B_GAP, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
     B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDSTATE, B_ROWS,
     B_POOL, B_WORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
@@ -96,25 +96,38 @@ struct HBlock { void* p; size_t cap; };
 static std::mutex g_pin_mu;
 static std::vector<HBlock> g_pin_free;
 
+// Requests are rounded up to quarter-octave size classes and matched exactly, so a steady stream of
+// calls with similar batch sizes re-uses the same blocks (cudaHostAlloc of ~100 MB costs tens of ms).
+static size_t pin_class(size_t bytes) {
+    if (bytes < 4096) return 4096;
+    size_t p = 4096;
+    while (p * 2 <= bytes) p *= 2;            // p <= bytes < 2p
+    const size_t q = p / 4;
+    return p + (bytes - p + q - 1) / q * q;     // p, 1.25p, 1.5p, 1.75p, 2p
+}
+static size_t g_pin_free_bytes = 0;
 static HBlock pin_get(size_t bytes) {
-    if (bytes < 256) bytes = 256;
+    const size_t cls = pin_class(bytes);
     {
         std::lock_guard<std::mutex> lk(g_pin_mu);
-        int best = -1;
-        for (int i = 0; i < (int)g_pin_free.size(); i++)
-            if (g_pin_free[i].cap >= bytes && g_pin_free[i].cap <= 2 * bytes + (1u << 20) &&
-                (best < 0 || g_pin_free[i].cap < g_pin_free[best].cap)) best = i;
-        if (best >= 0) { HBlock b = g_pin_free[best]; g_pin_free.erase(g_pin_free.begin() + best); return b; }
+        for (int i = (int)g_pin_free.size() - 1; i >= 0; i--)
+            if (g_pin_free[i].cap == cls) {
+                HBlock b = g_pin_free[i];
+                g_pin_free.erase(g_pin_free.begin() + i);
+                g_pin_free_bytes -= b.cap;
+                return b;
+            }
     }
-    HBlock b{nullptr, bytes + bytes / 8};
+    HBlock b{nullptr, cls};
     VGA_CUDA(cudaHostAlloc(&b.p, b.cap, cudaHostAllocDefault));
     return b;
 }
 static void pin_put(HBlock b) {
     if (!b.p) return;
     std::lock_guard<std::mutex> lk(g_pin_mu);
-    if (g_pin_free.size() >= 256) { cudaFreeHost(b.p); return; }
+    if (g_pin_free.size() >= 1024 || g_pin_free_bytes + b.cap > (8ull << 30)) { cudaFreeHost(b.p); return; }
     g_pin_free.push_back(b);
+    g_pin_free_bytes += b.cap;
 }
 
 template <class T> struct HArr {
@@ -284,6 +297,14 @@ struct Ctx {
     u32 launches = 0;
 };
 
+// VGA_HOST_TIMELINE=1: print host wall-clock marks of one call (where the host thread waits)
+static bool host_timeline() { static int v = -1; if (v < 0) { const char* e = getenv("VGA_HOST_TIMELINE"); v = e && *e == '1'; } return v; }
+static std::chrono::steady_clock::time_point g_tl0;
+static void tl_mark(const char* what) {
+    if (!host_timeline()) return;
+    fprintf(stderr, "[vga-tl] %9.3f ms  %s\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - g_tl0).count(), what);
+}
+
 // VGA_DEBUG_SYNC=1: synchronise and check after every stage so a device fault names its stage
 static bool debug_sync() { static int v = -1; if (v < 0) { const char* e = getenv("VGA_DEBUG_SYNC"); v = e && *e == '1'; } return v; }
 static void stage_check(cudaStream_t st, const char* name) {
@@ -312,16 +333,6 @@ template <class T> static void d2h_into(HArr<T>& dst, const T* dptr, size_t n, c
 // inclusive scan of in[0..n) into out[1..n], out[0]=0  (u64 output)
 template <class InT> static void scan_to_offsets(Ctx& c, const InT* in, u64* out, u32 n) {
     VGA_CUDA(cudaMemsetAsync(out, 0, sizeof(u64), c.st));
-    if (n == 0) return;
-    size_t tb = 0;
-    cub::DeviceScan::InclusiveSum(nullptr, tb, in, out + 1, (int)n, c.st);
-    void* tmp = c.ws->b[B_CUB].ensure(tb);
-    VGA_CUDA(cub::DeviceScan::InclusiveSum(tmp, tb, in, out + 1, (int)n, c.st));
-    c.launches += 2;
-}
-
-static void scan_to_offsets_u32(Ctx& c, const u32* in, u32* out, u32 n) {
-    VGA_CUDA(cudaMemsetAsync(out, 0, sizeof(u32), c.st));
     if (n == 0) return;
     size_t tb = 0;
     cub::DeviceScan::InclusiveSum(nullptr, tb, in, out + 1, (int)n, c.st);
@@ -363,6 +374,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     const bool want_scores = dbg || (P.flags & VGA_FLAG_CHAIN_SCORES);
     cudaStream_t st2 = w->st2;
     VGA_CUDA(cudaEventRecord(w->ev[0], st));
+    u32 A_total = 0;
     // ---- K1 seeding
     SeedBuffers sb;
     sb.seqs = d_seqs; sb.seq_off = d_seq_off; sb.n_reads = n;
@@ -383,14 +395,24 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     sb.read_aoff = w->b[B_AOFF].get<u32>(n + 1);
     c.launches += launch_seed_count(dv, sb, st);
     stage_check(st, "seed_count");
-    {   // anchors may not exceed 2^31 per chunk (CUB segmented sort takes int counts)
+    // anchors per read -> offsets; reads with more than CHAIN_SMAX anchors are listed for the CUB sort path.
+    // Anchors may not exceed 2^31 per chunk (32-bit anchor offsets, CUB takes int counts).
+    u32* big_ctr = w->b[B_CTR].get<u32>(16) + 8;
+    u32* big_list = w->b[B_BIG].get<u32>(3ull * n);
+    u32 n_big = 0;
+    {
         u64* tmp64 = w->b[B_SZOFF].get<u64>(n + 1);
         scan_to_offsets(c, sb.read_acnt, tmp64, n);
-        const u64 total64 = d2h_one(tmp64 + n, st);
+        VGA_CUDA(cudaMemsetAsync(big_ctr, 0, 4, st));
+        c.launches += launch_chain_prep(tmp64, n, sb.read_aoff, big_ctr, big_list, big_list + n, big_list + 2ull * n, st);
+        u64 total64 = 0;
+        VGA_CUDA(cudaMemcpyAsync(&total64, tmp64 + n, 8, cudaMemcpyDeviceToHost, st));
+        VGA_CUDA(cudaMemcpyAsync(&n_big, big_ctr, 4, cudaMemcpyDeviceToHost, st));
+        VGA_CUDA(cudaStreamSynchronize(st));
         if (total64 >= (1ull << 31) - 1) return false;
+        A_total = (u32)total64;
     }
-    scan_to_offsets_u32(c, sb.read_acnt, sb.read_aoff, n);
-    const u32 A = d2h_one(sb.read_aoff + n, st);
+    const u32 A = A_total;
     sb.a_qb = w->b[B_AQB].get<u32>(A); sb.a_tb = w->b[B_ATB].get<u32>(A); sb.a_te = w->b[B_ATE].get<u32>(A);
     sb.sort_key_in = w->b[B_KEYIN].get<u32>(A); sb.sort_val_in = w->b[B_VALIN].get<u32>(A);
     u32* key_out = w->b[B_KEYOUT].get<u32>(A);
@@ -398,29 +420,35 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     c.launches += launch_seed_emit(dv, sb, st);
     stage_check(st, "seed_emit");
     VGA_CUDA(cudaEventRecord(w->ev[1], st));
-    // ---- K2 per-read stable sort by target_end.position (src/chain.rs:386-389)
-    if (A > 0) {
-        size_t tb = 0;
-        cub::DeviceSegmentedSort::StableSortPairs(nullptr, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out, (int)A,
-                                                  (int)n, sb.read_aoff, sb.read_aoff + 1, st);
-        void* tmp = w->b[B_CUB].ensure(tb);
-        VGA_CUDA(cub::DeviceSegmentedSort::StableSortPairs(tmp, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out,
-                                                           (int)A, (int)n, sb.read_aoff, sb.read_aoff + 1, st));
-        c.launches += 3;
-    }
-    VGA_CUDA(cudaEventRecord(w->ev[2], st));
-    // ---- K3 chaining
+    tl_mark("seed done (host)");
+    // ---- K2 + K3: per-read stable sort by target_end.position (src/chain.rs:386-389) and chaining.
+    // Reads with up to CHAIN_SMAX anchors: one fused kernel (shared-memory bitonic sort + DP + backtrack).
+    // The others: CUB segmented sort over just their segments, then the same DP on the sorted order.
     upload_gapcost(c, dv.k, P.max_gap);
     ChainBuffers cb;
     cb.n_reads = n; cb.read_aoff = sb.read_aoff; cb.a_qb = sb.a_qb; cb.a_tb = sb.a_tb; cb.a_te = sb.a_te;
     cb.sidx = val_out; cb.gapcost = (const double*)w->b[B_GAP].p;
+    cb.big_list = big_list; cb.n_big = n_big;
     cb.f = w->b[B_F].get<double>(A); cb.pred = w->b[B_PRED].get<i32>(A);
     cb.pred_dbg = dbg ? w->b[B_PREDDBG].get<i32>(A) : nullptr;
     cb.n_chains = w->b[B_NCH].get<u32>(n); cb.n_members = w->b[B_NMEM].get<u32>(n);
     cb.clen = w->b[B_CLEN].get<u32>((u64)A + n); cb.cmem = w->b[B_CMEM].get<u32>(2ull * A + 2ull * n);
     cb.k = dv.k; cb.bandwidth = P.bandwidth; cb.max_gap = P.max_gap; cb.min_anchors = P.min_anchors;
-    c.launches += launch_chain(cb, st);
-    stage_check(st, "chain");
+    if (n_big < n) c.launches += launch_chain(cb, true, st);
+    stage_check(st, "chain (fused)");
+    VGA_CUDA(cudaEventRecord(w->ev[2], st));
+    if (n_big > 0) {
+        size_t tb = 0;
+        cub::DeviceSegmentedSort::StableSortPairs(nullptr, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out, (int)A,
+                                                  (int)n_big, big_list + n, big_list + 2ull * n, st);
+        void* tmp = w->b[B_CUB].ensure(tb);
+        VGA_CUDA(cub::DeviceSegmentedSort::StableSortPairs(tmp, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out,
+                                                           (int)A, (int)n_big, big_list + n, big_list + 2ull * n, st));
+        c.launches += 3;
+        c.launches += launch_chain(cb, false, st);
+        stage_check(st, "chain (big reads)");
+    }
+    tl_mark("sort+chain queued");
     u64* chain_off = w->b[B_CHOFF].get<u64>(n + 1);
     u64* member_off = w->b[B_MEMOFF].get<u64>(n + 1);
     scan_to_offsets(c, cb.n_chains, chain_off, n);
@@ -437,30 +465,39 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     stage_check(st, "chain_gather");
     VGA_CUDA(cudaEventRecord(w->ev[3], st));
 
-    // ---- chain results leave on the copy stream while the alignment stages run
+    tl_mark("chain_gather queued");
+    // ---- chain results leave on the copy stream while the alignment stages run.  They are queued
+    // only after the first POA fill launch (or right away when nothing gets aligned): the small
+    // blocking D2H reads of the stages in between would otherwise wait behind ~100 MB on the copy engine.
     O.n = n; O.NC = NC; O.NM = NM;
-    VGA_CUDA(cudaEventRecord(w->ev_copy, st));
-    VGA_CUDA(cudaStreamWaitEvent(st2, w->ev_copy, 0));
-    d2h_into(O.n_anchors, (const u32*)sb.read_acnt, n, st2);
-    d2h_into(O.chain_off, (const u64*)chain_off, (size_t)n + 1, st2);
-    d2h_into(O.chain_anchor_off, (const u64*)cg.chain_anchor_off, NC + 1, st2);
-    d2h_into(O.ca_qb, (const u32*)cg.ca_qb, NM, st2); d2h_into(O.ca_tb, (const u32*)cg.ca_tb, NM, st2);
-    d2h_into(O.ca_te, (const u32*)cg.ca_te, NM, st2);
-    if (want_scores) { d2h_into(O.ca_id, (const u32*)cg.ca_id, NM, st2); d2h_into(O.ca_score, (const double*)cg.ca_score, NM, st2); }
+    bool chain_d2h_queued = false;
+    auto queue_chain_d2h = [&]() {
+        if (chain_d2h_queued) return;
+        chain_d2h_queued = true;
+        VGA_CUDA(cudaStreamWaitEvent(st2, w->ev_copy, 0));
+        d2h_into(O.n_anchors, (const u32*)sb.read_acnt, n, st2);
+        d2h_into(O.chain_off, (const u64*)chain_off, (size_t)n + 1, st2);
+        d2h_into(O.chain_anchor_off, (const u64*)cg.chain_anchor_off, NC + 1, st2);
+        d2h_into(O.ca_qb, (const u32*)cg.ca_qb, NM, st2); d2h_into(O.ca_tb, (const u32*)cg.ca_tb, NM, st2);
+        d2h_into(O.ca_te, (const u32*)cg.ca_te, NM, st2);
+        if (want_scores) { d2h_into(O.ca_id, (const u32*)cg.ca_id, NM, st2); d2h_into(O.ca_score, (const double*)cg.ca_score, NM, st2); }
+        if (dbg) {
+            d2h_into(O.dbg_anchor_off, (const u64*)w->b[B_DBGSUBCNT].p, (size_t)n + 1, st2);
+            d2h_into(O.dbg_qb, (const u32*)sb.a_qb, A, st2); d2h_into(O.dbg_tb, (const u32*)sb.a_tb, A, st2);
+            d2h_into(O.dbg_te, (const u32*)sb.a_te, A, st2); d2h_into(O.dbg_sorted, (const u32*)val_out, A, st2);
+            d2h_into(O.dbg_f, (const double*)cb.f, A, st2); d2h_into(O.dbg_pred, (const i32*)cb.pred_dbg, A, st2);
+        }
+    };
     if (dbg) {
         u64* aoff64 = w->b[B_DBGSUBCNT].get<u64>(n + 1);
         scan_to_offsets(c, sb.read_acnt, aoff64, n);
-        VGA_CUDA(cudaEventRecord(w->ev_copy, st));
-        VGA_CUDA(cudaStreamWaitEvent(st2, w->ev_copy, 0));
-        d2h_into(O.dbg_anchor_off, (const u64*)aoff64, (size_t)n + 1, st2);
-        d2h_into(O.dbg_qb, (const u32*)sb.a_qb, A, st2); d2h_into(O.dbg_tb, (const u32*)sb.a_tb, A, st2);
-        d2h_into(O.dbg_te, (const u32*)sb.a_te, A, st2); d2h_into(O.dbg_sorted, (const u32*)val_out, A, st2);
-        d2h_into(O.dbg_f, (const double*)cb.f, A, st2); d2h_into(O.dbg_pred, (const i32*)cb.pred_dbg, A, st2);
     }
+    VGA_CUDA(cudaEventRecord(w->ev_copy, st));
     R.stats.n_probes += total_k; R.stats.n_anchors += A; R.stats.n_positions_read += A; R.stats.n_chains += NC;
     R.stats.n_bases += n_bases;
     R.stats.lookup_bytes += n_bases + 32ull * total_k + 8ull * A + 16ull * A;
 
+    tl_mark("chain d2h queued");
     // ---- alignment
     u32 NI = 0;
     u32* item_cnt = w->b[B_ITEMCNT].get<u32>(n);
@@ -474,6 +511,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     }
     if (NI == 0) {
         // every read is a placeholder (or alignment was not requested)
+        queue_chain_d2h();
         O.aln_status.alloc(n); O.aln_chain.alloc(n); O.aln_path_len.alloc(n); O.aln_start_off.alloc(n); O.aln_end_off.alloc(n);
         O.aln_n_aligned.alloc(n); O.aln_score.alloc(n); O.aln_cells.alloc(n); O.aln_path_off.alloc((size_t)n + 1);
         O.aln_run_off.alloc((size_t)n + 1); O.aln_path.alloc(0); O.aln_runs.alloc(0);
@@ -492,6 +530,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         VGA_CUDA(cudaStreamSynchronize(st));
         return true;
     }
+    tl_mark("NI known");
     items = w->b[B_ITEMS].get<AlignItem>(NI);
     item_build_kernel<<<(n + 255) / 256, 256, 0, st>>>(item_cnt, item_off, chain_off, n, items);
     c.launches++;
@@ -525,6 +564,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         if (h[0] > ext_cap) ext_cap = h[0] + h[0] / 4 + 1024;      // the counter kept counting: exact need is known
         else { w->scratch_words *= 2; w->scratch_zeroed = false; }
     }
+    tl_mark("sub_count done");
     u64* sz = w->b[B_SZ].get<u64>(4ull * NI);
     u64* szo = w->b[B_SZOFF].get<u64>(4ull * (NI + 1));
     item_sizes_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, sz, sz + NI, sz + 2ull * NI, sz + 3ull * NI);
@@ -536,6 +576,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     }
     for (int q = 0; q < 4; q++)
         if (tot[q] >= (1ull << 32)) { set_error("alignment batch exceeds 32-bit offsets; use smaller batches"); throw CudaFail{VGA_ERR_UNSUPPORTED}; }
+    tl_mark("sizes scanned");
     u32* d_nrows = w->b[B_RCNT].get<u32>(3ull * NI);
     item_bases_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, szo, szo + (NI + 1), szo + 2ull * (NI + 1), szo + 3ull * (NI + 1),
                                                         d_nrows, d_nrows + NI, d_nrows + 2ull * NI);
@@ -546,10 +587,14 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     sub.nd_remain_last = w->b[B_NDRL].get<i32>(tot[0]);
     c.launches += launch_sub_fill(dv, sub, st);
     stage_check(st, "sub_fill");
-    std::vector<u32> h_meta(3ull * NI);
-    VGA_CUDA(cudaMemcpyAsync(h_meta.data(), d_nrows, 12ull * NI, cudaMemcpyDeviceToHost, st));
+    HArr<u32> h_meta_pin;
+    h_meta_pin.alloc(3ull * NI);
+    struct PinGuard { HArr<u32>& a; ~PinGuard() { a.release(); } } h_meta_guard{h_meta_pin};
+    const u32* h_meta = h_meta_pin.data();
+    VGA_CUDA(cudaMemcpyAsync(h_meta_pin.data(), d_nrows, 12ull * NI, cudaMemcpyDeviceToHost, st));
     VGA_CUDA(cudaEventRecord(w->ev[4], st));
     VGA_CUDA(cudaStreamSynchronize(st));
+    tl_mark("sub_fill done, meta on host");
     // ---- K5 POA in waves
     PoaBuffers pb;
     memset(&pb, 0, sizeof(pb));
@@ -575,7 +620,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u64 est_total = 0;
     {
         const int NB = 48;
-        std::vector<std::vector<u32>> bucket((size_t)NCLS * NB);
+        std::vector<u32> key(NI), cnt((size_t)NCLS * NB + 1, 0);
         for (u32 i = 0; i < NI; i++) {
             const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
             const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
@@ -583,15 +628,17 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             est[i] = (u64)(nrows * (west + 4));
             est_total += est[i];
             const int ci = poa_class_for(qlen, nrows, west, P);
-            int lb = 0;
-            while (lb < NB - 1 && (est[i] >> lb) > 1) lb++;
-            bucket[(size_t)ci * NB + (NB - 1 - lb)].push_back(i);
+            const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
+            key[i] = (u32)(ci * NB + (NB - 1 - std::min(lb, NB - 1)));
+            cnt[key[i] + 1]++;
         }
-        for (int ci = 0; ci < NCLS; ci++)
-            for (int q = 0; q < NB; q++) {
-                std::vector<u32>& v = bucket[(size_t)ci * NB + q];
-                cls[ci].insert(cls[ci].end(), v.begin(), v.end());
-            }
+        for (size_t q = 1; q < cnt.size(); q++) cnt[q] += cnt[q - 1];
+        for (int ci = 0; ci < NCLS; ci++) cls[ci].resize(cnt[(size_t)(ci + 1) * NB] - cnt[(size_t)ci * NB]);
+        std::vector<u32> fill(cnt.begin(), cnt.end() - 1);
+        for (u32 i = 0; i < NI; i++) {
+            const u32 ci = key[i] / NB;
+            cls[ci][fill[key[i]]++ - cnt[(size_t)ci * NB]] = i;
+        }
     }
     size_t free_b = 0, total_b = 0;
     VGA_CUDA(cudaMemGetInfo(&free_b, &total_b));
@@ -604,6 +651,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     pb.pool = w->b[B_POOL].get<u32>(want_words);
     pb.pool_words = std::min<u64>(w->b[B_POOL].cap / 4, (1ull << 34) - 16);
     tbuf.pool = pb.pool;
+    tl_mark("pool ready");
     u32* d_work = w->b[B_WORK].get<u32>(NI);
     u32* d_status = w->b[B_STATUS].get<u32>(NI);
     std::vector<u32> h_status(NI);
@@ -635,6 +683,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             VGA_CUDA(cudaEventRecord(w->ev[10], st));
             item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
             c.launches++;
+            queue_chain_d2h();          // host-side queueing (and any pinned allocation) hides behind the fill kernel
             VGA_CUDA(cudaMemcpyAsync(h_status.data(), d_status, 4ull * nw, cudaMemcpyDeviceToHost, st));
             VGA_CUDA(cudaStreamSynchronize(st));
             float a = 0, bms = 0;
@@ -660,6 +709,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         }
     }
     VGA_CUDA(cudaEventRecord(w->ev[5], st));
+    tl_mark("poa waves done");
     // ---- selection + compaction
     i32* sel = w->b[B_SEL].get<i32>(n);
     u8* d_st8 = (u8*)w->b[B_STATUS].ensure(std::max<size_t>(4ull * NI, n));
@@ -702,6 +752,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         d2h_into(O.dbg_sub_handles, (const u64*)d_sub, tots[2], st);
         d2h_into(O.dbg_edges, (const u32*)d_edges, 2 * tots[3], st);
     }
+    tl_mark("aln d2h queued");
     // total cells over all items (GCUPS numerator)
     {
         std::vector<u64> h_cells(NI);
@@ -713,6 +764,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     VGA_CUDA(cudaEventRecord(w->ev[7], st));
     VGA_CUDA(cudaStreamSynchronize(st2));
     VGA_CUDA(cudaStreamSynchronize(st));
+    tl_mark("chunk done");
     R.stats.n_alignments += NI;
     R.stats.ms_poa += ms_fill; R.stats.ms_trace += ms_trace;
     return true;
@@ -838,6 +890,7 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
         const u64* d_off = d_off_in;
         VGA_CUDA(cudaEventRecord(t0, c.st));
         auto wall0 = std::chrono::steady_clock::now();
+        g_tl0 = wall0;
         if (n_reads > 0) {
             if (!d_seqs_in) {
                 for (u32 i = 0; i < n_reads; i++)
