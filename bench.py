@@ -403,7 +403,7 @@ def main():
         dominant = roof_poa if stage["ms_poa"] >= stage["ms_seed"] else roof_seed
         line = dict(base)
         line.update({"value": total_reads * K / (ms_dev_max * 1e-3), "ms_per_step": ms_dev_max / K,
-                     "clocks": clocks, "gpu_launches": int(sum(x["kernel_launches"] for x in acc)),
+                     "ms_steps": [round(x["ms_total"], 3) for x in acc], "clocks": clocks, "gpu_launches": int(sum(x["kernel_launches"] for x in acc)),
                      "aligned_fraction": total_aligned / total_reads, "stage_ms": stage,
                      "roofline": dominant, "roofline_poa": roof_poa, "roofline_lookup": roof_seed,
                      "setup": {"index_build_s": t_index, "index_image_bytes": nbytes if world > 1 else ix.image_size(),

@@ -86,6 +86,7 @@ struct SubBuffers {
 };
 int launch_sub_count(const DevIndex& ix, const SubBuffers& b, cudaStream_t st);
 int launch_sub_fill(const DevIndex& ix, const SubBuffers& b, cudaStream_t st);
+int launch_sub_rowmeta(const DevIndex& ix, const SubBuffers& b, u32* row_meta, cudaStream_t st);   // per-row records (k_subgraph.cu)
 
 struct PoaBuffers {
     u32 n_items;             // entries of work[]
@@ -96,16 +97,19 @@ struct PoaBuffers {
     const i32* nd_first_succ; const i32* nd_remain_last;
     NodeState* nd_state;     // per node, written by the fill kernel for later nodes
     RowInfo* rows;           // per row, written by the fill kernel for later rows / traceback
+    const u32* row_meta;     // per row: base | kind << 8 | last << 10 | remain << 11 (sub_rowmeta_kernel)
     // trace pool: one 32-bit word per band cell
     u32* pool; u64 pool_words; unsigned long long* pool_ctr;
     u32* work_ctr;
     i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
 };
-// kernel instances: classes 0..7 FIXED C=1..8 (qlen < 32*C), 8..10 SLIDE C=8,16,32
+// kernel classes: 0..2 = short reads, 8/16/32 lanes per alignment (k_poa_short.cu); 3..5 = SLIDE C=8,16,32 (k_poa.cu)
 int poa_class_count();
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P);
 int poa_class_wider(int cls);    // -1: none
 int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
+int launch_poa_fill_short(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
+bool poa_short_ok(i64 qlen, i64 nrows, const VgaParams& P);   // read short enough and scores within int16
 
 struct TraceBuffers {
     u32 n_items; const u32* work; AlignItem* items;

@@ -27,6 +27,7 @@
 // Roofline: INT32 ALU (no tensor cores: nothing here is a contraction).  Algorithmic work =
 // band cells; see DESIGN.md for ops/cell.
 #include <climits>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "internal.h"
@@ -502,16 +503,17 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     itp->start_off = start_off; itp->end_off = end_off;
 }
 
-// instances: FIXED C = 1..8 (reads up to 255 bases), SLIDE C = 8, 16, 32 (bands up to 1024 columns)
-int poa_class_count() { return 11; }
+// classes: 0..2 = short reads with 8 / 16 / 32 lanes per alignment (k_poa_short.cu: qlen < 256, int16 absolute scores,
+// bands up to 96 / 160 / 256 columns), 3..5 = SLIDE C = 8, 16, 32 (bands up to 256 / 512 / 1024 columns)
+static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;     // bands up to this use the 8-lane instance
+int poa_class_count() { return 6; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
-    const i64 step = P.mismatch > P.o1 + P.e1 ? P.mismatch : P.o1 + P.e1;
-    if (qlen < 256 && step * (nrows + qlen) <= 32000) return (int)(qlen / 32);   // FIXED, C = class + 1 (32*C > qlen)
-    if (west <= 256 - 8) return 8;
-    if (west <= 512 - 16) return 9;
-    return 10;
+    if (poa_short_ok(qlen, nrows, P)) return west <= (i64)g_short_w8 ? 0 : west <= 160 ? 1 : 2;
+    if (west <= 256 - 8) return 3;
+    if (west <= 512 - 16) return 4;
+    return 5;
 }
-int poa_class_wider(int cls) { return cls < 8 ? 8 : cls < 10 ? cls + 1 : -1; }
+int poa_class_wider(int cls) { return cls < 5 ? cls + 1 : -1; }
 
 template <int C, bool SLIDE>
 static void launch_fill(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
@@ -529,16 +531,9 @@ static void launch_fill(const DevIndex& ix, const PoaBuffers& b, int n_sms, cuda
 int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st) {
     if (b.n_items == 0) return 0;
     switch (cls) {
-        case 0: launch_fill<1, false>(ix, b, n_sms, st); break;
-        case 1: launch_fill<2, false>(ix, b, n_sms, st); break;
-        case 2: launch_fill<3, false>(ix, b, n_sms, st); break;
-        case 3: launch_fill<4, false>(ix, b, n_sms, st); break;
-        case 4: launch_fill<5, false>(ix, b, n_sms, st); break;
-        case 5: launch_fill<6, false>(ix, b, n_sms, st); break;
-        case 6: launch_fill<7, false>(ix, b, n_sms, st); break;
-        case 7: launch_fill<8, false>(ix, b, n_sms, st); break;
-        case 8: launch_fill<8, true>(ix, b, n_sms, st); break;
-        case 9: launch_fill<16, true>(ix, b, n_sms, st); break;
+        case 0: case 1: case 2: return launch_poa_fill_short(ix, b, cls, n_sms, st);
+        case 3: launch_fill<8, true>(ix, b, n_sms, st); break;
+        case 4: launch_fill<16, true>(ix, b, n_sms, st); break;
         default: launch_fill<32, true>(ix, b, n_sms, st); break;
     }
     return 1;

@@ -297,6 +297,34 @@ __global__ void __launch_bounds__(SUB_WARPS * 32) sub_fill_kernel(DevIndex ix, S
     }
 }
 
+// Per-row record for the short-read POA kernel: graph base, how the row gets its predecessor row, whether it is the
+// last row of its node, and max_remain of the row (abPOA's remaining graph length along the first out-edge):
+//   bits 0..7 base | 8..9 kind | 10 last | 11..31 remain
+// kind 0: the predecessor row is the previous row (inside a label, or a first row whose only predecessor is the
+// previous node); 1: virtual source; 2: any other first row (predecessors merged from their trace words).
+__global__ void __launch_bounds__(SUB_WARPS * 32) sub_rowmeta_kernel(DevIndex ix, SubBuffers b, u32* __restrict__ row_meta) {
+    const u32 lane = threadIdx.x & 31;
+    const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (u32 w = warp; w < b.n_items; w += n_warps) {
+        const AlignItem it = b.items[w];
+        const u32 nb = it.node_base;
+        u32* __restrict__ out = row_meta + it.row_base;
+        for (u32 s = 0; s < it.S; s++) {
+            const u32 r0 = b.nd_row_start[nb + s], len = b.nd_row_start[nb + s + 1] - r0;
+            const u32 src = b.nd_src[nb + s];
+            const u32 po = b.nd_pred_off[nb + s], pn = b.nd_pred_off[nb + s + 1] - po;
+            const u32 remain_last = (u32)b.nd_remain_last[nb + s];
+            const u32 kind0 = pn == 0 ? 1u : (pn == 1 && s > 0 && b.nd_pred[it.pred_base + po] == s - 1) ? 0u : 2u;
+            for (u32 o = lane; o < len; o += 32) {
+                const u32 remain = remain_last + (len - 1 - o);
+                out[r0 + o] = (u32)ix.seq_both[src + o] | ((o == 0 ? kind0 : 0u) << 8) | ((o == len - 1 ? 1u : 0u) << 10) |
+                              ((remain < (1u << 21) ? remain : (1u << 21) - 1) << 11);
+            }
+        }
+    }
+}
+
 static int grid_for_warps(u32 n_items, int warps_per_cta, u32 max_warps) {
     long long ctas = ((long long)n_items + warps_per_cta - 1) / warps_per_cta;
     long long cap = max_warps / warps_per_cta;
@@ -312,6 +340,11 @@ int launch_sub_count(const DevIndex& ix, const SubBuffers& b, cudaStream_t st) {
 
 int launch_sub_fill(const DevIndex& ix, const SubBuffers& b, cudaStream_t st) {
     sub_fill_kernel<<<grid_for_warps(b.n_items, SUB_WARPS, 148 * 64), SUB_WARPS * 32, 0, st>>>(ix, b);
+    return 1;
+}
+
+int launch_sub_rowmeta(const DevIndex& ix, const SubBuffers& b, u32* row_meta, cudaStream_t st) {
+    sub_rowmeta_kernel<<<grid_for_warps(b.n_items, SUB_WARPS, 148 * 64), SUB_WARPS * 32, 0, st>>>(ix, b, row_meta);
     return 1;
 }
 

@@ -44,7 +44,7 @@ enum {
     B_SEQS, B_SEQOFF, B_KOFF, B_KCNT, B_KSLOT, B_ACNT, B_AOFF, B_AQB, B_ATB, B_ATE, B_KEYIN, B_VALIN, B_KEYOUT, B_VALOUT,
     B_CUB, B_BIG, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
     B_CATE, B_CASC, B_GAP, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
-    B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDSTATE, B_ROWS,
+    B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDSTATE, B_ROWS, B_ROWMETA,
     B_POOL, B_WORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
     B_DBGSUBCNT, B_DBGSUBOFF, B_DBGSUB, B_DBGEDGECNT, B_DBGEDGEOFF, B_DBGEDGE, B_CELLS, B_COUNT
 };
@@ -586,6 +586,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     sub.nd_pred = w->b[B_NDPRED].get<u32>(tot[1]); sub.nd_first_succ = w->b[B_NDFS].get<i32>(tot[0]);
     sub.nd_remain_last = w->b[B_NDRL].get<i32>(tot[0]);
     c.launches += launch_sub_fill(dv, sub, st);
+    u32* d_row_meta = w->b[B_ROWMETA].get<u32>(tot[2]);
+    c.launches += launch_sub_rowmeta(dv, sub, d_row_meta, st);
     stage_check(st, "sub_fill");
     HArr<u32> h_meta_pin;
     h_meta_pin.alloc(3ull * NI);
@@ -603,6 +605,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     pb.nd_first_succ = sub.nd_first_succ; pb.nd_remain_last = sub.nd_remain_last;
     pb.nd_state = w->b[B_NDSTATE].get<NodeState>(tot[0]);
     pb.rows = w->b[B_ROWS].get<RowInfo>(tot[2]);
+    pb.row_meta = d_row_meta;
     pb.match = P.match; pb.mismatch = P.mismatch; pb.o1 = P.o1; pb.e1 = P.e1; pb.o2 = P.o2; pb.e2 = P.e2; pb.wb = P.wb; pb.wf = P.wf;
     pb.work_ctr = ctr + 2; pb.pool_ctr = (unsigned long long*)(ctr + 4);
     TraceBuffers tbuf;
@@ -868,9 +871,9 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
     if (params->max_gap > (1u << 24)) { set_error("max_gap too large"); return VGA_ERR_UNSUPPORTED; }
     {   // the 32-bit trace word keeps E'/F relative to H in 3 + 5 bit fields (k_poa.cu): bounds on the gap model
         const VgaParams& q = *params;
-        if (q.match < 0 || q.mismatch < 0 || q.e1 < 0 || q.e2 < 0 || q.o1 < 0 || q.o2 < 0 || q.o1 > 6 || q.o2 > 30 ||
+        if (q.match < 0 || q.mismatch < 0 || q.e1 < 1 || q.e2 < 1 || q.o1 < 0 || q.o2 < 0 || q.o1 > 6 || q.o2 > 30 ||
             q.e2 > q.o1 + q.e1 || q.e1 > q.o2 + q.e2 || q.match > 64 || q.mismatch > 64 || q.e1 > 64 || q.e2 > 64) {
-            set_error("POA gap model outside the supported range (o1 <= 6, o2 <= 30, e2 <= o1+e1, e1 <= o2+e2)");
+            set_error("POA gap model outside the supported range (e1, e2 >= 1, o1 <= 6, o2 <= 30, e2 <= o1+e1, e1 <= o2+e2)");
             return VGA_ERR_UNSUPPORTED;
         }
     }
