@@ -309,18 +309,21 @@ __global__ void __launch_bounds__(SUB_WARPS * 32) sub_rowmeta_kernel(DevIndex ix
     for (u32 w = warp; w < b.n_items; w += n_warps) {
         const AlignItem it = b.items[w];
         const u32 nb = it.node_base;
+        const u32* __restrict__ rs = b.nd_row_start + nb;
         u32* __restrict__ out = row_meta + it.row_base;
-        for (u32 s = 0; s < it.S; s++) {
-            const u32 r0 = b.nd_row_start[nb + s], len = b.nd_row_start[nb + s + 1] - r0;
-            const u32 src = b.nd_src[nb + s];
-            const u32 po = b.nd_pred_off[nb + s], pn = b.nd_pred_off[nb + s + 1] - po;
-            const u32 remain_last = (u32)b.nd_remain_last[nb + s];
-            const u32 kind0 = pn == 0 ? 1u : (pn == 1 && s > 0 && b.nd_pred[it.pred_base + po] == s - 1) ? 0u : 2u;
-            for (u32 o = lane; o < len; o += 32) {
-                const u32 remain = remain_last + (len - 1 - o);
-                out[r0 + o] = (u32)ix.seq_both[src + o] | ((o == 0 ? kind0 : 0u) << 8) | ((o == len - 1 ? 1u : 0u) << 10) |
-                              ((remain < (1u << 21) ? remain : (1u << 21) - 1) << 11);
+        // a lane per row; its node by binary search over the row starts (labels are short, so a loop over nodes would idle lanes)
+        for (u32 row = lane; row < it.nrows; row += 32) {
+            u32 lo = 0, hi = it.S;                       // rs[lo] <= row < rs[hi]
+            while (hi - lo > 1) { const u32 mid = (lo + hi) >> 1; if (rs[mid] <= row) lo = mid; else hi = mid; }
+            const u32 s = lo, r0 = rs[s], len = rs[s + 1] - r0, o = row - r0;
+            u32 kind = 0;
+            if (o == 0) {
+                const u32 po = b.nd_pred_off[nb + s], pn = b.nd_pred_off[nb + s + 1] - po;
+                kind = pn == 0 ? 1u : (pn == 1 && s > 0 && b.nd_pred[it.pred_base + po] == s - 1) ? 0u : 2u;
             }
+            const u32 remain = (u32)b.nd_remain_last[nb + s] + (len - 1 - o);
+            out[row] = (u32)ix.seq_both[b.nd_src[nb + s] + o] | (kind << 8) | ((o == len - 1 ? 1u : 0u) << 10) |
+                       ((remain < (1u << 21) ? remain : (1u << 21) - 1) << 11);
         }
     }
 }

@@ -45,7 +45,7 @@ enum {
     B_CUB, B_BIG, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
     B_CATE, B_CASC, B_GAP, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
     B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDSTATE, B_ROWS, B_ROWMETA,
-    B_POOL, B_WORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
+    B_POOL, B_WORK, B_TWORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
     B_DBGSUBCNT, B_DBGSUBOFF, B_DBGSUB, B_DBGEDGECNT, B_DBGEDGEOFF, B_DBGEDGE, B_CELLS, B_COUNT
 };
 
@@ -297,12 +297,19 @@ struct Ctx {
     u32 launches = 0;
 };
 
-// VGA_HOST_TIMELINE=1: print host wall-clock marks of one call (where the host thread waits)
-static bool host_timeline() { static int v = -1; if (v < 0) { const char* e = getenv("VGA_HOST_TIMELINE"); v = e && *e == '1'; } return v; }
+// VGA_HOST_TIMELINE=1: print host wall-clock marks of every call (where the host thread waits);
+// VGA_HOST_TIMELINE=<ms> (> 1): only for calls that took longer than that many milliseconds
+static int host_timeline() { static int v = -1; if (v < 0) { const char* e = getenv("VGA_HOST_TIMELINE"); v = e ? atoi(e) : 0; } return v; }
 static std::chrono::steady_clock::time_point g_tl0;
+static std::vector<std::pair<double, const char*>> g_tl;
 static void tl_mark(const char* what) {
     if (!host_timeline()) return;
-    fprintf(stderr, "[vga-tl] %9.3f ms  %s\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - g_tl0).count(), what);
+    g_tl.push_back({std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - g_tl0).count(), what});
+}
+static void tl_flush(double wall_ms) {
+    if (host_timeline() && (host_timeline() == 1 || wall_ms > host_timeline()))
+        for (auto& m : g_tl) fprintf(stderr, "[vga-tl] %9.3f ms  %s\n", m.first, m.second);
+    g_tl.clear();
 }
 
 // VGA_DEBUG_SYNC=1: synchronise and check after every stage so a device fault names its stage
@@ -656,16 +663,43 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     tbuf.pool = pb.pool;
     tl_mark("pool ready");
     u32* d_work = w->b[B_WORK].get<u32>(NI);
+    u32* d_twork = w->b[B_TWORK].get<u32>(NI);
     u32* d_status = w->b[B_STATUS].get<u32>(NI);
     std::vector<u32> h_status(NI);
     float ms_fill = 0, ms_trace = 0;
+    // Fill launches of all classes share the trace pool; the traceback of everything filled so far runs as ONE
+    // launch when the pool is about to run out (or at the end), after which the pool starts over.
+    std::vector<u32> trace_list;
+    trace_list.reserve(NI);
+    u64 pool_acc = warp_slack;                  // estimated words in use since the last traceback
+    VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
+    auto flush_trace = [&]() {
+        if (!trace_list.empty()) {
+            VGA_CUDA(cudaMemcpyAsync(d_twork, trace_list.data(), 4ull * trace_list.size(), cudaMemcpyHostToDevice, st));
+            tbuf.n_items = (u32)trace_list.size(); tbuf.work = d_twork;
+            VGA_CUDA(cudaEventRecord(w->ev[9], st));
+            c.launches += launch_poa_trace(dv, tbuf, st);
+            stage_check(st, "poa_trace");
+            VGA_CUDA(cudaEventRecord(w->ev[10], st));
+            VGA_CUDA(cudaEventSynchronize(w->ev[10]));
+            float t = 0;
+            cudaEventElapsedTime(&t, w->ev[9], w->ev[10]);
+            ms_trace += t;
+            trace_list.clear();
+        }
+        VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
+        pool_acc = warp_slack;
+    };
     for (int ci = 0; ci < NCLS; ci++) {
         std::vector<u32>& list = cls[ci];
         size_t pos = 0;
         int stall = 0;
         while (pos < list.size()) {
-            // take a wave whose estimate fits the pool
-            u64 acc = warp_slack;
+            // take a wave whose estimate fits what is left of the pool
+            const u64 first = est[list[pos]] + est[list[pos]] / 4;
+            if (pool_acc + first > pb.pool_words && pool_acc > warp_slack) flush_trace();
+            const bool fresh_pool = pool_acc == warp_slack;
+            u64 acc = pool_acc;
             size_t end = pos;
             while (end < list.size() && (end == pos || acc + est[list[end]] + est[list[end]] / 4 <= pb.pool_words)) {
                 acc += est[list[end]] + est[list[end]] / 4;
@@ -673,44 +707,44 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             }
             const u32 nw = (u32)(end - pos);
             VGA_CUDA(cudaMemcpyAsync(d_work, list.data() + pos, 4ull * nw, cudaMemcpyHostToDevice, st));
-            VGA_CUDA(cudaMemsetAsync(ctr + 2, 0, 24, st));
+            VGA_CUDA(cudaMemsetAsync(ctr + 2, 0, 4, st));
             pb.n_items = nw; pb.work = d_work;
-            tbuf.n_items = nw; tbuf.work = d_work;
             VGA_CUDA(cudaEventRecord(w->ev[8], st));
             c.launches += launch_poa_fill(dv, pb, ci, w->n_sms, st);
             stage_check(st, "poa_fill");
             R.stats.poa_launches++;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
-            c.launches += launch_poa_trace(dv, tbuf, st);
-            stage_check(st, "poa_trace");
-            VGA_CUDA(cudaEventRecord(w->ev[10], st));
             item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
             c.launches++;
             queue_chain_d2h();          // host-side queueing (and any pinned allocation) hides behind the fill kernel
             VGA_CUDA(cudaMemcpyAsync(h_status.data(), d_status, 4ull * nw, cudaMemcpyDeviceToHost, st));
             VGA_CUDA(cudaStreamSynchronize(st));
-            float a = 0, bms = 0;
-            cudaEventElapsedTime(&a, w->ev[8], w->ev[9]); cudaEventElapsedTime(&bms, w->ev[9], w->ev[10]);
-            ms_fill += a; ms_trace += bms;
+            float a = 0;
+            cudaEventElapsedTime(&a, w->ev[8], w->ev[9]);
+            ms_fill += a;
+            pool_acc = acc;
             std::vector<u32> again;
             u32 done = 0;
             for (u32 x = 0; x < nw; x++) {
                 const u32 it = list[pos + x];
                 if (h_status[x] == IT_RETRY_WIDER) { const int nc = poa_class_wider(ci); if (nc >= 0) cls[nc].push_back(it); else done++; }
                 else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
-                else done++;
+                else { done++; if (h_status[x] == VGA_ALN_OK) trace_list.push_back(it); }
             }
             pos = end;
             if (!again.empty()) {
-                if (done == 0 && again.size() == nw) {
+                // the pool ran out: trace what is complete, start the pool over and run the rest again
+                flush_trace();
+                if (fresh_pool && done == 0 && again.size() == nw) {
                     // nothing fitted: the pool is too small for even one alignment of this wave
                     if (++stall > 2) { set_error("POA trace pool too small for a single alignment"); throw CudaFail{VGA_ERR_NOMEM}; }
-                    for (u32 it : again) est[it] *= 4;
                 }
+                for (u32 it : again) est[it] *= 2;
                 list.insert(list.end(), again.begin(), again.end());
             }
         }
     }
+    flush_trace();
     VGA_CUDA(cudaEventRecord(w->ev[5], st));
     tl_mark("poa waves done");
     // ---- selection + compaction
@@ -932,6 +966,8 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
         VGA_CUDA(cudaStreamSynchronize(c.st));
         VGA_CUDA(cudaEventElapsedTime(&R->stats.ms_total, t0, c.ws->ev[9]));
         R->stats.ms_wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+        tl_mark("call done");
+        tl_flush(R->stats.ms_wall);
         R->stats.d2h_bytes = g_d2h_bytes;
         R->stats.n_reads = n_reads;
         R->stats.kernel_launches = c.launches;
