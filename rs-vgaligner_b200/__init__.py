@@ -120,7 +120,7 @@ def gpu_lib():
     """The CUDA library.  There is no fallback: a missing library is an error."""
     global _gpu
     if _gpu is None:
-        path = os.path.join(_HERE, "libvgaligner_gpu.so")
+        path = os.environ.get("VGA_GPU_LIB") or os.path.join(_HERE, "libvgaligner_gpu.so")
         if not os.path.exists(path):
             raise VgaError("libvgaligner_gpu.so is not built: run `make gpu` (or __graft_entry__.build()); "
                            "the map path has no CPU fallback")

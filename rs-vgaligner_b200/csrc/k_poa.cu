@@ -505,7 +505,8 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
 
 // classes: 0..2 = short reads with 8 / 16 / 32 lanes per alignment (k_poa_short.cu: qlen < 256, int16 absolute scores,
 // bands up to 96 / 160 / 256 columns), 3..5 = SLIDE C = 8, 16, 32 (bands up to 256 / 512 / 1024 columns)
-static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;     // bands up to this use the 8-lane instance
+// bands up to this many columns use the 8-lane instance; off by default: measured slower than 16 lanes on every config
+static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
 int poa_class_count() { return 6; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
     if (poa_short_ok(qlen, nrows, P)) return west <= (i64)g_short_w8 ? 0 : west <= 160 ? 1 : 2;

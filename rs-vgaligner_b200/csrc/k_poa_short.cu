@@ -323,21 +323,25 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
                 }
             } else {                  // merge of the predecessors' last rows, decoded from their trace words
                 const u32* __restrict__ pl = b.nd_pred + pred_base + po;
-                for (i32 jb = jlo; jb <= end + 1; jb += G) {
-                    const i32 j = jb + (i32)gl;
-                    i32 hv = S16, e1v = S16, e2v = S16;
-                    for (u32 x = 0; x < np; x++) {
-                        const u32 p = pl[x];
-                        const i32 pb = b.nd_state[nb + p].beg, pe = b.nd_state[nb + p].end;
-                        if (j >= pb && j <= pe) {
-                            const u32 v = b.pool[(u64)b.rows[row_base + b.nd_row_start[nb + p + 1] - 1].toff * 4 + (u32)(j - pb)];
-                            const i32 hx = sext16(v);
-                            hv = imax(hv, hx);
-                            e1v = imax(e1v, hx - oe1 + (i32)((v >> 16) & 7u));
-                            e2v = imax(e2v, hx - oe2 + (i32)((v >> 19) & 31u));
+                for (u32 x = 0; x < np; x++) {
+                    // one predecessor at a time: its band and trace row are read once, its words stream through the lanes
+                    const u32 p = pl[x];
+                    const int2 pbe = *(const int2*)(b.nd_state + nb + p);
+                    const u32* __restrict__ tw = b.pool + (u64)b.rows[row_base + b.nd_row_start[nb + p + 1] - 1].toff * 4;
+#pragma unroll 2
+                    for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
+                        i32 hv = S16, e1v = S16, e2v = S16;
+                        if (j >= pbe.x && j <= pbe.y) {
+                            const u32 v = tw[j - pbe.x];
+                            hv = sext16(v);
+                            e1v = hv - oe1 + (i32)((v >> 16) & 7u);
+                            e2v = hv - oe2 + (i32)((v >> 19) & 31u);
                         }
+                        if (x > 0) {
+                            hv = imax(hv, (i32)sm.h[j + PAD]); e1v = imax(e1v, (i32)sm.e1[j + PAD]); e2v = imax(e2v, (i32)sm.e2[j + PAD]);
+                        }
+                        sm.h[j + PAD] = (short)hv; sm.e1[j + PAD] = (short)e1v; sm.e2[j + PAD] = (short)e2v;
                     }
-                    if (j <= end + 1) { sm.h[j + PAD] = (short)hv; sm.e1[j + PAD] = (short)e1v; sm.e2[j + PAD] = (short)e2v; }
                 }
             }
         }
