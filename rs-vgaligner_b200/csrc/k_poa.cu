@@ -345,8 +345,13 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
 // ---------------------------------------------------------------------------------------------
 struct TCell { i32 h, e1, e2; bool ok; };
 
-__global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffers b) {
-    const u32 idx = blockIdx.x * blockDim.x + threadIdx.x;
+// `spread` = threads per alignment (a power of two <= 32): only the first of them works.  With few, long
+// alignments a warp of 32 different tracebacks would serialise its divergent steps; spreading them over
+// warps trades idle lanes (there are plenty) for independent progress.
+__global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffers b, u32 spread) {
+    const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid & (spread - 1)) return;
+    const u32 idx = tid / spread;
     if (idx >= b.n_items) return;
     const u32 w = b.work[idx];
     AlignItem* itp = b.items + w;
@@ -542,7 +547,11 @@ int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms,
 
 int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st) {
     if (b.n_items == 0) return 0;
-    poa_trace_kernel<<<(b.n_items + 127) / 128, 128, 0, st>>>(ix, b);
+    // enough tracebacks to fill the machine: one per thread; otherwise spread them out (up to one per warp)
+    u32 spread = 1;
+    while (spread < 32 && (u64)b.n_items * spread * 2 <= 148ull * 2048) spread <<= 1;
+    const u64 threads = (u64)b.n_items * spread;
+    poa_trace_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
     return 1;
 }
 
