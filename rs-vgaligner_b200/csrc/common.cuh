@@ -92,6 +92,9 @@ static const i32 POA_DEEP = -(1 << 30);      // generator value of masked cells 
 // row_base); meta: number of predecessor rows (low 24 bits, 0 = virtual source) | graph base << 24;
 // node/off: subgraph node index and offset inside its label.  Everything the traceback needs for a
 // row with a single predecessor is in this one 32-byte record.
+// trace row layout: the word of column j of a row with band [beg,end] is pool[toff*4 + j - trace_col0(beg)], i.e. rows are
+// stored from the 8-column block that contains beg (the pair kernel stores whole blocks with 16-byte vectors)
+__host__ __device__ static inline i32 trace_col0(i32 beg) { return beg & ~7; }
 struct RowInfo { i32 beg, end; u32 toff; i32 ref; u32 prow, meta, node, off; };
 // per subgraph node: band, row-maximum span and maximum of the node's LAST row
 struct NodeState { i32 beg, end, lpos, rpos, mx, pad0, pad1, pad2; };

@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 // the 32 lanes cover columns [cbb*C, (cbb+32)*C): the band must fit from its block-aligned start
                 if (SLIDE && status == VGA_ALN_OK && end - cbb * C + 1 > 32 * C) status = IT_RETRY_WIDER;
                 // ---- pool space: one trace word per band cell, rows start on 16-byte boundaries
-                const u64 need = (u64)((W + 3) & ~3);
+                const u64 need = (u64)((W + (beg & 7) + 3) & ~3);          // word 0 of a row is column beg & ~7 (trace_col0)
                 if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
                     unsigned long long got = 0;
                     const u64 take = need > POOL_CHUNK ? need : POOL_CHUNK;
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
 #pragma unroll
                                 for (int t = -1; t < C; t++) {
                                     const i32 j = j0 + t;
-                                    wv[t + 1] = (j >= pb && j <= pe) ? tw[j - pb] : 0xffff8000u;
+                                    wv[t + 1] = (j >= pb && j <= pe) ? tw[j - trace_col0(pb)] : 0xffff8000u;
                                 }
 #pragma unroll
                                 for (int t = -1; t < C; t++) {
@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 }
 #pragma unroll
                 for (int t = 0; t < C; t++) {
-                    if (t >= tlo && t <= thi) tr[j0 + t - beg] = wd[t];
+                    if (t >= tlo && t <= thi) tr[j0 + t - trace_col0(beg)] = wd[t];
                 }
                 // ---- row maximum and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i)
                 const i32 mx = __reduce_max_sync(FULL, lmax);
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 i32 h = INT_MIN;
                 if (s < S && b.nd_first_succ[nb + s] < 0) {
                     const RowInfo ri = rows[rs[s + 1] - 1];
-                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - ri.beg)]);
+                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - trace_col0(ri.beg))]);
                 }
                 const i32 mx = __reduce_max_sync(FULL, h);
                 if (mx > best) {                             // strict: the first node wins ties
@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
         if (cur_len) runs[--wpos] = (cur_op << 28) | cur_len;
         cur_op = op; cur_len = 1;
     };
-    auto word_at = [&](const RowInfo& r, i32 jj) -> u32 { return pool[(u64)r.toff * 4 + (u32)(jj - r.beg)]; };
+    auto word_at = [&](const RowInfo& r, i32 jj) -> u32 { return pool[(u64)r.toff * 4 + (u32)(jj - trace_col0(r.beg))]; };
     auto decode = [&](const RowInfo& r, i32 jj, u32 v) {
         TCell c; c.h = c.e1 = c.e2 = POA_NEG_INF; c.ok = false;
         if (jj >= r.beg && jj <= r.end) {
@@ -508,13 +508,20 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     itp->start_off = start_off; itp->end_off = end_off;
 }
 
-// classes: 0..2 = short reads with 8 / 16 / 32 lanes per alignment (k_poa_short.cu: qlen < 256, int16 absolute scores,
-// bands up to 96 / 160 / 256 columns), 3..5 = SLIDE C = 8, 16, 32 (bands up to 256 / 512 / 1024 columns)
-// bands up to this many columns use the 8-lane instance; off by default: measured slower than 16 lanes on every config
+// classes: 0..1 = short reads on the 16x2 kernel with 4 / 8 lanes per alignment (k_poa_pair.cu: qlen < 246, int16 absolute
+// scores, bands up to 16 / 32 blocks of 8 columns), 2 = short reads with 32 lanes (k_poa_short.cu, any read < 256),
+// 3..5 = SLIDE C = 8, 16, 32 (bands up to 256 / 512 / 1024 columns).  An item that does not fit its class moves to the next.
+// VGA_POA_PAIR=0 restores the 8 / 16 / 32-lane kernels of k_poa_short.cu on classes 0..2 (A/B measurements).
+static int g_pair = getenv("VGA_POA_PAIR") ? atoi(getenv("VGA_POA_PAIR")) : 1;
+// alignments start on the 4-lane instance when VGA_POA_G4 is set (default: 8 lanes)
+static int g_pair_g4 = getenv("VGA_POA_G4") ? atoi(getenv("VGA_POA_G4")) : 0;
 static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
 int poa_class_count() { return 6; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
-    if (poa_short_ok(qlen, nrows, P)) return west <= (i64)g_short_w8 ? 0 : west <= 160 ? 1 : 2;
+    if (g_pair) {
+        if (poa_pair_ok(qlen, nrows, P)) return g_pair_g4 ? 0 : 1;
+        if (poa_short_ok(qlen, nrows, P)) return 2;
+    } else if (poa_short_ok(qlen, nrows, P)) return west <= (i64)g_short_w8 ? 0 : west <= 160 ? 1 : 2;
     if (west <= 256 - 8) return 3;
     if (west <= 512 - 16) return 4;
     return 5;
@@ -537,7 +544,9 @@ static void launch_fill(const DevIndex& ix, const PoaBuffers& b, int n_sms, cuda
 int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st) {
     if (b.n_items == 0) return 0;
     switch (cls) {
-        case 0: case 1: case 2: return launch_poa_fill_short(ix, b, cls, n_sms, st);
+        case 0: case 1: if (g_pair) return launch_poa_fill_pair(ix, b, cls, n_sms, st);
+        // fall through
+        case 2: return launch_poa_fill_short(ix, b, cls, n_sms, st);
         case 3: launch_fill<8, true>(ix, b, n_sms, st); break;
         case 4: launch_fill<16, true>(ix, b, n_sms, st); break;
         default: launch_fill<32, true>(ix, b, n_sms, st); break;

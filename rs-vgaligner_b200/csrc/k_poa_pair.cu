@@ -1,0 +1,500 @@
+// K5 (short reads, 16x2 arithmetic) — banded sequence-to-graph POA fill for reads shorter than 256 bases, replacing
+// the abPOA call at the reference's FFI seam (src/align.rs:190-202).  Same alignment definition, trace word
+// format, RowInfo / NodeState records and work-queue protocol as k_poa.cu / k_poa_short.cu; the
+// traceback kernel is shared.
+//
+// What is different from k_poa_short.cu: the DP arithmetic runs two query columns per 32-bit register on the
+// sm_100a 16x2 integer instructions (VIADD.16x2, VIMNMX3.S16x2, VIADDMNMX.S16x2[.RELU]); absolute scores fit
+// int16 in this class (same criterion as before).
+//   * Columns are grouped in aligned BLOCKS of 8 (block b = columns 8b-8 .. 8b-1, so column -1 exists).  Inside a
+//     block, 32-bit word t (t = 0..3) holds column t in its low half and column t+4 in its high half.  A block is
+//     thus two independent 4-column chains (A = columns 0..3 in the low halves, B = columns 4..7 in the high
+//     halves): the left neighbour of pair t is pair t-1 for BOTH halves, so the diagonal operand and the serial
+//     part of the F1/F2 prefix-max scans need no per-pair shuffling.  Chains are stitched per lane in scalar code
+//     (2 chains per block), lanes by Kogge-Stone over the group.
+//   * The previous row (H, E1', E2') and the query profile live in shared memory in exactly this layout: one
+//     LDS.128 / STS.128 per plane and block.  A GROUP of G lanes owns one (read, chain); lane l computes NB
+//     consecutive blocks starting at block (beg+8)/8 + l*NB, NB = 1..4 chosen per row from the band width.
+//   * Band limits inside the first / last block are applied with validity words from a small shared table
+//     (masked cells get Hhat = -inf exactly); trace rows are stored as whole blocks with 16-byte vectors, which is
+//     why word 0 of a trace row is column beg & ~7 (trace_col0, common.cuh).
+//   * Row maximum: 16x2 running max, one group reduction, then VIMNMX.S16x2 predicate outputs mark the columns
+//     equal to it; leftmost / rightmost column from the lane's bit mask and one packed group reduction.
+// Roofline: INT32 ALU issue.  Algorithmic work = band cells.
+#include <climits>
+#include <cstdlib>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace vga {
+
+static const int PP_WARPS = 4;                 // warps per CTA
+static const u64 PAIR_POOL_CHUNK = 4096;       // trace words a group takes from the pool per refill (multiple of 8)
+static const i32 NEG16 = -32000;               // -inf of the int16 planes; reachable scores are >= -30000 in this class
+static const u32 NEGP = 0x83008300u;           // NEG16 in both halves
+static const i32 PAIR_SCORE_LIMIT = 30000;
+static const int VT_WORDS = 8 * 9;             // validity table entries (uint4 each): [a = 0..7][z = 0..8]
+
+__device__ __forceinline__ i32 imax(i32 a, i32 b) { return a > b ? a : b; }
+__device__ __forceinline__ i32 imin(i32 a, i32 b) { return a < b ? a : b; }
+__device__ __forceinline__ i32 sext16(u32 w) { return (i32)(short)(w & 0xffffu); }
+__device__ __forceinline__ u32 pair16(i32 lo, i32 hi) { return __byte_perm((u32)lo, (u32)hi, 0x5410); }
+__device__ __forceinline__ u32 both16(i32 v) { return __byte_perm((u32)v, (u32)v, 0x1010); }
+// half-word index of query column j (j >= -8) inside a plane
+__device__ __forceinline__ int hw_index(i32 j) {
+    const i32 c = j + 8;
+    return (int)(((c >> 3) << 3) | ((c & 3) << 1) | ((c >> 2) & 1));
+}
+
+struct PairConst {
+    u32 ne1p, ne2p, noe1p, noe2p;      // -e1, -e2, -(o1+e1), -(o2+e2) in both halves
+    u32 o1p, o2p, o1p1, o2p1;          // o1, o2, o1+1, o2+1 in both halves
+    i32 e1, e2;
+};
+struct PairRowOut { i32 mx, lpos, rpos; };
+
+template <int G> __device__ __forceinline__ u32 pair_group_mask(u32 lane) {
+    return G == 32 ? 0xffffffffu : (((1u << (G & 31)) - 1u) << (lane & ~(u32)(G - 1)));
+}
+
+// One DP row of one group.  planes = H, E1', E2' (nblk blocks each) of the group; prof = profile plane of the row's
+// graph base; vtab = validity table; tr = trace word of column beg & ~7.
+template <int G, int NB>
+__device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 gl, i32 beg, i32 end, uint4* __restrict__ planes,
+                                                int nblk, const uint4* __restrict__ prof, const uint4* __restrict__ vtab,
+                                                u32* __restrict__ tr) {
+    const i32 b0 = (beg + 8) >> 3, bend = (end + 8) >> 3;
+    const i32 bme = b0 + (i32)gl * NB;                  // the lane's first block
+    const i32 cfirst = bme * 8 - 8;                     // and its first column
+    const i32 D = beg - cfirst, Eo = end - cfirst + 1;
+    uint4* const Hpl = planes;
+    uint4* const E1pl = planes + nblk;
+    uint4* const E2pl = planes + 2 * nblk;
+    u32 hh[NB][4], fl1[NB][4], fl2[NB][4], x1[NB][4], x2[NB][4];
+    u32 R1[NB], R2[NB];
+    // ---- sweep 1: Hhat = max(M, E1, E2) masked to the band, chain-local part of the F scans (F' = F + o + e)
+    u32 hprev = ((const u32*)(Hpl + (imin(bme, nblk - 1) - 1)))[3];
+#pragma unroll
+    for (int k = 0; k < NB; k++) {
+        const int bk = imin(bme + k, nblk - 1);         // lanes right of the band read the spare block (all their cells are masked)
+        const uint4 hv = Hpl[bk], e1v = E1pl[bk], e2v = E2pl[bk], pv = prof[bk];
+        const i32 a = __viaddmax_s32(D, -8 * k, 0);                    // invalid cells at the block's left  (0..7)
+        const i32 z = imin(__viaddmax_s32(Eo, -8 * k, 0), 8);          // cells r < z are left of end+1      (0..8)
+        const uint4 V = vtab[a * 9 + z];
+        const u32 hw[4] = {hv.x, hv.y, hv.z, hv.w};
+        const u32 pw[4] = {pv.x, pv.y, pv.z, pv.w};
+        const u32 vw[4] = {V.x, V.y, V.z, V.w};
+        x1[k][0] = e1v.x; x1[k][1] = e1v.y; x1[k][2] = e1v.z; x1[k][3] = e1v.w;
+        x2[k][0] = e2v.x; x2[k][1] = e2v.y; x2[k][2] = e2v.z; x2[k][3] = e2v.w;
+        u32 hd = __byte_perm(hprev, hv.w, 0x5432);      // (column 8k-1, column 8k+3): diagonal operands of pair 0
+        u32 r1 = NEGP, r2 = NEGP;
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            const u32 m = __vadd2(hd, pw[t]);
+            u32 h = __vimax3_s16x2(m, x1[k][t], x2[k][t]);
+            h = (h & vw[t]) | (NEGP & ~vw[t]);
+            hh[k][t] = h;
+            fl1[k][t] = r1; fl2[k][t] = r2;
+            r1 = __viaddmax_s16x2(r1, K.ne1p, h);
+            r2 = __viaddmax_s16x2(r2, K.ne2p, h);
+            hd = hw[t];
+        }
+        hprev = hv.w;
+        R1[k] = r1; R2[k] = r2;
+    }
+    // ---- stitch the chains of the lane (A0, B0, A1, B1, ...), then the lanes of the group
+    u32 in1[NB], in2[NB];
+    i32 c1 = NEG16, c2 = NEG16;
+#pragma unroll
+    for (int k = 0; k < NB; k++) {
+        const i32 a1 = sext16(R1[k]), b1 = (i32)R1[k] >> 16, a2 = sext16(R2[k]), b2 = (i32)R2[k] >> 16;
+        const i32 ia1 = c1, ia2 = c2;
+        c1 = __viaddmax_s32(c1, -4 * K.e1, a1); c2 = __viaddmax_s32(c2, -4 * K.e2, a2);
+        in1[k] = pair16(ia1, c1); in2[k] = pair16(ia2, c2);
+        c1 = __viaddmax_s32(c1, -4 * K.e1, b1); c2 = __viaddmax_s32(c2, -4 * K.e2, b2);
+    }
+#pragma unroll
+    for (int d = 1; d < G; d <<= 1) {       // shfl_up leaves lanes < d unchanged, and max(v, v - c) = v
+        const i32 t1 = __shfl_up_sync(gm, c1, d, G), t2 = __shfl_up_sync(gm, c2, d, G);
+        c1 = __viaddmax_s32(t1, -K.e1 * 8 * NB * d, c1);
+        c2 = __viaddmax_s32(t2, -K.e2 * 8 * NB * d, c2);
+    }
+    c1 = __shfl_up_sync(gm, c1, 1, G); c2 = __shfl_up_sync(gm, c2, 1, G);
+    if (gl == 0) { c1 = NEG16; c2 = NEG16; }
+    {
+        const u32 c1p = both16(c1), c2p = both16(c2);
+#pragma unroll
+        for (int k = 0; k < NB; k++) {
+            in1[k] = __viaddmax_s16x2(c1p, pair16(-K.e1 * 8 * k, -K.e1 * (8 * k + 4)), in1[k]);
+            in2[k] = __viaddmax_s16x2(c2p, pair16(-K.e2 * 8 * k, -K.e2 * (8 * k + 4)), in2[k]);
+        }
+    }
+    // ---- sweep 2a: H and the running maximum
+    u32 H[NB][4], f1[NB][4], f2[NB][4];
+    u32 mxacc = NEGP;
+#pragma unroll
+    for (int k = 0; k < NB; k++) {
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            f1[k][t] = __viaddmax_s16x2(in1[k], both16(-K.e1 * t), fl1[k][t]);
+            f2[k][t] = __viaddmax_s16x2(in2[k], both16(-K.e2 * t), fl2[k][t]);
+            const u32 hp = __viaddmax_s16x2(f1[k][t], K.noe1p, hh[k][t]);
+            H[k][t] = __viaddmax_s16x2(f2[k][t], K.noe2p, hp);
+            mxacc = __vmaxs2(mxacc, H[k][t]);
+        }
+    }
+    // 1 - H of the column left of the lane's first one (F fields of pair 0 of block 0); lane 0 has none (don't care)
+    u32 qleft = __shfl_up_sync(gm, __vadd2(~H[NB - 1][3], 0x00020002u), 1, G);
+    // ---- sweep 2b: E', trace words, stores
+#pragma unroll
+    for (int k = 0; k < NB; k++) {
+        u32 q[4], wlo[4], whi[4], e1n[4], e2n[4];
+#pragma unroll
+        for (int t = 0; t < 4; t++) q[t] = __vadd2(~H[k][t], 0x00020002u);         // 1 - H
+        const u32 ql0 = __byte_perm(qleft, q[3], 0x5432);                          // (column 8k-1, column 8k+3)
+        qleft = q[3];
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            const u32 nq = ~H[k][t];
+            const u32 u1 = __vadd2(nq, K.o1p1), u2 = __vadd2(nq, K.o2p1);           // o - H
+            const u32 d1 = __viaddmin_s16x2_relu(x1[k][t], u1, K.o1p);              // E1' - (H - oe1) in [0, o1]
+            const u32 d2 = __viaddmin_s16x2_relu(x2[k][t], u2, K.o2p);
+            const u32 ql = t == 0 ? ql0 : q[t - 1];
+            const u32 g1 = __viaddmin_s16x2_relu(f1[k][t], ql, K.o1p1);             // max(F1 - (Hleft - oe1), -1) + 1
+            const u32 g2 = __viaddmin_s16x2_relu(f2[k][t], ql, K.o2p1);
+            const u32 hi = d1 + d2 * 8u + g1 * 256u + g2 * 2048u;                   // fields are bounded: no carry between halves
+            wlo[t] = __byte_perm(H[k][t], hi, 0x5410);
+            whi[t] = __byte_perm(H[k][t], hi, 0x7632);
+            e1n[t] = __viaddmax_s16x2(x1[k][t], K.ne1p, __vadd2(H[k][t], K.noe1p));
+            e2n[t] = __viaddmax_s16x2(x2[k][t], K.ne2p, __vadd2(H[k][t], K.noe2p));
+        }
+        if (bme + k <= bend) {
+            uint4* const t4 = (uint4*)(tr + 8 * (bme + k - b0));
+            t4[0] = make_uint4(wlo[0], wlo[1], wlo[2], wlo[3]);
+            t4[1] = make_uint4(whi[0], whi[1], whi[2], whi[3]);
+            Hpl[bme + k] = make_uint4(H[k][0], H[k][1], H[k][2], H[k][3]);
+            E1pl[bme + k] = make_uint4(e1n[0], e1n[1], e1n[2], e1n[3]);
+            E2pl[bme + k] = make_uint4(e2n[0], e2n[1], e2n[2], e2n[3]);
+        }
+    }
+    // guards: H(beg-1) = -inf (diagonal of column beg in the next row) and E'(end+1) = -inf (vertical of column end+1).
+    // A guard inside a block stored this row is written by the block's owner after its stores; other blocks are not stored.
+    if (gl == 0 && (beg & 7) == 0) ((short*)Hpl)[hw_index(beg - 1)] = (short)NEG16;
+    {
+        const i32 ow = imin((((end + 9) >> 3) - b0) / NB, G - 1);
+        if ((i32)gl == ow) {
+            const int x = hw_index(end + 1);
+            ((short*)E1pl)[x] = (short)NEG16;
+            ((short*)E2pl)[x] = (short)NEG16;
+        }
+    }
+    // ---- row maximum and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i).  Masked cells are below every
+    // in-band value: left of beg they are -inf, right of end they hold an F that decays from a band cell.
+    i32 mx = imax(sext16(mxacc), (i32)mxacc >> 16);
+#pragma unroll
+    for (int d = G / 2; d > 0; d >>= 1) mx = imax(mx, __shfl_xor_sync(gm, mx, d, G));
+    const u32 mxp = both16(mx);
+    u32 eq = 0;
+#pragma unroll
+    for (int k = 0; k < NB; k++) {
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            bool ph, pl;
+            (void)__vibmax_s16x2(H[k][t], mxp, &ph, &pl);          // H >= mx  <=>  H == mx
+            if (pl) eq |= 1u << (8 * k + t);
+            if (ph) eq |= 1u << (8 * k + t + 4);
+        }
+    }
+    u32 key = 0;                                  // (511 - leftmost) << 16 | rightmost; lanes without a maximum lose both
+    if (eq) key = ((u32)(511 - (cfirst + __ffs((int)eq) - 1)) << 16) | (u32)(cfirst + 31 - __clz((int)eq));
+#pragma unroll
+    for (int d = G / 2; d > 0; d >>= 1) key = __vmaxs2(key, __shfl_xor_sync(gm, key, d, G));
+    PairRowOut o;
+    o.mx = mx;
+    o.lpos = 511 - (i32)(key >> 16);
+    o.rpos = (i32)(key & 0xffffu);
+    return o;
+}
+
+// NBMAX = blocks per lane the row body is instantiated for (register budget); wider bands move to the next class
+template <int G, int NBMAX>
+__global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex ix, PoaBuffers b, int nblk) {
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    uint4* const vtab = (uint4*)dyn_smem;
+    uint4* const planes = vtab + VT_WORDS + (size_t)(threadIdx.x / G) * 8 * nblk;     // H, E1', E2', 5 profile planes
+    short* const Hs = (short*)planes;
+    short* const E1s = (short*)(planes + nblk);
+    short* const E2s = (short*)(planes + 2 * nblk);
+    const u32 lane = threadIdx.x & 31;
+    const u32 gl = lane & (G - 1);
+    const u32 gm = pair_group_mask<G>(lane);
+    // validity table: entry (a, z), word t: low half = column t, high half = column t+4; valid iff a <= column < z
+    for (int i = threadIdx.x; i < VT_WORDS; i += blockDim.x) {
+        const int a = i / 9, z = i % 9;
+        u32 w[4];
+        for (int t = 0; t < 4; t++) w[t] = ((a <= t && t < z) ? 0xffffu : 0u) | ((a <= t + 4 && t + 4 < z) ? 0xffff0000u : 0u);
+        vtab[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    __syncthreads();
+    PairConst K;
+    K.e1 = b.e1; K.e2 = b.e2;
+    K.ne1p = both16(-b.e1); K.ne2p = both16(-b.e2);
+    K.noe1p = both16(-(b.o1 + b.e1)); K.noe2p = both16(-(b.o2 + b.e2));
+    K.o1p = both16(b.o1); K.o2p = both16(b.o2); K.o1p1 = both16(b.o1 + 1); K.o2p1 = both16(b.o2 + 1);
+    const i32 oe1 = b.o1 + b.e1, oe2 = b.o2 + b.e2;
+    const i32 smatch = b.match, smis = -b.mismatch;
+    if (gl == 0) Hs[hw_index(-1)] = (short)NEG16;       // column -1: M(i,0) does not exist
+    const int ncols = (nblk - 1) * 8;                   // columns -8 .. ncols-9 are backed by real blocks
+    // ---- group-uniform state of the alignment in flight
+    bool active = false;
+    u32 w = 0, nb = 0, S = 0, pred_base = 0, row_base = 0, nrows = 0;
+    i32 qlen = 0, wband = 0, end0 = 0;
+    const u8* __restrict__ q = nullptr;
+    u32 row = 0, s = 0, o = 0, metas = 0;
+    i32 beg = 0, end = 0, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
+    u64 cells = 0;
+    u32 status = VGA_ALN_OK, custom_base = 0xffffffffu;
+    u64 pool_cur = 0, pool_end = 0;                 // this group's current chunk of the trace pool (words)
+
+    // result record of the item in flight; the group goes back to fetching
+    auto finish = [&]() {
+        i32 best = INT_MIN;
+        u32 bs = 0xffffffffu;
+        if (status == VGA_ALN_OK) {
+            // global end: sink predecessors (nodes without successors, ascending) that reach column qlen
+            const u32* __restrict__ rs = b.nd_row_start + nb;
+            const RowInfo* __restrict__ rows = b.rows + row_base;
+            __syncwarp(gm);
+            for (u32 s0 = 0; s0 < S; s0 += G) {
+                const u32 sx = s0 + gl;
+                i32 h = INT_MIN;
+                if (sx < S && b.nd_first_succ[nb + sx] < 0) {
+                    const RowInfo ri = rows[rs[sx + 1] - 1];
+                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - trace_col0(ri.beg))]);
+                }
+                i32 mx = h;
+#pragma unroll
+                for (int d = G / 2; d > 0; d >>= 1) mx = imax(mx, __shfl_xor_sync(gm, mx, d, G));
+                if (mx > best) {                             // strict: the first node wins ties
+                    best = mx;
+                    i32 mn = h == mx ? (i32)sx : INT_MAX;
+#pragma unroll
+                    for (int d = G / 2; d > 0; d >>= 1) mn = imin(mn, __shfl_xor_sync(gm, mn, d, G));
+                    bs = (u32)mn;
+                }
+            }
+            if (bs == 0xffffffffu) status = VGA_ALN_EMPTY;
+        }
+        if (gl == 0) {
+            AlignItem* out = b.items + w;
+            out->status = status;
+            out->score = status == VGA_ALN_OK ? best : 0;
+            out->end_node = bs;
+            out->cells = cells;
+            out->n_runs = 0; out->n_path = 0; out->path_len = 0; out->start_off = 0; out->end_off = 0; out->n_aligned = 0;
+        }
+        active = false;
+    };
+
+    for (;;) {
+        if (!active) {
+            // ---- next (read, chain) of the work list
+            u32 wi = 0;
+            if (gl == 0) wi = atomicAdd(b.work_ctr, 1u);
+            wi = __shfl_sync(gm, wi, 0, G);
+            if (wi >= b.n_items) break;
+            w = b.work[wi];
+            const AlignItem it = b.items[w];
+            qlen = (i32)it.qlen;
+            q = (const u8*)b.seqs + it.q_off;
+            wband = b.wb + (i32)(b.wf * (float)qlen);
+            nb = it.node_base; S = it.S; row_base = it.row_base; pred_base = it.pred_base; nrows = it.nrows;
+            status = VGA_ALN_OK;
+            cells = 0; row = 0; s = 0; o = 0; ppb = 0; ppe = -1; lpos = 0; rpos = 0; mxrow = 0;
+            custom_base = 0xffffffffu;
+            active = true;
+            if (S == 0 || nrows == 0) { status = VGA_ALN_EMPTY; finish(); continue; }
+            // absolute H is kept as int16 (trace words and shared memory): every DP step loses at most
+            // max(mismatch, o1+e1), so reachable scores are >= -that*(rows+qlen); other alignments go to the general kernel
+            if (qlen + 10 > ncols - 8 || (i64)imax(b.mismatch, oe1) * ((i64)nrows + qlen) > PAIR_SCORE_LIMIT) {
+                status = IT_RETRY_WIDER;
+                finish();
+                continue;
+            }
+            {   // band end of the virtual source row: max_remain of the first row + 1
+                const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
+                end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+            }
+            // query profile: score of column j (query base j-1) against A, C, T, G (order of the 2-bit code (c >> 1) & 3)
+            __syncwarp(gm);
+            for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G) {
+                const u32 c = (j >= 1 && j <= qlen) ? q[j - 1] : 0u;
+                const int x = hw_index(j);
+                ((short*)(planes + 3 * nblk))[x] = (short)(c == 'A' ? smatch : smis);
+                ((short*)(planes + 4 * nblk))[x] = (short)(c == 'C' ? smatch : smis);
+                ((short*)(planes + 5 * nblk))[x] = (short)(c == 'T' ? smatch : smis);
+                ((short*)(planes + 6 * nblk))[x] = (short)(c == 'G' ? smatch : smis);
+            }
+            __syncwarp(gm);
+        }
+        // ---- one DP row; its record (sub_rowmeta_kernel) is fetched G rows at a time
+        if ((row & (G - 1)) == 0) metas = (row + gl < nrows) ? b.row_meta[row_base + row + gl] : 0u;
+        const u32 meta = __shfl_sync(gm, metas, row & (G - 1), G);
+        const u32 base = meta & 0xffu, kind = (meta >> 8) & 3u;
+        // predecessor row: the previous row unless this is a first row with other predecessors
+        i32 mpl = lpos + 1, mpr = rpos + 1, min_pb = ppb, max_pe = ppe;
+        u32 prow = row - 1, np = 1, po = 0;
+        if (kind == 1) { mpl = 1; mpr = 1; min_pb = 0; max_pe = end0; np = 0; prow = 0; }      // virtual source row
+        else if (kind == 2) {
+            __syncwarp(gm);       // NodeState / RowInfo / trace words of earlier rows were written by other lanes of the group
+            po = b.nd_pred_off[nb + s];
+            np = b.nd_pred_off[nb + s + 1] - po;
+            const u32* __restrict__ pl = b.nd_pred + pred_base + po;
+            mpl = INT_MAX; mpr = 0; min_pb = INT_MAX; max_pe = -1;
+            for (u32 x = 0; x < np; x++) {
+                const NodeState ns = b.nd_state[nb + pl[x]];
+                mpl = imin(mpl, ns.lpos + 1); mpr = imax(mpr, ns.rpos + 1);
+                min_pb = imin(min_pb, ns.beg); max_pe = imax(max_pe, ns.end);
+            }
+            prow = b.nd_row_start[nb + pl[0] + 1] - 1;
+        }
+        // adaptive band (abPOA GET_AD_DP_BEGIN/END + clipping to the predecessors' bands)
+        const i32 r = qlen - (i32)(meta >> 11);
+        beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
+        end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
+        const i32 W = end - beg + 1;
+        const i32 nblocks = ((end + 8) >> 3) - ((beg + 8) >> 3) + 1;
+        int cr = (nblocks + G - 1) / G;               // blocks per lane
+        if (beg > end) status = VGA_ALN_BAND_ERR;
+        else if (cr > NBMAX) status = IT_RETRY_WIDER;
+        // pool space: whole blocks, one trace word per cell
+        const u64 need = (u64)nblocks * 8;
+        if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
+            unsigned long long got = 0;
+            const u64 take = need > PAIR_POOL_CHUNK ? need : PAIR_POOL_CHUNK;
+            if (gl == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
+            got = __shfl_sync(gm, got, 0, G);
+            if (got + take > b.pool_words) status = IT_RETRY_POOL;
+            else { pool_cur = got; pool_end = got + take; }
+        }
+        if (status != VGA_ALN_OK) { finish(); continue; }
+        u32* __restrict__ tr = b.pool + pool_cur;
+        if (gl == 0) {
+            uint4* dst = (uint4*)(b.rows + row_base + row);
+            dst[0] = make_uint4((u32)beg, (u32)end, (u32)(pool_cur >> 2), 0u);
+            dst[1] = make_uint4(prow, (np < 0xffffffu ? np : 0xffffffu) | (base << 24), s, o);
+        }
+        pool_cur += need;
+        cells += (u64)W;
+        if (kind != 0) {
+            // the predecessor row is not the one in shared memory: build it there (columns beg-1 .. end+1)
+            const i32 jlo = imax(beg - 1, 0);
+            if (kind == 1) {          // virtual source row
+                __syncwarp(gm);
+                for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
+                    const bool in0 = j <= end0;
+                    const int x = hw_index(j);
+                    Hs[x] = (short)(!in0 ? NEG16 : j == 0 ? 0 : imax(-(b.o1 + b.e1 * j), -(b.o2 + b.e2 * j)));
+                    E1s[x] = (short)(j == 0 ? -oe1 : NEG16);
+                    E2s[x] = (short)(j == 0 ? -oe2 : NEG16);
+                }
+            } else {                  // merge of the predecessors' last rows, decoded from their trace words
+                const u32* __restrict__ pl = b.nd_pred + pred_base + po;
+                for (u32 x = 0; x < np; x++) {
+                    // one predecessor at a time: its band and trace row are read once, its words stream through the lanes
+                    const u32 p = pl[x];
+                    const int2 pbe = *(const int2*)(b.nd_state + nb + p);
+                    const u32* __restrict__ tw = b.pool + (u64)b.rows[row_base + b.nd_row_start[nb + p + 1] - 1].toff * 4;
+                    const i32 pc0 = trace_col0(pbe.x);
+#pragma unroll 2
+                    for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
+                        i32 hv = NEG16, e1v = NEG16, e2v = NEG16;
+                        if (j >= pbe.x && j <= pbe.y) {
+                            const u32 v = tw[j - pc0];
+                            hv = sext16(v);
+                            e1v = hv - oe1 + (i32)((v >> 16) & 7u);
+                            e2v = hv - oe2 + (i32)((v >> 19) & 31u);
+                        }
+                        const int xx = hw_index(j);
+                        if (x > 0) {
+                            hv = imax(hv, (i32)Hs[xx]); e1v = imax(e1v, (i32)E1s[xx]); e2v = imax(e2v, (i32)E2s[xx]);
+                        }
+                        Hs[xx] = (short)hv; E1s[xx] = (short)e1v; E2s[xx] = (short)e2v;
+                    }
+                }
+            }
+        }
+        // substitution profile row of this graph base
+        u32 code = (base >> 1) & 3u;
+        if (base != ((0x47544341u >> (8 * code)) & 0xffu)) {          // not A, C, T, G: custom row
+            code = 4;
+            if (base != custom_base) {
+                __syncwarp(gm);
+                for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G)
+                    ((short*)(planes + 7 * nblk))[hw_index(j)] = (short)((j >= 1 && j <= qlen && q[j - 1] == base) ? smatch : smis);
+                custom_base = base;
+            }
+        }
+        __syncwarp(gm);
+        const uint4* pr = planes + (3 + code) * nblk;
+        // the groups of the warp that are here together agree on the largest block count among them (stay converged)
+        cr = __reduce_max_sync(__activemask(), cr);
+        PairRowOut ro;
+        if (cr == 1) ro = row_pairs<G, 1>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
+        else if (NBMAX >= 3 && cr == 2) ro = row_pairs<G, (NBMAX >= 3 ? 2 : 1)>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
+        else if (NBMAX >= 4 && cr == 3) ro = row_pairs<G, (NBMAX >= 4 ? 3 : 1)>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
+        else ro = row_pairs<G, NBMAX>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
+        lpos = ro.lpos; rpos = ro.rpos; mxrow = ro.mx;
+        ppb = beg; ppe = end;
+        if (meta & 0x400u) {
+            // last row of its node: it may be a predecessor of later nodes' first rows
+            if (gl == 0) {
+                int4* dst = (int4*)(b.nd_state + nb + s);
+                dst[0] = make_int4(beg, end, lpos, rpos);
+                dst[1] = make_int4(mxrow, 0, 0, 0);
+            }
+            s++; o = 0;
+        } else o++;
+        row++;
+        if (row == nrows) finish();
+    }
+}
+
+template <int G, int NBMAX>
+static void launch_pair(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
+    int per_sm = 0;
+    const int groups_per_cta = PP_WARPS * 32 / G;
+    int qmax = b.qmax_short < 16 ? 16 : b.qmax_short > 255 ? 255 : b.qmax_short;
+    const int nblk = ((qmax + 9) >> 3) + 3;         // columns -8 .. qmax+1 (+ slack), plus the spare block
+    const size_t smem_bytes = ((size_t)VT_WORDS + (size_t)groups_per_cta * 8 * nblk) * sizeof(uint4);
+    static size_t attr_bytes = 0;
+    if (smem_bytes > attr_bytes) {
+        VGA_CUDA(cudaFuncSetAttribute(poa_fill_pair_kernel<G, NBMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        attr_bytes = smem_bytes;
+    }
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, poa_fill_pair_kernel<G, NBMAX>, PP_WARPS * 32, smem_bytes);
+    if (per_sm < 1) per_sm = 1;
+    long long ctas = (long long)n_sms * per_sm;
+    const long long need = ((long long)b.n_items + groups_per_cta - 1) / groups_per_cta;
+    if (ctas > need) ctas = need;
+    if (ctas < 1) ctas = 1;
+    poa_fill_pair_kernel<G, NBMAX><<<(unsigned)ctas, PP_WARPS * 32, smem_bytes, st>>>(ix, b, nblk);
+}
+
+// pair classes: 0 = 4 lanes per alignment (bands up to 12 blocks of 8 columns), 1 = 8 lanes (up to 24 blocks: every band of a read < 178)
+int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st) {
+    if (b.n_items == 0) return 0;
+    if (cls == 0) launch_pair<4, 3>(ix, b, n_sms, st);
+    else launch_pair<8, 3>(ix, b, n_sms, st);
+    return 1;
+}
+
+// the 16x2 kernel's field arithmetic assumes the default-sized gap model (decays and constants stay inside int16)
+bool poa_pair_ok(i64 qlen, i64 nrows, const VgaParams& P) {
+    const i64 step = P.mismatch > P.o1 + P.e1 ? P.mismatch : P.o1 + P.e1;
+    return qlen < 246 && step * (nrows + qlen) <= PAIR_SCORE_LIMIT && P.e1 >= 1 && P.e1 <= 2 && P.e2 >= 1 && P.e2 <= 2 &&
+           P.o1 >= 0 && P.o1 <= 6 && P.o2 >= 0 && P.o2 <= 30 && P.match >= 0 && P.match <= 64 && P.mismatch >= 0 && P.mismatch <= 64;
+}
+
+}  // namespace vga

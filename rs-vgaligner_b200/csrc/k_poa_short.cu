@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
                 i32 h = INT_MIN;
                 if (sx < S && b.nd_first_succ[nb + sx] < 0) {
                     const RowInfo ri = rows[rs[sx + 1] - 1];
-                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - ri.beg)]);
+                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - trace_col0(ri.beg))]);
                 }
                 const i32 mx = group_max<G>(gm, h);
                 if (mx > best) {                             // strict: the first node wins ties
@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
         if (beg > end) status = VGA_ALN_BAND_ERR;
         else if (cr == 0) status = IT_RETRY_WIDER;
         // pool space: one trace word per band cell, rows start on 16-byte boundaries
-        const u64 need = (u64)((W + 3) & ~3);
+        const u64 need = (u64)((W + (beg & 7) + 3) & ~3);          // word 0 of a row is column beg & ~7 (trace_col0)
         if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
             unsigned long long got = 0;
             const u64 take = need > GROUP_POOL_CHUNK ? need : GROUP_POOL_CHUNK;
@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
             else { pool_cur = got; pool_end = got + take; }
         }
         if (status != VGA_ALN_OK) { finish(); continue; }
-        u32* __restrict__ tr = b.pool + pool_cur;
+        u32* __restrict__ tr = b.pool + pool_cur + (beg & 7);
         if (gl == 0) {
             uint4* dst = (uint4*)(b.rows + row_base + row);
             dst[0] = make_uint4((u32)beg, (u32)end, (u32)(pool_cur >> 2), 0u);
@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
                     for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
                         i32 hv = S16, e1v = S16, e2v = S16;
                         if (j >= pbe.x && j <= pbe.y) {
-                            const u32 v = tw[j - pbe.x];
+                            const u32 v = tw[j - trace_col0(pbe.x)];
                             hv = sext16(v);
                             e1v = hv - oe1 + (i32)((v >> 16) & 7u);
                             e2v = hv - oe2 + (i32)((v >> 19) & 31u);

@@ -614,6 +614,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     pb.rows = w->b[B_ROWS].get<RowInfo>(tot[2]);
     pb.row_meta = d_row_meta;
     pb.match = P.match; pb.mismatch = P.mismatch; pb.o1 = P.o1; pb.e1 = P.e1; pb.o2 = P.o2; pb.e2 = P.e2; pb.wb = P.wb; pb.wf = P.wf;
+    pb.qmax_short = 0;
     pb.work_ctr = ctr + 2; pb.pool_ctr = (unsigned long long*)(ctr + 4);
     TraceBuffers tbuf;
     memset(&tbuf, 0, sizeof(tbuf));
@@ -635,7 +636,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
             const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
             const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
-            est[i] = (u64)(nrows * (west + 4));
+            est[i] = (u64)(nrows * (west + 12));           // rows are stored from an 8-column boundary (trace_col0)
+            if (poa_short_ok(qlen, nrows, P) && qlen > (i64)pb.qmax_short) pb.qmax_short = (i32)qlen;
             est_total += est[i];
             const int ci = poa_class_for(qlen, nrows, west, P);
             const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
@@ -685,6 +687,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             float t = 0;
             cudaEventElapsedTime(&t, w->ev[9], w->ev[10]);
             ms_trace += t;
+            if (host_timeline()) fprintf(stderr, "[vga] poa trace: %zu items, %.3f ms\n", trace_list.size(), t);
             trace_list.clear();
         }
         VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
@@ -722,6 +725,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             float a = 0;
             cudaEventElapsedTime(&a, w->ev[8], w->ev[9]);
             ms_fill += a;
+            if (host_timeline()) fprintf(stderr, "[vga] poa fill class %d: %u items, %.3f ms\n", ci, nw, a);
             pool_acc = acc;
             std::vector<u32> again;
             u32 done = 0;
