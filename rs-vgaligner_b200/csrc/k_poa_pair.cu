@@ -1,7 +1,9 @@
-// K5 (short reads, 16x2 arithmetic) — banded sequence-to-graph POA fill for reads shorter than 256 bases, replacing
+// K5 (short reads, 16x2 arithmetic) — banded sequence-to-graph POA fill for reads shorter than 246 bases, replacing
 // the abPOA call at the reference's FFI seam (src/align.rs:190-202).  Same alignment definition, trace word
 // format, RowInfo / NodeState records and work-queue protocol as k_poa.cu / k_poa_short.cu; the
-// traceback kernel is shared.
+// traceback kernel is shared.  This instance is compiled for abPOA's default gap model (o1=4, e1=2, o2=24, e2=1 —
+// the only one the reference ever uses, src/align.rs:190-202), so every gap constant is an immediate; other gap
+// models run on the 32-bit kernels.
 //
 // What is different from k_poa_short.cu: the DP arithmetic runs two query columns per 32-bit register on the
 // sm_100a 16x2 integer instructions (VIADD.16x2, VIMNMX3.S16x2, VIADDMNMX.S16x2[.RELU]); absolute scores fit
@@ -13,8 +15,13 @@
 //     part of the F1/F2 prefix-max scans need no per-pair shuffling.  Chains are stitched per lane in scalar code
 //     (2 chains per block), lanes by Kogge-Stone over the group.
 //   * The previous row (H, E1', E2') and the query profile live in shared memory in exactly this layout: one
-//     LDS.128 / STS.128 per plane and block.  A GROUP of G lanes owns one (read, chain); lane l computes NB
-//     consecutive blocks starting at block (beg+8)/8 + l*NB, NB = 1..4 chosen per row from the band width.
+//     LDS.128 / STS.128 per plane and block.
+//   * A GROUP of G lanes owns one (read, chain).  A row is computed in SPANS of G*NB blocks (lane l: NB consecutive
+//     blocks); a warp step advances every group of the warp by one span, so a group with a narrow band moves on to
+//     its next row while a group with a wide band works on the next span of the same row — nobody computes columns
+//     it does not need.  F, the old H of the boundary column and 1-H of the boundary column are carried between
+//     spans in registers.  All 32 lanes execute every step (groups without work run it with stores disabled), so
+//     the shuffles of the step use the full mask.
 //   * Band limits inside the first / last block are applied with validity words from a small shared table
 //     (masked cells get Hhat = -inf exactly); trace rows are stored as whole blocks with 16-byte vectors, which is
 //     why word 0 of a trace row is column beg & ~7 (trace_col0, common.cuh).
@@ -35,6 +42,10 @@ static const i32 NEG16 = -32000;               // -inf of the int16 planes; reac
 static const u32 NEGP = 0x83008300u;           // NEG16 in both halves
 static const i32 PAIR_SCORE_LIMIT = 30000;
 static const int VT_WORDS = 8 * 9;             // validity table entries (uint4 each): [a = 0..7][z = 0..8]
+// abPOA's default convex gap model (rs-abPOA defaults)
+static const i32 PO1 = 4, PE1 = 2, PO2 = 24, PE2 = 1, POE1 = PO1 + PE1, POE2 = PO2 + PE2;
+#define P16(v) ((u32)(((u32)(v) & 0xffffu) * 0x10001u))           // v in both halves (compile-time)
+#define P16LH(lo, hi) ((u32)(((u32)(lo) & 0xffffu) | (((u32)(hi) & 0xffffu) << 16)))
 
 __device__ __forceinline__ i32 imax(i32 a, i32 b) { return a > b ? a : b; }
 __device__ __forceinline__ i32 imin(i32 a, i32 b) { return a < b ? a : b; }
@@ -47,25 +58,28 @@ __device__ __forceinline__ int hw_index(i32 j) {
     return (int)(((c >> 3) << 3) | ((c & 3) << 1) | ((c >> 2) & 1));
 }
 
-struct PairConst {
-    u32 ne1p, ne2p, noe1p, noe2p;      // -e1, -e2, -(o1+e1), -(o2+e2) in both halves
-    u32 o1p, o2p, o1p1, o2p1;          // o1, o2, o1+1, o2+1 in both halves
-    i32 e1, e2;
+struct SpanOut { i32 mx, lpos, rpos; };
+// carried from one span of a row to the next (group-uniform)
+struct SpanCarry {
+    i32 fc1, fc2;      // F1', F2' arriving at the first column of the span (F' = F + o + e)
+    u32 hq;            // low half: old H (previous row) of the column left of the span; high half: 1 - new H of that column
 };
-struct PairRowOut { i32 mx, lpos, rpos; };
 
 template <int G> __device__ __forceinline__ u32 pair_group_mask(u32 lane) {
     return G == 32 ? 0xffffffffu : (((1u << (G & 31)) - 1u) << (lane & ~(u32)(G - 1)));
 }
 
-// One DP row of one group.  planes = H, E1', E2' (nblk blocks each) of the group; prof = profile plane of the row's
-// graph base; vtab = validity table; tr = trace word of column beg & ~7.
+// One span (G*NB blocks) of one DP row, executed by all 32 lanes of the warp (one group each G lanes).
+// planes = H, E1', E2' (nblk blocks each) of the group; prof = profile plane of the row's graph base; vtab = validity
+// table; tr = trace word of column beg & ~7.  live = false: a group without work (no stores).
 template <int G, int NB>
-__device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 gl, i32 beg, i32 end, uint4* __restrict__ planes,
-                                                int nblk, const uint4* __restrict__ prof, const uint4* __restrict__ vtab,
-                                                u32* __restrict__ tr) {
+__device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone, bool live, bool last, SpanCarry& cy,
+                                             uint4* __restrict__ planes, int nblk, const uint4* __restrict__ prof,
+                                             const uint4* __restrict__ vtab, u32* __restrict__ tr) {
+    const u32 FULLM = 0xffffffffu;
     const i32 b0 = (beg + 8) >> 3, bend = (end + 8) >> 3;
-    const i32 bme = b0 + (i32)gl * NB;                  // the lane's first block
+    const i32 bsp = b0 + bdone;                         // first block of the span (bdone blocks of the row are computed)
+    const i32 bme = bsp + (i32)gl * NB;                 // the lane's first block
     const i32 cfirst = bme * 8 - 8;                     // and its first column
     const i32 D = beg - cfirst, Eo = end - cfirst + 1;
     uint4* const Hpl = planes;
@@ -75,6 +89,7 @@ __device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 
     u32 R1[NB], R2[NB];
     // ---- sweep 1: Hhat = max(M, E1, E2) masked to the band, chain-local part of the F scans (F' = F + o + e)
     u32 hprev = ((const u32*)(Hpl + (imin(bme, nblk - 1) - 1)))[3];
+    if (gl == 0 && bdone > 0) hprev = cy.hq << 16;         // the previous span has already overwritten that block
 #pragma unroll
     for (int k = 0; k < NB; k++) {
         const int bk = imin(bme + k, nblk - 1);         // lanes right of the band read the spare block (all their cells are masked)
@@ -96,13 +111,14 @@ __device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 
             h = (h & vw[t]) | (NEGP & ~vw[t]);
             hh[k][t] = h;
             fl1[k][t] = r1; fl2[k][t] = r2;
-            r1 = __viaddmax_s16x2(r1, K.ne1p, h);
-            r2 = __viaddmax_s16x2(r2, K.ne2p, h);
+            r1 = __viaddmax_s16x2(r1, P16(-PE1), h);
+            r2 = __viaddmax_s16x2(r2, P16(-PE2), h);
             hd = hw[t];
         }
         hprev = hv.w;
         R1[k] = r1; R2[k] = r2;
     }
+    const u32 hold_last = hprev;            // old H of the lane's last block, word 3 (its high half is the column left of the next lane)
     // ---- stitch the chains of the lane (A0, B0, A1, B1, ...), then the lanes of the group
     u32 in1[NB], in2[NB];
     i32 c1 = NEG16, c2 = NEG16;
@@ -110,24 +126,27 @@ __device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 
     for (int k = 0; k < NB; k++) {
         const i32 a1 = sext16(R1[k]), b1 = (i32)R1[k] >> 16, a2 = sext16(R2[k]), b2 = (i32)R2[k] >> 16;
         const i32 ia1 = c1, ia2 = c2;
-        c1 = __viaddmax_s32(c1, -4 * K.e1, a1); c2 = __viaddmax_s32(c2, -4 * K.e2, a2);
+        c1 = __viaddmax_s32(c1, -4 * PE1, a1); c2 = __viaddmax_s32(c2, -4 * PE2, a2);
         in1[k] = pair16(ia1, c1); in2[k] = pair16(ia2, c2);
-        c1 = __viaddmax_s32(c1, -4 * K.e1, b1); c2 = __viaddmax_s32(c2, -4 * K.e2, b2);
+        c1 = __viaddmax_s32(c1, -4 * PE1, b1); c2 = __viaddmax_s32(c2, -4 * PE2, b2);
     }
+    // what arrives from the previous spans passes through lane 0's columns
+    if (gl == 0) { c1 = __viaddmax_s32(cy.fc1, -PE1 * 8 * NB, c1); c2 = __viaddmax_s32(cy.fc2, -PE2 * 8 * NB, c2); }
 #pragma unroll
     for (int d = 1; d < G; d <<= 1) {       // shfl_up leaves lanes < d unchanged, and max(v, v - c) = v
-        const i32 t1 = __shfl_up_sync(gm, c1, d, G), t2 = __shfl_up_sync(gm, c2, d, G);
-        c1 = __viaddmax_s32(t1, -K.e1 * 8 * NB * d, c1);
-        c2 = __viaddmax_s32(t2, -K.e2 * 8 * NB * d, c2);
+        const i32 t1 = __shfl_up_sync(FULLM, c1, d, G), t2 = __shfl_up_sync(FULLM, c2, d, G);
+        c1 = __viaddmax_s32(t1, -PE1 * 8 * NB * d, c1);
+        c2 = __viaddmax_s32(t2, -PE2 * 8 * NB * d, c2);
     }
-    c1 = __shfl_up_sync(gm, c1, 1, G); c2 = __shfl_up_sync(gm, c2, 1, G);
-    if (gl == 0) { c1 = NEG16; c2 = NEG16; }
+    const i32 tot1 = c1, tot2 = c2;         // inclusive: F' arriving right of the lane's last column
+    c1 = __shfl_up_sync(FULLM, c1, 1, G); c2 = __shfl_up_sync(FULLM, c2, 1, G);
+    if (gl == 0) { c1 = cy.fc1; c2 = cy.fc2; }
     {
         const u32 c1p = both16(c1), c2p = both16(c2);
 #pragma unroll
         for (int k = 0; k < NB; k++) {
-            in1[k] = __viaddmax_s16x2(c1p, pair16(-K.e1 * 8 * k, -K.e1 * (8 * k + 4)), in1[k]);
-            in2[k] = __viaddmax_s16x2(c2p, pair16(-K.e2 * 8 * k, -K.e2 * (8 * k + 4)), in2[k]);
+            in1[k] = __viaddmax_s16x2(c1p, P16LH(-PE1 * 8 * k, -PE1 * (8 * k + 4)), in1[k]);
+            in2[k] = __viaddmax_s16x2(c2p, P16LH(-PE2 * 8 * k, -PE2 * (8 * k + 4)), in2[k]);
         }
     }
     // ---- sweep 2a: H and the running maximum
@@ -137,15 +156,21 @@ __device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 
     for (int k = 0; k < NB; k++) {
 #pragma unroll
         for (int t = 0; t < 4; t++) {
-            f1[k][t] = __viaddmax_s16x2(in1[k], both16(-K.e1 * t), fl1[k][t]);
-            f2[k][t] = __viaddmax_s16x2(in2[k], both16(-K.e2 * t), fl2[k][t]);
-            const u32 hp = __viaddmax_s16x2(f1[k][t], K.noe1p, hh[k][t]);
-            H[k][t] = __viaddmax_s16x2(f2[k][t], K.noe2p, hp);
+            f1[k][t] = __viaddmax_s16x2(in1[k], P16(-PE1 * t), fl1[k][t]);
+            f2[k][t] = __viaddmax_s16x2(in2[k], P16(-PE2 * t), fl2[k][t]);
+            const u32 hp = __viaddmax_s16x2(f1[k][t], P16(-POE1), hh[k][t]);
+            H[k][t] = __viaddmax_s16x2(f2[k][t], P16(-POE2), hp);
             mxacc = __vmaxs2(mxacc, H[k][t]);
         }
     }
-    // 1 - H of the column left of the lane's first one (F fields of pair 0 of block 0); lane 0 has none (don't care)
-    u32 qleft = __shfl_up_sync(gm, __vadd2(~H[NB - 1][3], 0x00020002u), 1, G);
+    // 1 - H of the column left of the lane's first one (F fields of pair 0 of block 0); the first column of a row has none (don't care)
+    const u32 qlast = __vadd2(~H[NB - 1][3], 0x00020002u);
+    u32 qleft = __shfl_up_sync(FULLM, qlast, 1, G);
+    if (gl == 0) qleft = cy.hq;
+    // carries for the next span: everything comes from the last lane of the group
+    cy.fc1 = __shfl_sync(FULLM, tot1, G - 1, G);
+    cy.fc2 = __shfl_sync(FULLM, tot2, G - 1, G);
+    cy.hq = __shfl_sync(FULLM, __byte_perm(hold_last, qlast, 0x7632), G - 1, G);
     // ---- sweep 2b: E', trace words, stores
 #pragma unroll
     for (int k = 0; k < NB; k++) {
@@ -157,19 +182,19 @@ __device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 
 #pragma unroll
         for (int t = 0; t < 4; t++) {
             const u32 nq = ~H[k][t];
-            const u32 u1 = __vadd2(nq, K.o1p1), u2 = __vadd2(nq, K.o2p1);           // o - H
-            const u32 d1 = __viaddmin_s16x2_relu(x1[k][t], u1, K.o1p);              // E1' - (H - oe1) in [0, o1]
-            const u32 d2 = __viaddmin_s16x2_relu(x2[k][t], u2, K.o2p);
+            const u32 u1 = __vadd2(nq, P16(PO1 + 1)), u2 = __vadd2(nq, P16(PO2 + 1));   // o - H
+            const u32 d1 = __viaddmin_s16x2_relu(x1[k][t], u1, P16(PO1));           // E1' - (H - oe1) in [0, o1]
+            const u32 d2 = __viaddmin_s16x2_relu(x2[k][t], u2, P16(PO2));
             const u32 ql = t == 0 ? ql0 : q[t - 1];
-            const u32 g1 = __viaddmin_s16x2_relu(f1[k][t], ql, K.o1p1);             // max(F1 - (Hleft - oe1), -1) + 1
-            const u32 g2 = __viaddmin_s16x2_relu(f2[k][t], ql, K.o2p1);
+            const u32 g1 = __viaddmin_s16x2_relu(f1[k][t], ql, P16(PO1 + 1));       // max(F1 - (Hleft - oe1), -1) + 1
+            const u32 g2 = __viaddmin_s16x2_relu(f2[k][t], ql, P16(PO2 + 1));
             const u32 hi = d1 + d2 * 8u + g1 * 256u + g2 * 2048u;                   // fields are bounded: no carry between halves
             wlo[t] = __byte_perm(H[k][t], hi, 0x5410);
             whi[t] = __byte_perm(H[k][t], hi, 0x7632);
-            e1n[t] = __viaddmax_s16x2(x1[k][t], K.ne1p, __vadd2(H[k][t], K.noe1p));
-            e2n[t] = __viaddmax_s16x2(x2[k][t], K.ne2p, __vadd2(H[k][t], K.noe2p));
+            e1n[t] = __viaddmax_s16x2(x1[k][t], P16(-PE1), __vadd2(H[k][t], P16(-POE1)));
+            e2n[t] = __viaddmax_s16x2(x2[k][t], P16(-PE2), __vadd2(H[k][t], P16(-POE2)));
         }
-        if (bme + k <= bend) {
+        if (live && bme + k <= bend) {
             uint4* const t4 = (uint4*)(tr + 8 * (bme + k - b0));
             t4[0] = make_uint4(wlo[0], wlo[1], wlo[2], wlo[3]);
             t4[1] = make_uint4(whi[0], whi[1], whi[2], whi[3]);
@@ -180,20 +205,20 @@ __device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 
     }
     // guards: H(beg-1) = -inf (diagonal of column beg in the next row) and E'(end+1) = -inf (vertical of column end+1).
     // A guard inside a block stored this row is written by the block's owner after its stores; other blocks are not stored.
-    if (gl == 0 && (beg & 7) == 0) ((short*)Hpl)[hw_index(beg - 1)] = (short)NEG16;
-    {
-        const i32 ow = imin((((end + 9) >> 3) - b0) / NB, G - 1);
+    if (live && bdone == 0 && gl == 0 && (beg & 7) == 0) ((short*)Hpl)[hw_index(beg - 1)] = (short)NEG16;
+    if (live && last) {
+        const i32 ow = imin((((end + 9) >> 3) - bsp) / NB, G - 1);
         if ((i32)gl == ow) {
             const int x = hw_index(end + 1);
             ((short*)E1pl)[x] = (short)NEG16;
             ((short*)E2pl)[x] = (short)NEG16;
         }
     }
-    // ---- row maximum and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i).  Masked cells are below every
-    // in-band value: left of beg they are -inf, right of end they hold an F that decays from a band cell.
+    // ---- maximum of the span and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i).  Masked cells are below
+    // every in-band value of their block: left of beg they are -inf, right of end they hold an F that decays from H(end).
     i32 mx = imax(sext16(mxacc), (i32)mxacc >> 16);
 #pragma unroll
-    for (int d = G / 2; d > 0; d >>= 1) mx = imax(mx, __shfl_xor_sync(gm, mx, d, G));
+    for (int d = G / 2; d > 0; d >>= 1) mx = imax(mx, __shfl_xor_sync(FULLM, mx, d, G));
     const u32 mxp = both16(mx);
     u32 eq = 0;
 #pragma unroll
@@ -209,18 +234,22 @@ __device__ __forceinline__ PairRowOut row_pairs(const PairConst& K, u32 gm, u32 
     u32 key = 0;                                  // (511 - leftmost) << 16 | rightmost; lanes without a maximum lose both
     if (eq) key = ((u32)(511 - (cfirst + __ffs((int)eq) - 1)) << 16) | (u32)(cfirst + 31 - __clz((int)eq));
 #pragma unroll
-    for (int d = G / 2; d > 0; d >>= 1) key = __vmaxs2(key, __shfl_xor_sync(gm, key, d, G));
-    PairRowOut o;
+    for (int d = G / 2; d > 0; d >>= 1) key = __vmaxs2(key, __shfl_xor_sync(FULLM, key, d, G));
+    SpanOut o;
     o.mx = mx;
     o.lpos = 511 - (i32)(key >> 16);
     o.rpos = (i32)(key & 0xffffu);
     return o;
 }
 
-// NBMAX = blocks per lane the row body is instantiated for (register budget); wider bands move to the next class
+enum { PH_FETCH = 0, PH_ROW = 1, PH_SPAN = 2, PH_DONE = 3 };
+
+// NBMAX: a step computes up to G*NBMAX blocks of a row; the width of a step (1..NBMAX blocks per lane) is the largest
+// any group of the warp still needs, so a warp of narrow rows runs the short body.
 template <int G, int NBMAX>
 __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex ix, PoaBuffers b, int nblk) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
+    const u32 FULLM = 0xffffffffu;
     uint4* const vtab = (uint4*)dyn_smem;
     uint4* const planes = vtab + VT_WORDS + (size_t)(threadIdx.x / G) * 8 * nblk;     // H, E1', E2', 5 profile planes
     short* const Hs = (short*)planes;
@@ -237,25 +266,24 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
         vtab[i] = make_uint4(w[0], w[1], w[2], w[3]);
     }
     __syncthreads();
-    PairConst K;
-    K.e1 = b.e1; K.e2 = b.e2;
-    K.ne1p = both16(-b.e1); K.ne2p = both16(-b.e2);
-    K.noe1p = both16(-(b.o1 + b.e1)); K.noe2p = both16(-(b.o2 + b.e2));
-    K.o1p = both16(b.o1); K.o2p = both16(b.o2); K.o1p1 = both16(b.o1 + 1); K.o2p1 = both16(b.o2 + 1);
-    const i32 oe1 = b.o1 + b.e1, oe2 = b.o2 + b.e2;
     const i32 smatch = b.match, smis = -b.mismatch;
     if (gl == 0) Hs[hw_index(-1)] = (short)NEG16;       // column -1: M(i,0) does not exist
     const int ncols = (nblk - 1) * 8;                   // columns -8 .. ncols-9 are backed by real blocks
     // ---- group-uniform state of the alignment in flight
-    bool active = false;
+    int phase = PH_FETCH;
     u32 w = 0, nb = 0, S = 0, pred_base = 0, row_base = 0, nrows = 0;
     i32 qlen = 0, wband = 0, end0 = 0;
     const u8* __restrict__ q = nullptr;
-    u32 row = 0, s = 0, o = 0, metas = 0;
-    i32 beg = 0, end = 0, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
+    u32 row = 0, s = 0, o = 0, metas = 0, meta = 0;
+    i32 beg = 0, end = -1, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
+    i32 bdone = 0, nblocks_row = 1, rl = 0, rr = 0;
     u64 cells = 0;
     u32 status = VGA_ALN_OK, custom_base = 0xffffffffu;
     u64 pool_cur = 0, pool_end = 0;                 // this group's current chunk of the trace pool (words)
+    u32* tr = b.pool;
+    const uint4* pr = planes + 3 * nblk;
+    SpanCarry cy;
+    cy.fc1 = NEG16; cy.fc2 = NEG16; cy.hq = 0;
 
     // result record of the item in flight; the group goes back to fetching
     auto finish = [&]() {
@@ -294,170 +322,194 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
             out->cells = cells;
             out->n_runs = 0; out->n_path = 0; out->path_len = 0; out->start_off = 0; out->end_off = 0; out->n_aligned = 0;
         }
-        active = false;
+        phase = PH_FETCH;
     };
 
     for (;;) {
-        if (!active) {
-            // ---- next (read, chain) of the work list
+        // ---- A: next (read, chain) of the work list (groups without an item)
+        if (phase == PH_FETCH) {
             u32 wi = 0;
             if (gl == 0) wi = atomicAdd(b.work_ctr, 1u);
             wi = __shfl_sync(gm, wi, 0, G);
-            if (wi >= b.n_items) break;
-            w = b.work[wi];
-            const AlignItem it = b.items[w];
-            qlen = (i32)it.qlen;
-            q = (const u8*)b.seqs + it.q_off;
-            wband = b.wb + (i32)(b.wf * (float)qlen);
-            nb = it.node_base; S = it.S; row_base = it.row_base; pred_base = it.pred_base; nrows = it.nrows;
-            status = VGA_ALN_OK;
-            cells = 0; row = 0; s = 0; o = 0; ppb = 0; ppe = -1; lpos = 0; rpos = 0; mxrow = 0;
-            custom_base = 0xffffffffu;
-            active = true;
-            if (S == 0 || nrows == 0) { status = VGA_ALN_EMPTY; finish(); continue; }
-            // absolute H is kept as int16 (trace words and shared memory): every DP step loses at most
-            // max(mismatch, o1+e1), so reachable scores are >= -that*(rows+qlen); other alignments go to the general kernel
-            if (qlen + 10 > ncols - 8 || (i64)imax(b.mismatch, oe1) * ((i64)nrows + qlen) > PAIR_SCORE_LIMIT) {
-                status = IT_RETRY_WIDER;
-                finish();
-                continue;
-            }
-            {   // band end of the virtual source row: max_remain of the first row + 1
-                const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
-                end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
-            }
-            // query profile: score of column j (query base j-1) against A, C, T, G (order of the 2-bit code (c >> 1) & 3)
-            __syncwarp(gm);
-            for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G) {
-                const u32 c = (j >= 1 && j <= qlen) ? q[j - 1] : 0u;
-                const int x = hw_index(j);
-                ((short*)(planes + 3 * nblk))[x] = (short)(c == 'A' ? smatch : smis);
-                ((short*)(planes + 4 * nblk))[x] = (short)(c == 'C' ? smatch : smis);
-                ((short*)(planes + 5 * nblk))[x] = (short)(c == 'T' ? smatch : smis);
-                ((short*)(planes + 6 * nblk))[x] = (short)(c == 'G' ? smatch : smis);
-            }
-            __syncwarp(gm);
-        }
-        // ---- one DP row; its record (sub_rowmeta_kernel) is fetched G rows at a time
-        if ((row & (G - 1)) == 0) metas = (row + gl < nrows) ? b.row_meta[row_base + row + gl] : 0u;
-        const u32 meta = __shfl_sync(gm, metas, row & (G - 1), G);
-        const u32 base = meta & 0xffu, kind = (meta >> 8) & 3u;
-        // predecessor row: the previous row unless this is a first row with other predecessors
-        i32 mpl = lpos + 1, mpr = rpos + 1, min_pb = ppb, max_pe = ppe;
-        u32 prow = row - 1, np = 1, po = 0;
-        if (kind == 1) { mpl = 1; mpr = 1; min_pb = 0; max_pe = end0; np = 0; prow = 0; }      // virtual source row
-        else if (kind == 2) {
-            __syncwarp(gm);       // NodeState / RowInfo / trace words of earlier rows were written by other lanes of the group
-            po = b.nd_pred_off[nb + s];
-            np = b.nd_pred_off[nb + s + 1] - po;
-            const u32* __restrict__ pl = b.nd_pred + pred_base + po;
-            mpl = INT_MAX; mpr = 0; min_pb = INT_MAX; max_pe = -1;
-            for (u32 x = 0; x < np; x++) {
-                const NodeState ns = b.nd_state[nb + pl[x]];
-                mpl = imin(mpl, ns.lpos + 1); mpr = imax(mpr, ns.rpos + 1);
-                min_pb = imin(min_pb, ns.beg); max_pe = imax(max_pe, ns.end);
-            }
-            prow = b.nd_row_start[nb + pl[0] + 1] - 1;
-        }
-        // adaptive band (abPOA GET_AD_DP_BEGIN/END + clipping to the predecessors' bands)
-        const i32 r = qlen - (i32)(meta >> 11);
-        beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
-        end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
-        const i32 W = end - beg + 1;
-        const i32 nblocks = ((end + 8) >> 3) - ((beg + 8) >> 3) + 1;
-        int cr = (nblocks + G - 1) / G;               // blocks per lane
-        if (beg > end) status = VGA_ALN_BAND_ERR;
-        else if (cr > NBMAX) status = IT_RETRY_WIDER;
-        // pool space: whole blocks, one trace word per cell
-        const u64 need = (u64)nblocks * 8;
-        if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
-            unsigned long long got = 0;
-            const u64 take = need > PAIR_POOL_CHUNK ? need : PAIR_POOL_CHUNK;
-            if (gl == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
-            got = __shfl_sync(gm, got, 0, G);
-            if (got + take > b.pool_words) status = IT_RETRY_POOL;
-            else { pool_cur = got; pool_end = got + take; }
-        }
-        if (status != VGA_ALN_OK) { finish(); continue; }
-        u32* __restrict__ tr = b.pool + pool_cur;
-        if (gl == 0) {
-            uint4* dst = (uint4*)(b.rows + row_base + row);
-            dst[0] = make_uint4((u32)beg, (u32)end, (u32)(pool_cur >> 2), 0u);
-            dst[1] = make_uint4(prow, (np < 0xffffffu ? np : 0xffffffu) | (base << 24), s, o);
-        }
-        pool_cur += need;
-        cells += (u64)W;
-        if (kind != 0) {
-            // the predecessor row is not the one in shared memory: build it there (columns beg-1 .. end+1)
-            const i32 jlo = imax(beg - 1, 0);
-            if (kind == 1) {          // virtual source row
-                __syncwarp(gm);
-                for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
-                    const bool in0 = j <= end0;
-                    const int x = hw_index(j);
-                    Hs[x] = (short)(!in0 ? NEG16 : j == 0 ? 0 : imax(-(b.o1 + b.e1 * j), -(b.o2 + b.e2 * j)));
-                    E1s[x] = (short)(j == 0 ? -oe1 : NEG16);
-                    E2s[x] = (short)(j == 0 ? -oe2 : NEG16);
-                }
-            } else {                  // merge of the predecessors' last rows, decoded from their trace words
-                const u32* __restrict__ pl = b.nd_pred + pred_base + po;
-                for (u32 x = 0; x < np; x++) {
-                    // one predecessor at a time: its band and trace row are read once, its words stream through the lanes
-                    const u32 p = pl[x];
-                    const int2 pbe = *(const int2*)(b.nd_state + nb + p);
-                    const u32* __restrict__ tw = b.pool + (u64)b.rows[row_base + b.nd_row_start[nb + p + 1] - 1].toff * 4;
-                    const i32 pc0 = trace_col0(pbe.x);
-#pragma unroll 2
-                    for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
-                        i32 hv = NEG16, e1v = NEG16, e2v = NEG16;
-                        if (j >= pbe.x && j <= pbe.y) {
-                            const u32 v = tw[j - pc0];
-                            hv = sext16(v);
-                            e1v = hv - oe1 + (i32)((v >> 16) & 7u);
-                            e2v = hv - oe2 + (i32)((v >> 19) & 31u);
-                        }
-                        const int xx = hw_index(j);
-                        if (x > 0) {
-                            hv = imax(hv, (i32)Hs[xx]); e1v = imax(e1v, (i32)E1s[xx]); e2v = imax(e2v, (i32)E2s[xx]);
-                        }
-                        Hs[xx] = (short)hv; E1s[xx] = (short)e1v; E2s[xx] = (short)e2v;
+            if (wi >= b.n_items) phase = PH_DONE;
+            else {
+                w = b.work[wi];
+                const AlignItem it = b.items[w];
+                qlen = (i32)it.qlen;
+                q = (const u8*)b.seqs + it.q_off;
+                wband = b.wb + (i32)(b.wf * (float)qlen);
+                nb = it.node_base; S = it.S; row_base = it.row_base; pred_base = it.pred_base; nrows = it.nrows;
+                status = VGA_ALN_OK;
+                cells = 0; row = 0; s = 0; o = 0; ppb = 0; ppe = -1; lpos = 0; rpos = 0; mxrow = 0;
+                custom_base = 0xffffffffu;
+                phase = PH_ROW;
+                if (S == 0 || nrows == 0) { status = VGA_ALN_EMPTY; finish(); }
+                // absolute H is kept as int16 (trace words and shared memory): every DP step loses at most
+                // max(mismatch, o1+e1), so reachable scores are >= -that*(rows+qlen); other alignments go to the general kernel
+                else if (qlen + 10 > ncols - 8 || (i64)imax(b.mismatch, POE1) * ((i64)nrows + qlen) > PAIR_SCORE_LIMIT) {
+                    status = IT_RETRY_WIDER;
+                    finish();
+                } else {
+                    {   // band end of the virtual source row: max_remain of the first row + 1
+                        const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
+                        end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+                    }
+                    // query profile: score of column j (query base j-1) against A, C, T, G (order of the 2-bit code (c >> 1) & 3)
+                    __syncwarp(gm);
+                    for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G) {
+                        const u32 c = (j >= 1 && j <= qlen) ? q[j - 1] : 0u;
+                        const int x = hw_index(j);
+                        ((short*)(planes + 3 * nblk))[x] = (short)(c == 'A' ? smatch : smis);
+                        ((short*)(planes + 4 * nblk))[x] = (short)(c == 'C' ? smatch : smis);
+                        ((short*)(planes + 5 * nblk))[x] = (short)(c == 'T' ? smatch : smis);
+                        ((short*)(planes + 6 * nblk))[x] = (short)(c == 'G' ? smatch : smis);
                     }
                 }
             }
         }
-        // substitution profile row of this graph base
-        u32 code = (base >> 1) & 3u;
-        if (base != ((0x47544341u >> (8 * code)) & 0xffu)) {          // not A, C, T, G: custom row
-            code = 4;
-            if (base != custom_base) {
-                __syncwarp(gm);
-                for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G)
-                    ((short*)(planes + 7 * nblk))[hw_index(j)] = (short)((j >= 1 && j <= qlen && q[j - 1] == base) ? smatch : smis);
-                custom_base = base;
+        // ---- B: row prologue (groups that start a DP row); row records (sub_rowmeta_kernel) are fetched G rows at a time
+        if (phase == PH_ROW && (row & (G - 1)) == 0) metas = (row + gl < nrows) ? b.row_meta[row_base + row + gl] : 0u;
+        {
+            const u32 mt = __shfl_sync(FULLM, metas, row & (G - 1), G);
+            if (phase == PH_ROW) meta = mt;
+        }
+        if (phase == PH_ROW) {
+            const u32 base = meta & 0xffu, kind = (meta >> 8) & 3u;
+            // predecessor row: the previous row unless this is a first row with other predecessors
+            i32 mpl = lpos + 1, mpr = rpos + 1, min_pb = ppb, max_pe = ppe;
+            u32 prow = row - 1, np = 1, po = 0;
+            if (kind == 1) { mpl = 1; mpr = 1; min_pb = 0; max_pe = end0; np = 0; prow = 0; }      // virtual source row
+            else if (kind == 2) {
+                __syncwarp(gm);       // NodeState / RowInfo / trace words of earlier rows were written by other lanes of the group
+                po = b.nd_pred_off[nb + s];
+                np = b.nd_pred_off[nb + s + 1] - po;
+                const u32* __restrict__ pl = b.nd_pred + pred_base + po;
+                mpl = INT_MAX; mpr = 0; min_pb = INT_MAX; max_pe = -1;
+                for (u32 x = 0; x < np; x++) {
+                    const NodeState ns = b.nd_state[nb + pl[x]];
+                    mpl = imin(mpl, ns.lpos + 1); mpr = imax(mpr, ns.rpos + 1);
+                    min_pb = imin(min_pb, ns.beg); max_pe = imax(max_pe, ns.end);
+                }
+                prow = b.nd_row_start[nb + pl[0] + 1] - 1;
+            }
+            // adaptive band (abPOA GET_AD_DP_BEGIN/END + clipping to the predecessors' bands)
+            const i32 r = qlen - (i32)(meta >> 11);
+            beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
+            end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
+            const i32 W = end - beg + 1;
+            const i32 nblocks = ((end + 8) >> 3) - ((beg + 8) >> 3) + 1;
+            if (beg > end) status = VGA_ALN_BAND_ERR;
+            // pool space: whole blocks, one trace word per cell
+            const u64 need = (u64)nblocks * 8;
+            if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
+                unsigned long long got = 0;
+                const u64 take = need > PAIR_POOL_CHUNK ? need : PAIR_POOL_CHUNK;
+                if (gl == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
+                got = __shfl_sync(gm, got, 0, G);
+                if (got + take > b.pool_words) status = IT_RETRY_POOL;
+                else { pool_cur = got; pool_end = got + take; }
+            }
+            if (status != VGA_ALN_OK) finish();
+            else {
+                tr = b.pool + pool_cur;
+                if (gl == 0) {
+                    uint4* dst = (uint4*)(b.rows + row_base + row);
+                    dst[0] = make_uint4((u32)beg, (u32)end, (u32)(pool_cur >> 2), 0u);
+                    dst[1] = make_uint4(prow, (np < 0xffffffu ? np : 0xffffffu) | (base << 24), s, o);
+                }
+                pool_cur += need;
+                cells += (u64)W;
+                if (kind != 0) {
+                    // the predecessor row is not the one in shared memory: build it there (columns beg-1 .. end+1)
+                    const i32 jlo = imax(beg - 1, 0);
+                    if (kind == 1) {          // virtual source row
+                        __syncwarp(gm);
+                        for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
+                            const bool in0 = j <= end0;
+                            const int x = hw_index(j);
+                            Hs[x] = (short)(!in0 ? NEG16 : j == 0 ? 0 : imax(-(PO1 + PE1 * j), -(PO2 + PE2 * j)));
+                            E1s[x] = (short)(j == 0 ? -POE1 : NEG16);
+                            E2s[x] = (short)(j == 0 ? -POE2 : NEG16);
+                        }
+                    } else {                  // merge of the predecessors' last rows, decoded from their trace words
+                        const u32* __restrict__ pl = b.nd_pred + pred_base + po;
+                        for (u32 x = 0; x < np; x++) {
+                            // one predecessor at a time: its band and trace row are read once, its words stream through the lanes
+                            const u32 p = pl[x];
+                            const int2 pbe = *(const int2*)(b.nd_state + nb + p);
+                            const u32* __restrict__ tw = b.pool + (u64)b.rows[row_base + b.nd_row_start[nb + p + 1] - 1].toff * 4;
+                            const i32 pc0 = trace_col0(pbe.x);
+#pragma unroll 2
+                            for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
+                                i32 hv = NEG16, e1v = NEG16, e2v = NEG16;
+                                if (j >= pbe.x && j <= pbe.y) {
+                                    const u32 v = tw[j - pc0];
+                                    hv = sext16(v);
+                                    e1v = hv - POE1 + (i32)((v >> 16) & 7u);
+                                    e2v = hv - POE2 + (i32)((v >> 19) & 31u);
+                                }
+                                const int xx = hw_index(j);
+                                if (x > 0) {
+                                    hv = imax(hv, (i32)Hs[xx]); e1v = imax(e1v, (i32)E1s[xx]); e2v = imax(e2v, (i32)E2s[xx]);
+                                }
+                                Hs[xx] = (short)hv; E1s[xx] = (short)e1v; E2s[xx] = (short)e2v;
+                            }
+                        }
+                    }
+                }
+                // substitution profile row of this graph base
+                u32 code = (base >> 1) & 3u;
+                if (base != ((0x47544341u >> (8 * code)) & 0xffu)) {          // not A, C, T, G: custom row
+                    code = 4;
+                    if (base != custom_base) {
+                        __syncwarp(gm);
+                        for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G)
+                            ((short*)(planes + 7 * nblk))[hw_index(j)] = (short)((j >= 1 && j <= qlen && q[j - 1] == base) ? smatch : smis);
+                        custom_base = base;
+                    }
+                }
+                pr = planes + (3 + code) * nblk;
+                bdone = 0;
+                nblocks_row = nblocks;
+                cy.fc1 = NEG16; cy.fc2 = NEG16; cy.hq = 0;
+                phase = PH_SPAN;
             }
         }
-        __syncwarp(gm);
-        const uint4* pr = planes + (3 + code) * nblk;
-        // the groups of the warp that are here together agree on the largest block count among them (stay converged)
-        cr = __reduce_max_sync(__activemask(), cr);
-        PairRowOut ro;
-        if (cr == 1) ro = row_pairs<G, 1>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
-        else if (NBMAX >= 3 && cr == 2) ro = row_pairs<G, (NBMAX >= 3 ? 2 : 1)>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
-        else if (NBMAX >= 4 && cr == 3) ro = row_pairs<G, (NBMAX >= 4 ? 3 : 1)>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
-        else ro = row_pairs<G, NBMAX>(K, gm, gl, beg, end, planes, nblk, pr, vtab, tr);
-        lpos = ro.lpos; rpos = ro.rpos; mxrow = ro.mx;
-        ppb = beg; ppe = end;
-        if (meta & 0x400u) {
-            // last row of its node: it may be a predecessor of later nodes' first rows
-            if (gl == 0) {
-                int4* dst = (int4*)(b.nd_state + nb + s);
-                dst[0] = make_int4(beg, end, lpos, rpos);
-                dst[1] = make_int4(mxrow, 0, 0, 0);
+        // ---- C: one span of every group's row; all 32 lanes take part (groups without a row run it with stores disabled)
+        __syncwarp();
+        if (__all_sync(FULLM, phase == PH_DONE)) break;
+        const bool live = phase == PH_SPAN;
+        const i32 left = live ? nblocks_row - bdone : 0;
+        const int nbw = __reduce_max_sync(FULLM, (u32)imin((left + G - 1) / G, NBMAX));     // blocks per lane of this step
+        SpanOut so;
+        if (NBMAX >= 3 && nbw == 3)
+            so = span_step<G, (NBMAX >= 3 ? 3 : 1)>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 3, cy, planes, nblk, pr, vtab, tr);
+        else if (NBMAX >= 2 && nbw == 2)
+            so = span_step<G, (NBMAX >= 2 ? 2 : 1)>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 2, cy, planes, nblk, pr, vtab, tr);
+        else
+            so = span_step<G, 1>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G, cy, planes, nblk, pr, vtab, tr);
+        // ---- D: row epilogue
+        if (live) {
+            if (bdone == 0 || so.mx > mxrow) { mxrow = so.mx; rl = so.lpos; rr = so.rpos; }
+            else if (so.mx == mxrow) rr = so.rpos;
+            bdone += G * nbw;
+            if (bdone >= nblocks_row) {
+                lpos = rl; rpos = rr;
+                ppb = beg; ppe = end;
+                if (meta & 0x400u) {
+                    // last row of its node: it may be a predecessor of later nodes' first rows
+                    if (gl == 0) {
+                        int4* dst = (int4*)(b.nd_state + nb + s);
+                        dst[0] = make_int4(beg, end, lpos, rpos);
+                        dst[1] = make_int4(mxrow, 0, 0, 0);
+                    }
+                    s++; o = 0;
+                } else o++;
+                row++;
+                phase = PH_ROW;
+                if (row == nrows) finish();
             }
-            s++; o = 0;
-        } else o++;
-        row++;
-        if (row == nrows) finish();
+        }
     }
 }
 
@@ -482,19 +534,22 @@ static void launch_pair(const DevIndex& ix, const PoaBuffers& b, int n_sms, cuda
     poa_fill_pair_kernel<G, NBMAX><<<(unsigned)ctas, PP_WARPS * 32, smem_bytes, st>>>(ix, b, nblk);
 }
 
-// pair classes: 0 = 4 lanes per alignment (bands up to 12 blocks of 8 columns), 1 = 8 lanes (up to 24 blocks: every band of a read < 178)
+// pair classes: 0 = 4 lanes, 1 = 8 lanes per alignment; both with steps of up to 3 blocks per lane
 int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st) {
     if (b.n_items == 0) return 0;
+    static const int nbmax = getenv("VGA_POA_NBMAX") ? atoi(getenv("VGA_POA_NBMAX")) : 3;     // A/B measurements
     if (cls == 0) launch_pair<4, 3>(ix, b, n_sms, st);
+    else if (nbmax == 1) launch_pair<8, 1>(ix, b, n_sms, st);
+    else if (nbmax == 2) launch_pair<8, 2>(ix, b, n_sms, st);
     else launch_pair<8, 3>(ix, b, n_sms, st);
     return 1;
 }
 
-// the 16x2 kernel's field arithmetic assumes the default-sized gap model (decays and constants stay inside int16)
+// the 16x2 kernel is compiled for abPOA's default gap model; match / mismatch come in through the query profile
 bool poa_pair_ok(i64 qlen, i64 nrows, const VgaParams& P) {
-    const i64 step = P.mismatch > P.o1 + P.e1 ? P.mismatch : P.o1 + P.e1;
-    return qlen < 246 && step * (nrows + qlen) <= PAIR_SCORE_LIMIT && P.e1 >= 1 && P.e1 <= 2 && P.e2 >= 1 && P.e2 <= 2 &&
-           P.o1 >= 0 && P.o1 <= 6 && P.o2 >= 0 && P.o2 <= 30 && P.match >= 0 && P.match <= 64 && P.mismatch >= 0 && P.mismatch <= 64;
+    const i64 step = P.mismatch > POE1 ? P.mismatch : POE1;
+    return qlen < 246 && step * (nrows + qlen) <= PAIR_SCORE_LIMIT && P.o1 == PO1 && P.e1 == PE1 && P.o2 == PO2 && P.e2 == PE2 &&
+           P.match >= 0 && P.match <= 64 && P.mismatch >= 0 && P.mismatch <= 64;
 }
 
 }  // namespace vga
