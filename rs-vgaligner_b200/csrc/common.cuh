@@ -57,7 +57,7 @@ struct IndexHeader {
     u64 off_pos_te;     // u32[n_pos]      KmerPos.end.position
     u64 pad[8];
 };
-static const u64 INDEX_MAGIC = 0x3158444947414756ull;  // "VGAGIDX1"
+static const u64 INDEX_MAGIC = 0x3258444947414756ull;  // "VGAGIDX2" (slot keys in bit-plane form)
 
 struct DevIndex {       // resolved device pointers, passed to kernels by value
     u32 k, n_nodes, n_edges, L;
@@ -73,6 +73,18 @@ struct DevIndex {       // resolved device pointers, passed to kernels by value
     const u32* pos_te;
 };
 
+// Slot keys are stored in BIT-PLANE form: bit t of the low word = bit 0 of the 2-bit code (A0 C1 G2 T3) of base t of
+// the k-mer (t = 0 is the first base), bit t of the high word = bit 1.  The seeding kernel gets both words of a
+// query k-mer from two warp ballots and a funnel shift, without packing bases one by one.
+__host__ __device__ static inline u64 kmer_planes_from_2bit(u64 key2bit, u32 k) {
+    u64 lo = 0, hi = 0;
+    for (u32 t = 0; t < k; t++) {
+        const u64 c = (key2bit >> (2 * (k - 1 - t))) & 3u;     // first base is the most significant pair (VgaIndexView.key_kmer2bit)
+        lo |= (c & 1u) << t;
+        hi |= (c >> 1) << t;
+    }
+    return (hi << 32) | lo;
+}
 __host__ __device__ static inline u64 kmer_slot_hash(u64 key) {
     key *= 0x9E3779B97F4A7C15ull;
     key ^= key >> 29;

@@ -102,9 +102,10 @@ struct PoaBuffers {
     u32* pool; u64 pool_words; unsigned long long* pool_ctr;
     u32* work_ctr;
     i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
+    i32 nb_hint;             // pair kernel: blocks per lane and step worth instantiating (2 or 3), from rows per query base
     i32 qmax_short;          // longest read among the items of the short-read classes (sizes the pair kernel's shared memory)
 };
-// kernel classes: 0..1 = short reads on the 16x2 kernel, 4 / 8 lanes per alignment (k_poa_pair.cu); 2 = short reads, 32 lanes
+// kernel classes: 0..1 = short reads on the 16x2 kernel (k_poa_pair.cu; 1 = with the per-row range check); 2 = short reads, 32 lanes
 // (k_poa_short.cu); 3..5 = SLIDE C=8,16,32 (k_poa.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
 int poa_class_count();
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P);
@@ -113,6 +114,7 @@ int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms,
 int launch_poa_fill_short(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 bool poa_short_ok(i64 qlen, i64 nrows, const VgaParams& P);   // read short enough and scores within int16
 int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);   // k_poa_pair.cu
+bool poa_pair_checked_ok(i64 qlen, i64 nrows, const VgaParams& P);   // same, scores checked per row instead of bounded a priori
 bool poa_pair_ok(i64 qlen, i64 nrows, const VgaParams& P);    // 16x2 kernel: short read, int16 scores, default-sized gap model
 
 struct TraceBuffers {

@@ -42,6 +42,16 @@ __device__ __forceinline__ i32 score_pair(u32 qb_a, u32 tb_a, u32 te_a, double f
     return __double2int_rn(round(x));                                 // f64::round: half away from zero
 }
 
+// r / 1000.0 correctly rounded, for an integer score r, without the division subroutine on the DP's critical path:
+// q0 = RN(r * RN(1/1000)), one FMA for the exact remainder, one FMA for the correction.  Equal to the IEEE quotient for
+// EVERY r in [-1e6, 2^31) — checked exhaustively on the host (tests/test_host.py::test_div1000_identity runs a stride of it).
+__device__ __forceinline__ double div1000(i32 r) {
+    const double a = (double)r;
+    const double q0 = __dmul_rn(a, 0.001);
+    const double rem = __fma_rn(-1000.0, q0, a);
+    return __fma_rn(rem, 0.001, q0);
+}
+
 // One warp per read.  FUSED: reads with at most CHAIN_SMAX anchors — the stable sort by
 // target_end.position (src/chain.rs:386-389) is a bitonic sort of (te, id) keys in shared memory,
 // and the integer scores / predecessor distances of the whole read stay in shared memory for the
@@ -122,7 +132,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
             i32 p = -1;
             if (m > rk) { r_i = m; p = (i32)(i - dmin); }                // :430-443 strict >
             if (m > r_max) r_max = m;                                    // :445-447 (all proposals)
-            const double f_i = __ddiv_rn((double)r_i, 1000.0);           // :360-363
+            const double f_i = div1000(r_i);                                 // :360-363
             if (lane == 0) {
                 rf[si] = f_i;
                 b.f[base + i] = f_i;
@@ -137,7 +147,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
             u32* creg = b.cmem + 2ull * base + 2ull * r;
             u32* cl = b.clen + base + r;
             u32 n_ch = 0, tail = 0;
-            const double curr_max = __ddiv_rn((double)r_max, 1000.0);
+            const double curr_max = div1000(r_max);
             for (u32 i = n; i-- > 0;) {
                 const bool cand = FUSED ? (pd[i] != 0 && rr[i] == r_max)
                                         : (b.pred[base + i] >= 0 && b.f[base + i] == curr_max);     // :469

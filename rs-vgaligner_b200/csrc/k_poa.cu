@@ -508,18 +508,20 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     itp->start_off = start_off; itp->end_off = end_off;
 }
 
-// classes: 0..1 = short reads on the 16x2 kernel with 4 / 8 lanes per alignment (k_poa_pair.cu: qlen < 246, int16 absolute
-// scores, bands up to 16 / 32 blocks of 8 columns), 2 = short reads with 32 lanes (k_poa_short.cu, any read < 256),
-// 3..5 = SLIDE C = 8, 16, 32 (bands up to 256 / 512 / 1024 columns).  An item that does not fit its class moves to the next.
+// classes: 0 = short reads on the 16x2 kernel (k_poa_pair.cu: qlen < 246, default gap model, int16 absolute scores bounded
+// by the row count), 1 = the same kernel with a per-row range check for longer subgraphs, 2 = short reads with 32 lanes
+// (k_poa_short.cu, any gap model, reads < 256), 3..5 = SLIDE C = 8, 16, 32 (bands up to 256 / 512 / 1024 columns).
+// An item that does not fit its class moves to the next.
 // VGA_POA_PAIR=0 restores the 8 / 16 / 32-lane kernels of k_poa_short.cu on classes 0..2 (A/B measurements).
 static int g_pair = getenv("VGA_POA_PAIR") ? atoi(getenv("VGA_POA_PAIR")) : 1;
-// alignments start on the 4-lane instance when VGA_POA_G4 is set (default: 8 lanes)
-static int g_pair_g4 = getenv("VGA_POA_G4") ? atoi(getenv("VGA_POA_G4")) : 0;
+// off by default: measured slower than the SLIDE kernel on the few very long subgraphs of 17-DRB1-3123-smooth (one 8-lane group per item is a longer critical path than one warp per item)
+static int g_pair_chk = getenv("VGA_POA_CHK") ? atoi(getenv("VGA_POA_CHK")) : 0;
 static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
 int poa_class_count() { return 6; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
     if (g_pair) {
-        if (poa_pair_ok(qlen, nrows, P)) return g_pair_g4 ? 0 : 1;
+        if (poa_pair_ok(qlen, nrows, P)) return 0;
+        if (g_pair_chk && poa_pair_checked_ok(qlen, nrows, P)) return 1;
         if (poa_short_ok(qlen, nrows, P)) return 2;
     } else if (poa_short_ok(qlen, nrows, P)) return west <= (i64)g_short_w8 ? 0 : west <= 160 ? 1 : 2;
     if (west <= 256 - 8) return 3;

@@ -58,7 +58,7 @@ __device__ __forceinline__ int hw_index(i32 j) {
     return (int)(((c >> 3) << 3) | ((c & 3) << 1) | ((c >> 2) & 1));
 }
 
-struct SpanOut { i32 mx, lpos, rpos; };
+struct SpanOut { i32 mx, lpos, rpos, mn; };   // mn: smallest Hhat of a band cell (CHK instances only)
 // carried from one span of a row to the next (group-uniform)
 struct SpanCarry {
     i32 fc1, fc2;      // F1', F2' arriving at the first column of the span (F' = F + o + e)
@@ -72,7 +72,9 @@ template <int G> __device__ __forceinline__ u32 pair_group_mask(u32 lane) {
 // One span (G*NB blocks) of one DP row, executed by all 32 lanes of the warp (one group each G lanes).
 // planes = H, E1', E2' (nblk blocks each) of the group; prof = profile plane of the row's graph base; vtab = validity
 // table; tr = trace word of column beg & ~7.  live = false: a group without work (no stores).
-template <int G, int NB>
+// CHK: also return the smallest in-band Hhat of the span (Hhat <= H, so it bounds H from below) — for alignments whose
+// row count does not prove a priori that every reachable score fits the int16 planes.
+template <int G, int NB, bool CHK>
 __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone, bool live, bool last, SpanCarry& cy,
                                              uint4* __restrict__ planes, int nblk, const uint4* __restrict__ prof,
                                              const uint4* __restrict__ vtab, u32* __restrict__ tr) {
@@ -87,6 +89,7 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
     uint4* const E2pl = planes + 2 * nblk;
     u32 hh[NB][4], fl1[NB][4], fl2[NB][4], x1[NB][4], x2[NB][4];
     u32 R1[NB], R2[NB];
+    u32 mnacc = 0x7fff7fffu;
     // ---- sweep 1: Hhat = max(M, E1, E2) masked to the band, chain-local part of the F scans (F' = F + o + e)
     u32 hprev = ((const u32*)(Hpl + (imin(bme, nblk - 1) - 1)))[3];
     if (gl == 0 && bdone > 0) hprev = cy.hq << 16;         // the previous span has already overwritten that block
@@ -108,6 +111,7 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
         for (int t = 0; t < 4; t++) {
             const u32 m = __vadd2(hd, pw[t]);
             u32 h = __vimax3_s16x2(m, x1[k][t], x2[k][t]);
+            if (CHK) mnacc = __vmins2(mnacc, (h & vw[t]) | (0x7fff7fffu & ~vw[t]));
             h = (h & vw[t]) | (NEGP & ~vw[t]);
             hh[k][t] = h;
             fl1[k][t] = r1; fl2[k][t] = r2;
@@ -236,6 +240,13 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
 #pragma unroll
     for (int d = G / 2; d > 0; d >>= 1) key = __vmaxs2(key, __shfl_xor_sync(FULLM, key, d, G));
     SpanOut o;
+    o.mn = 0;
+    if (CHK) {
+        i32 mn = imin(sext16(mnacc), (i32)mnacc >> 16);
+#pragma unroll
+        for (int d = G / 2; d > 0; d >>= 1) mn = imin(mn, __shfl_xor_sync(FULLM, mn, d, G));
+        o.mn = mn;
+    }
     o.mx = mx;
     o.lpos = 511 - (i32)(key >> 16);
     o.rpos = (i32)(key & 0xffffu);
@@ -246,8 +257,8 @@ enum { PH_FETCH = 0, PH_ROW = 1, PH_SPAN = 2, PH_DONE = 3 };
 
 // NBMAX: a step computes up to G*NBMAX blocks of a row; the width of a step (1..NBMAX blocks per lane) is the largest
 // any group of the warp still needs, so a warp of narrow rows runs the short body.
-template <int G, int NBMAX>
-__global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex ix, PoaBuffers b, int nblk) {
+template <int G, int NBMAX, int MINB, bool CHK>
+__global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevIndex ix, PoaBuffers b, int nblk) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     const u32 FULLM = 0xffffffffu;
     uint4* const vtab = (uint4*)dyn_smem;
@@ -274,7 +285,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
     u32 w = 0, nb = 0, S = 0, pred_base = 0, row_base = 0, nrows = 0;
     i32 qlen = 0, wband = 0, end0 = 0;
     const u8* __restrict__ q = nullptr;
-    u32 row = 0, s = 0, o = 0, metas = 0, meta = 0;
+    u32 row = 0, s = 0, o = 0, metas = 0, metas_next = 0, meta = 0;
     i32 beg = 0, end = -1, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
     i32 bdone = 0, nblocks_row = 1, rl = 0, rr = 0;
     u64 cells = 0;
@@ -346,7 +357,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
                 if (S == 0 || nrows == 0) { status = VGA_ALN_EMPTY; finish(); }
                 // absolute H is kept as int16 (trace words and shared memory): every DP step loses at most
                 // max(mismatch, o1+e1), so reachable scores are >= -that*(rows+qlen); other alignments go to the general kernel
-                else if (qlen + 10 > ncols - 8 || (i64)imax(b.mismatch, POE1) * ((i64)nrows + qlen) > PAIR_SCORE_LIMIT) {
+                else if (qlen + 2 > ncols - 8 || (!CHK && (i64)imax(b.mismatch, POE1) * ((i64)nrows + qlen) > PAIR_SCORE_LIMIT)) {
                     status = IT_RETRY_WIDER;
                     finish();
                 } else {
@@ -368,7 +379,11 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
             }
         }
         // ---- B: row prologue (groups that start a DP row); row records (sub_rowmeta_kernel) are fetched G rows at a time
-        if (phase == PH_ROW && (row & (G - 1)) == 0) metas = (row + gl < nrows) ? b.row_meta[row_base + row + gl] : 0u;
+        // (the batch after the current one is already in flight, so its latency is not on the row's critical path)
+        if (phase == PH_ROW && (row & (G - 1)) == 0) {
+            metas = row == 0 ? ((gl < nrows) ? b.row_meta[row_base + gl] : 0u) : metas_next;
+            metas_next = (row + G + gl < nrows) ? b.row_meta[row_base + row + G + gl] : 0u;
+        }
         {
             const u32 mt = __shfl_sync(FULLM, metas, row & (G - 1), G);
             if (phase == PH_ROW) meta = mt;
@@ -437,7 +452,8 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
                             // one predecessor at a time: its band and trace row are read once, its words stream through the lanes
                             const u32 p = pl[x];
                             const int2 pbe = *(const int2*)(b.nd_state + nb + p);
-                            const u32* __restrict__ tw = b.pool + (u64)b.rows[row_base + b.nd_row_start[nb + p + 1] - 1].toff * 4;
+                            // this kernel keeps the trace offset of a node's last row in NodeState.pad0 (one dependent load less)
+                            const u32* __restrict__ tw = b.pool + (u64)(u32)b.nd_state[nb + p].pad0 * 4;
                             const i32 pc0 = trace_col0(pbe.x);
 #pragma unroll 2
                             for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
@@ -483,13 +499,17 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
         const int nbw = __reduce_max_sync(FULLM, (u32)imin((left + G - 1) / G, NBMAX));     // blocks per lane of this step
         SpanOut so;
         if (NBMAX >= 3 && nbw == 3)
-            so = span_step<G, (NBMAX >= 3 ? 3 : 1)>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 3, cy, planes, nblk, pr, vtab, tr);
+            so = span_step<G, (NBMAX >= 3 ? 3 : 1), CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 3, cy, planes, nblk, pr, vtab, tr);
         else if (NBMAX >= 2 && nbw == 2)
-            so = span_step<G, (NBMAX >= 2 ? 2 : 1)>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 2, cy, planes, nblk, pr, vtab, tr);
+            so = span_step<G, (NBMAX >= 2 ? 2 : 1), CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 2, cy, planes, nblk, pr, vtab, tr);
         else
-            so = span_step<G, 1>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G, cy, planes, nblk, pr, vtab, tr);
+            so = span_step<G, 1, CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G, cy, planes, nblk, pr, vtab, tr);
         // ---- D: row epilogue
         if (live) {
+            // a band cell below the int16 range of this class: the alignment is redone by the 32-bit kernel
+            if (CHK && so.mn < -PAIR_SCORE_LIMIT) { status = IT_RETRY_WIDER; finish(); }
+        }
+        if (phase == PH_SPAN) {
             if (bdone == 0 || so.mx > mxrow) { mxrow = so.mx; rl = so.lpos; rr = so.rpos; }
             else if (so.mx == mxrow) rr = so.rpos;
             bdone += G * nbw;
@@ -501,7 +521,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
                     if (gl == 0) {
                         int4* dst = (int4*)(b.nd_state + nb + s);
                         dst[0] = make_int4(beg, end, lpos, rpos);
-                        dst[1] = make_int4(mxrow, 0, 0, 0);
+                        dst[1] = make_int4(mxrow, (i32)(u32)((u64)(tr - b.pool) >> 2), 0, 0);
                     }
                     s++; o = 0;
                 } else o++;
@@ -513,39 +533,47 @@ __global__ void __launch_bounds__(PP_WARPS * 32) poa_fill_pair_kernel(DevIndex i
     }
 }
 
-template <int G, int NBMAX>
+template <int G, int NBMAX, int MINB, bool CHK>
 static void launch_pair(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
     int per_sm = 0;
     const int groups_per_cta = PP_WARPS * 32 / G;
     int qmax = b.qmax_short < 16 ? 16 : b.qmax_short > 255 ? 255 : b.qmax_short;
-    const int nblk = ((qmax + 9) >> 3) + 3;         // columns -8 .. qmax+1 (+ slack), plus the spare block
+    const int nblk = ((qmax + 9) >> 3) + 2;         // columns -8 .. qmax+1, plus the spare block
     const size_t smem_bytes = ((size_t)VT_WORDS + (size_t)groups_per_cta * 8 * nblk) * sizeof(uint4);
     static size_t attr_bytes = 0;
     if (smem_bytes > attr_bytes) {
-        VGA_CUDA(cudaFuncSetAttribute(poa_fill_pair_kernel<G, NBMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        VGA_CUDA(cudaFuncSetAttribute(poa_fill_pair_kernel<G, NBMAX, MINB, CHK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
         attr_bytes = smem_bytes;
     }
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, poa_fill_pair_kernel<G, NBMAX>, PP_WARPS * 32, smem_bytes);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, poa_fill_pair_kernel<G, NBMAX, MINB, CHK>, PP_WARPS * 32, smem_bytes);
     if (per_sm < 1) per_sm = 1;
     long long ctas = (long long)n_sms * per_sm;
     const long long need = ((long long)b.n_items + groups_per_cta - 1) / groups_per_cta;
     if (ctas > need) ctas = need;
     if (ctas < 1) ctas = 1;
-    poa_fill_pair_kernel<G, NBMAX><<<(unsigned)ctas, PP_WARPS * 32, smem_bytes, st>>>(ix, b, nblk);
+    poa_fill_pair_kernel<G, NBMAX, MINB, CHK><<<(unsigned)ctas, PP_WARPS * 32, smem_bytes, st>>>(ix, b, nblk);
 }
 
-// pair classes: 0 = 4 lanes, 1 = 8 lanes per alignment; both with steps of up to 3 blocks per lane
+// pair classes: 0 = alignments whose row count bounds every reachable score inside int16 (poa_pair_ok), 1 = longer
+// subgraphs, same kernel with the per-row range check (poa_pair_checked_ok).  8 lanes per alignment, steps of up to
+// nb_hint blocks per lane.
 int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st) {
     if (b.n_items == 0) return 0;
-    static const int nbmax = getenv("VGA_POA_NBMAX") ? atoi(getenv("VGA_POA_NBMAX")) : 3;     // A/B measurements
-    if (cls == 0) launch_pair<4, 3>(ix, b, n_sms, st);
-    else if (nbmax == 1) launch_pair<8, 1>(ix, b, n_sms, st);
-    else if (nbmax == 2) launch_pair<8, 2>(ix, b, n_sms, st);
-    else launch_pair<8, 3>(ix, b, n_sms, st);
+    static const int nbenv = getenv("VGA_POA_NBMAX") ? atoi(getenv("VGA_POA_NBMAX")) : 0;     // A/B measurements
+    const int nbmax = nbenv ? nbenv : b.nb_hint;
+    if (cls == 1) { if (nbmax <= 2) launch_pair<8, 2, 4, true>(ix, b, n_sms, st); else launch_pair<8, 3, 4, true>(ix, b, n_sms, st); }
+    else if (nbmax == 1) launch_pair<8, 1, 4, false>(ix, b, n_sms, st);
+    else if (nbmax == 2) launch_pair<8, 2, 4, false>(ix, b, n_sms, st);
+    else launch_pair<8, 3, 4, false>(ix, b, n_sms, st);
     return 1;
 }
 
 // the 16x2 kernel is compiled for abPOA's default gap model; match / mismatch come in through the query profile
+bool poa_pair_checked_ok(i64 qlen, i64 nrows, const VgaParams& P) {
+    (void)nrows;
+    return qlen < 246 && P.o1 == PO1 && P.e1 == PE1 && P.o2 == PO2 && P.e2 == PE2 &&
+           P.match >= 0 && P.match <= 64 && P.mismatch >= 0 && P.mismatch <= 64;
+}
 bool poa_pair_ok(i64 qlen, i64 nrows, const VgaParams& P) {
     const i64 step = P.mismatch > POE1 ? P.mismatch : POE1;
     return qlen < 246 && step * (nrows + qlen) <= PAIR_SCORE_LIMIT && P.o1 == PO1 && P.e1 == PE1 && P.o2 == PO2 && P.e2 == PE2 &&

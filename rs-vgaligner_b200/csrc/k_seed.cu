@@ -31,45 +31,54 @@ __device__ __forceinline__ u32 base_code(u32 c) {
     return ok ? x : 4u;
 }
 
+// A warp owns a read.  Each lane classifies ONE read byte per 32-position chunk; three ballots give the bit planes of
+// the 2-bit codes (and of the non-ACGT / past-the-end flag) for 32 positions, and the k-mer starting at position
+// i0+lane is a funnel shift over the planes of this chunk and the next one — the slot keys are stored in the same
+// bit-plane form (kmer_planes_from_2bit), so no per-base packing happens here.
 __global__ void __launch_bounds__(SEED_WARPS * 32)
 seed_count_kernel(DevIndex ix, const char* __restrict__ seqs, const u64* __restrict__ seq_off, u32 n,
                   const u64* __restrict__ read_koff, u32* __restrict__ kcnt, u32* __restrict__ koff,
                   u32* __restrict__ read_acnt) {
+    const u32 FULL = 0xffffffffu;
     const u32 lane = threadIdx.x & 31;
     const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
     const u32 k = ix.k;
+    const u32 kmask = k >= 32 ? 0xffffffffu : ((1u << k) - 1u);
     for (u32 r = warp; r < n; r += n_warps) {
         const u64 sb = seq_off[r];
+        const u32 len = (u32)(seq_off[r + 1] - sb);
         const u64 kb = read_koff[r];
         const u32 nk = (u32)(read_koff[r + 1] - kb);
         const u8* s = (const u8*)seqs + sb;
         u32 total = 0;
+        // planes of the current chunk
+        u32 c = lane < len ? base_code(s[lane]) : 4u;
+        u32 p0 = __ballot_sync(FULL, c & 1u), p1 = __ballot_sync(FULL, c & 2u), pb = __ballot_sync(FULL, c & 4u);
         for (u32 i0 = 0; i0 < nk; i0 += 32) {
+            const u32 jn = i0 + 32 + lane;
+            c = jn < len ? base_code(s[jn]) : 4u;
+            const u32 n0 = __ballot_sync(FULL, c & 1u), n1 = __ballot_sync(FULL, c & 2u), nbad = __ballot_sync(FULL, c & 4u);
             const u32 i = i0 + lane;
             u32 cnt = 0, off = 0;
             if (i < nk) {
-                u64 key = 0;
-                u32 bad = 0;
-                for (u32 t = 0; t < k; t++) {
-                    u32 c = base_code(s[i + t]);
-                    bad |= c & 4;
-                    key = (key << 2) | (c & 3);
-                }
+                const u32 bad = __funnelshift_r(pb, nbad, lane) & kmask;
                 if (!bad) {
+                    const u32 lo = __funnelshift_r(p0, n0, lane) & kmask, hi = __funnelshift_r(p1, n1, lane) & kmask;
+                    const u64 key = ((u64)hi << 32) | lo;
                     u32 h = (u32)kmer_slot_hash(key) & ix.slot_mask;
                     while (true) {
                         const uint4 raw = __ldg((const uint4*)(ix.slots + h));
-                        const u64 skey = ((u64)raw.y << 32) | raw.x;
                         if (raw.w == 0) break;                      // empty slot: not in index
-                        if (skey == key) { off = raw.z; cnt = raw.w; break; }
+                        if (raw.x == lo && raw.y == hi) { off = raw.z; cnt = raw.w; break; }
                         h = (h + 1) & ix.slot_mask;
                     }
                 }
                 kcnt[kb + i] = cnt;
                 koff[kb + i] = off;
             }
-            total += __reduce_add_sync(0xffffffffu, cnt);
+            total += __reduce_add_sync(FULL, cnt);
+            p0 = n0; p1 = n1; pb = nbad;
         }
         if (lane == 0) read_acnt[r] = total;
     }

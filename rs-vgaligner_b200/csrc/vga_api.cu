@@ -614,7 +614,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     pb.rows = w->b[B_ROWS].get<RowInfo>(tot[2]);
     pb.row_meta = d_row_meta;
     pb.match = P.match; pb.mismatch = P.mismatch; pb.o1 = P.o1; pb.e1 = P.e1; pb.o2 = P.o2; pb.e2 = P.e2; pb.wb = P.wb; pb.wf = P.wf;
-    pb.qmax_short = 0;
+    pb.qmax_short = 0; pb.nb_hint = 3;
     pb.work_ctr = ctr + 2; pb.pool_ctr = (unsigned long long*)(ctr + 4);
     TraceBuffers tbuf;
     memset(&tbuf, 0, sizeof(tbuf));
@@ -629,6 +629,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     std::vector<u64> est(NI);
     std::vector<std::vector<u32>> cls(NCLS);
     u64 est_total = 0;
+    u64 sum_rows = 0, sum_q = 0;
     {
         const int NB = 48;
         std::vector<u32> key(NI), cnt((size_t)NCLS * NB + 1, 0);
@@ -637,7 +638,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
             const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
             est[i] = (u64)(nrows * (west + 12));           // rows are stored from an 8-column boundary (trace_col0)
-            if (poa_short_ok(qlen, nrows, P) && qlen > (i64)pb.qmax_short) pb.qmax_short = (i32)qlen;
+            if (qlen < 256) { if (qlen > (i64)pb.qmax_short) pb.qmax_short = (i32)qlen; sum_rows += (u64)nrows; sum_q += (u64)qlen; }
             est_total += est[i];
             const int ci = poa_class_for(qlen, nrows, west, P);
             const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
@@ -652,6 +653,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             cls[ci][fill[key[i]]++ - cnt[(size_t)ci * NB]] = i;
         }
     }
+    // subgraphs much longer than their reads spend most rows at full band width: worth the 3-block step body (more registers)
+    pb.nb_hint = sum_rows >= 3 * sum_q ? 3 : 2;
     size_t free_b = 0, total_b = 0;
     VGA_CUDA(cudaMemGetInfo(&free_b, &total_b));
     const u64 warp_slack = (u64)w->n_sms * 64 * 8192;

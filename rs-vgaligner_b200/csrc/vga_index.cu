@@ -3,6 +3,7 @@
 // (src/index.rs:319-320): open addressing keyed by the 2-bit packed k-mer, exact membership,
 // identical positions in identical (table) order.  Only forward/forward positions are kept because
 // map_reads hard-codes only_forward=true (src/map.rs:62, src/chain.rs:154-156).
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -77,7 +78,7 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
         if (v->k < 32 && (v->key_kmer2bit[i] >> (2 * v->k)) != 0) {
             set_error("key_kmer2bit has bits above 2k"); return VGA_ERR_INVALID;
         }
-        if (cnt) ents.push_back({v->key_kmer2bit[i], off, cnt});
+        if (cnt) ents.push_back({kmer_planes_from_2bit(v->key_kmer2bit[i], v->k), off, cnt});
     }
     if (ptb.size() >= (1ull << 32)) { set_error("too many k-mer positions"); return VGA_ERR_UNSUPPORTED; }
     u64 n_slots = 16;

@@ -99,3 +99,29 @@ def test_simulators_are_seeded():
     assert g1 == g2 and g1 != vg.synth_gfa(50000, 100, 2)
     sx = vg.Index.build_from_text(g1, 15)
     assert 49000 < sx.view.seq_len < 53000 and sx.view.n_nodes > 1000
+
+
+def test_div1000_identity(tmp_path):
+    """k_chain.cu turns the integer score r into the f64 the reference stores (src/chain.rs:360-363) with
+    q0 = r*0.001, rem = fma(-1000, q0, r), q = fma(rem, 0.001, q0) instead of a division.  The identity
+    q == r/1000.0 was checked for every r in [-1e6, 2^31); this runs a stride of that check plus both ends."""
+    import subprocess
+    src = tmp_path / "div.c"
+    src.write_text(r'''
+#include <math.h>
+#include <stdio.h>
+#include <stdint.h>
+static int bad(int64_t r) { double a = (double)r, q0 = a * 0.001, rem = fma(-1000.0, q0, a); return fma(rem, 0.001, q0) != a / 1000.0; }
+int main(void) {
+    uint64_t n = 0;
+    for (int64_t r = -1000000; r < (1ll << 31); r += 61) n += bad(r);
+    for (int64_t r = (1ll << 31) - 4000000; r < (1ll << 31); r++) n += bad(r);
+    for (int64_t r = 0; r < 4000000; r++) n += bad(r);
+    printf("%llu\n", (unsigned long long)n);
+    return 0;
+}
+''')
+    exe = tmp_path / "div"
+    subprocess.run(["gcc", "-O2", "-ffp-contract=off", "-o", str(exe), str(src), "-lm"], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.strip()
+    assert out == "0"
