@@ -150,7 +150,27 @@ def pick_cpu_sample(vg, orc, ix, reads, threads, budget_s):
     return int(max(n0, min(reads.n, rate * budget_s)))
 
 
+# stdout carries exactly ONE JSON line: file descriptor 1 is pointed at stderr for the whole run (NCCL's banner, any
+# library chatter), and the line is written to the saved descriptor at the end.
+_JSON_FD = None
+
+
+def capture_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, data)
+
+
 def main():
+    capture_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -197,7 +217,7 @@ def main():
                                       "sample": "%d reads of the workload per step, oracle port, threads over reads" % n_sample},
                      "e2e": {"value": rate, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                      "gpu_launches": 0, "aligned_fraction": aligned / n_sample, "cpu_gcups": cells / sec / 1e9})
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     # ------------------------------------------------------------------ our arm (GPU)
@@ -211,9 +231,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout carries exactly one JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL prints its version banner on stdout (NCCL_DEBUG=VERSION/WARN/INFO); emit() keeps it off the JSON stream
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     L = vg.gpu_lib()
     rc = L.vga_init(local_rank)
@@ -392,7 +411,7 @@ def main():
         poa_ms, poa_launches = mean("ms_poa"), max(1, s["poa_launches"])
         gcups = s["poa_cells"] / (poa_ms * 1e-3) / 1e9 if poa_ms > 0 else 0.0
         gcups_peak = int32_peak / 17.0 / 1e9
-        roof_poa = {"kernel": "poa_fill_kernel", "bound": "int32_alu", "achieved": gcups, "peak": gcups_peak, "unit": "GCUPS",
+        roof_poa = {"kernel": "poa_fill_pair_kernel (short reads) / poa_fill_kernel<SLIDE> (long reads): all fill launches of a step", "bound": "int32_alu", "achieved": gcups, "peak": gcups_peak, "unit": "GCUPS",
                     "frac": gcups / gcups_peak if gcups_peak else None, "traffic": traffic.get("poa_fill_bytes_per_launch"),
                     "peak_source": "measured here: %.1f T int32 op/s (IADD+IMNMX streams) / 17 ops per cell" % (int32_peak / 1e12),
                     "launches_per_step": poa_launches, "ms_per_launch": poa_ms / poa_launches,
@@ -422,7 +441,7 @@ def main():
             line["cpu_baseline"] = {"value": rate, "unit": "reads/s", "cores": threads, "kind": "port",
                                     "sample": "first %d reads of rank 0's shard, oracle port with threads over reads, %.1f s" % (n_sample, sec),
                                     "cpu_gcups": cells / sec / 1e9}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
