@@ -61,14 +61,15 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
     __shared__ u32 s_q[CHAIN_WARPS][RING], s_tb[CHAIN_WARPS][RING], s_te[CHAIN_WARPS][RING];
     __shared__ double s_f[CHAIN_WARPS][RING];
     __shared__ unsigned long long s_key[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
-    __shared__ i32 s_r[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
     __shared__ u8 s_pd[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
     const u32 lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
     const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
     u32* rq = s_q[wl]; u32* rtb = s_tb[wl]; u32* rte = s_te[wl]; double* rf = s_f[wl];
     unsigned long long* keys = s_key[FUSED ? wl : 0];
-    i32* rr = s_r[FUSED ? wl : 0];
+    // integer score of sorted anchor i: kept in the HIGH word of keys[i] (its te) once the anchor has been staged into the
+    // ring (a block of 32 is staged before any score of that block is written), the low word (anchor id) stays
+    i32* rr2 = (i32*)keys;
     u8* pd = s_pd[FUSED ? wl : 0];
     const i32 rk = (i32)b.k * 1000;                                       // Anchor::new: max_chain_score = k
     const u32 n_work = FUSED ? b.n_reads : b.n_big;
@@ -136,47 +137,59 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
             if (lane == 0) {
                 rf[si] = f_i;
                 b.f[base + i] = f_i;
-                if (FUSED) { rr[i] = r_i; pd[i] = p < 0 ? 0 : (u8)dmin; }
+                if (FUSED) { rr2[2 * i + 1] = r_i; pd[i] = p < 0 ? 0 : (u8)dmin; }
                 else b.pred[base + i] = p;
                 if (b.pred_dbg) b.pred_dbg[base + i] = p < 0 ? -1 : (i32)(FUSED ? (u32)keys[p] : b.sidx[base + p]);
             }
             __syncwarp();
         }
-        // ---- backtracking (:455-558), sequential by construction
-        if (lane == 0) {
+        // ---- backtracking (:455-558).  The reference visits i = n-1 .. 0 and starts a chain at every anchor that still has
+        // a predecessor and carries the maximum score; candidates are found 32 anchors at a time by ballot (a chain consumes
+        // only anchors below its start, so the block is re-examined after every extraction), the walk itself is lane 0's.
+        {
             u32* creg = b.cmem + 2ull * base + 2ull * r;
             u32* cl = b.clen + base + r;
-            u32 n_ch = 0, tail = 0;
+            u32 n_ch = 0, tail = 0;                                      // lane 0's
             const double curr_max = div1000(r_max);
-            for (u32 i = n; i-- > 0;) {
-                const bool cand = FUSED ? (pd[i] != 0 && rr[i] == r_max)
-                                        : (b.pred[base + i] >= 0 && b.f[base + i] == curr_max);     // :469
-                if (cand) {
-                    const u32 start = tail;
-                    u32 cur = i;
-                    for (;;) {
-                        i32 p;
-                        if (FUSED) { p = pd[cur] ? (i32)(cur - pd[cur]) : -1; pd[cur] = 0; }
-                        else { p = b.pred[base + cur]; b.pred[base + cur] = -1; }       // :478 consume
-                        creg[tail++] = cur;                              // :498 the terminal is pushed too
-                        if (p < 0) break;
-                        cur = (u32)p;
-                    }
-                    const u32 len = tail - start;
-                    if (len >= b.min_anchors) {                          // :545-548
-                        for (u32 y = 0; y < len / 2; y++) {
-                            u32 t = creg[start + y];
-                            creg[start + y] = creg[tail - 1 - y];
-                            creg[tail - 1 - y] = t;
+            for (i32 c0 = (i32)((n - 1) & ~31u); c0 >= 0; c0 -= 32) {
+                for (;;) {
+                    const u32 ii = (u32)c0 + lane;
+                    bool cand = false;
+                    if (ii < n) cand = FUSED ? (pd[ii] != 0 && rr2[2 * ii + 1] == r_max)
+                                             : (b.pred[base + ii] >= 0 && b.f[base + ii] == curr_max);     // :469
+                    const u32 cm = __ballot_sync(FULLM, cand);
+                    if (cm == 0) break;
+                    if (lane == 0) {
+                        const u32 i = (u32)c0 + 31u - (u32)__clz((int)cm);
+                        const u32 start = tail;
+                        u32 cur = i;
+                        for (;;) {
+                            i32 p;
+                            if (FUSED) { p = pd[cur] ? (i32)(cur - pd[cur]) : -1; pd[cur] = 0; }
+                            else { p = b.pred[base + cur]; b.pred[base + cur] = -1; }       // :478 consume
+                            creg[tail++] = cur;                              // :498 the terminal is pushed too
+                            if (p < 0) break;
+                            cur = (u32)p;
                         }
-                        cl[n_ch++] = len;
-                    } else {
-                        tail = start;
+                        const u32 len = tail - start;
+                        if (len >= b.min_anchors) {                          // :545-548
+                            for (u32 y = 0; y < len / 2; y++) {
+                                u32 t = creg[start + y];
+                                creg[start + y] = creg[tail - 1 - y];
+                                creg[tail - 1 - y] = t;
+                            }
+                            cl[n_ch++] = len;
+                        } else {
+                            tail = start;
+                        }
                     }
+                    __syncwarp();
                 }
             }
-            b.n_chains[r] = n_ch;
-            b.n_members[r] = tail;
+            if (lane == 0) {
+                b.n_chains[r] = n_ch;
+                b.n_members[r] = tail;
+            }
         }
         __syncwarp();
     }

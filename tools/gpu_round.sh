@@ -15,7 +15,7 @@ done
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_ref_C2.json 2> $O/${TAG}_bench_ref_C2.err; echo "ref rc=$?"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/${TAG}_launches_C2.csv \
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:poa_fill_group_kernel -c 2 -o $O/${TAG}_full_poa_group_C2 -f \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:poa_fill_pair_kernel -c 2 -o $O/${TAG}_full_poa_pair_C2 -f \
   python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:seed_ -c 2 -o $O/${TAG}_full_seed_C4 -f \
   python bench.py --steps 1 --warmup 1 --workload C4 --reads 400000 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_full_seed.log 2>&1; echo "ncu seed rc=$?"
