@@ -663,8 +663,12 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     if (want_words > max_words) want_words = max_words;
     if (want_words > (1ull << 34) - (1u << 20)) want_words = (1ull << 34) - (1u << 20);   // RowInfo.toff: u32 in 4-word units
     if (want_words < (1ull << 22)) want_words = 1ull << 22;
+    // VGA_POOL_MAX_WORDS caps the pool (tests: forces several waves and the pool-overflow path on small inputs)
+    u64 pool_cap_env = ~0ull;
+    if (const char* e = getenv("VGA_POOL_MAX_WORDS")) { const long long v = atoll(e); if (v > 0) pool_cap_env = (u64)v; }
+    if (want_words > pool_cap_env) want_words = pool_cap_env;
     pb.pool = w->b[B_POOL].get<u32>(want_words);
-    pb.pool_words = std::min<u64>(w->b[B_POOL].cap / 4, (1ull << 34) - 16);
+    pb.pool_words = std::min<u64>(std::min<u64>(w->b[B_POOL].cap / 4, (1ull << 34) - 16), pool_cap_env);
     tbuf.pool = pb.pool;
     tl_mark("pool ready");
     u32* d_work = w->b[B_WORK].get<u32>(NI);
@@ -700,15 +704,22 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         std::vector<u32>& list = cls[ci];
         size_t pos = 0;
         int stall = 0;
+        // Waves are admitted on the a-priori estimate (widest band on every row).  Tried and dropped: scaling the estimate by
+        // the measured pool use of earlier waves (overflows and reruns cost more than fuller waves gain) and accounting the
+        // real use instead of the estimate (leaves room for tiny follow-up waves that cannot fill the machine).
+        const double scale = 1.0;
+        auto cost = [&](u32 it) { return (u64)((double)(est[it] + est[it] / 4) * scale) + 64; };
         while (pos < list.size()) {
             // take a wave whose estimate fits what is left of the pool
-            const u64 first = est[list[pos]] + est[list[pos]] / 4;
+            const u64 first = cost(list[pos]);
             if (pool_acc + first > pb.pool_words && pool_acc > warp_slack) flush_trace();
             const bool fresh_pool = pool_acc == warp_slack;
-            u64 acc = pool_acc;
+            const u64 used_before = pool_acc - warp_slack;
+            u64 acc = pool_acc, wave_est = 0;
             size_t end = pos;
-            while (end < list.size() && (end == pos || acc + est[list[end]] + est[list[end]] / 4 <= pb.pool_words)) {
-                acc += est[list[end]] + est[list[end]] / 4;
+            while (end < list.size() && (end == pos || acc + cost(list[end]) <= pb.pool_words)) {
+                acc += cost(list[end]);
+                wave_est += est[list[end]] + est[list[end]] / 4;
                 end++;
             }
             const u32 nw = (u32)(end - pos);
@@ -724,11 +735,14 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             c.launches++;
             queue_chain_d2h();          // host-side queueing (and any pinned allocation) hides behind the fill kernel
             VGA_CUDA(cudaMemcpyAsync(h_status.data(), d_status, 4ull * nw, cudaMemcpyDeviceToHost, st));
+            unsigned long long used_now = 0;
+            VGA_CUDA(cudaMemcpyAsync(&used_now, ctr + 4, 8, cudaMemcpyDeviceToHost, st));
             VGA_CUDA(cudaStreamSynchronize(st));
             float a = 0;
             cudaEventElapsedTime(&a, w->ev[8], w->ev[9]);
             ms_fill += a;
-            if (host_timeline()) fprintf(stderr, "[vga] poa fill class %d: %u items, %.3f ms\n", ci, nw, a);
+            if (host_timeline()) fprintf(stderr, "[vga] poa fill class %d: %u items, %.3f ms (pool: %.2f of the estimate)\n", ci, nw, a,
+                                         wave_est ? (double)(used_now - used_before) / (double)wave_est : 0.0);
             pool_acc = acc;
             std::vector<u32> again;
             u32 done = 0;

@@ -111,6 +111,21 @@ def test_hla_graphs_short_reads(graph, k, n, length):
     assert (g.aln_status == vg.ALN_OK).mean() > 0.5
 
 
+@pytest.mark.gpu
+def test_small_trace_pool_waves_and_overflow(monkeypatch):
+    """A trace pool far smaller than the batch needs: alignments run in several waves, the calibrated wave estimate
+    overshoots at least sometimes and the pool-overflow path (IT_RETRY_POOL -> traceback, start over, rerun) is taken.
+    Results must not depend on any of it."""
+    ix = vg.Index.build(fixture_path("graphs/2-DRB1-3123.gfa"), 11)
+    reads = vg.simulate_reads(ix, 3000, 150, 0.01, 0.0005, 0.0005, 0.1, 5)
+    # 148 SMs x 64 x 8192 words are set aside for chunks in flight; leave ~12 M words (the batch needs > 100 M)
+    monkeypatch.setenv("VGA_POOL_MAX_WORDS", str(148 * 64 * 8192 + 12_000_000))
+    g, o = both(ix, reads)
+    monkeypatch.delenv("VGA_POOL_MAX_WORDS")
+    check_all(g, o)
+    assert g.stats["poa_launches"] >= 3
+
+
 def test_cyclic_inverting_graph():
     """5-B3106 has back links and '-' orientations (reverse handles in the extension)."""
     ix = vg.Index.build(fixture_path("graphs/5-B3106.gfa"), 11)
