@@ -106,7 +106,7 @@ struct PoaBuffers {
     i32 qmax_short;          // longest read among the items of the short-read classes (sizes the pair kernel's shared memory)
 };
 // kernel classes: 0..1 = short reads on the 16x2 kernel (k_poa_pair.cu; 1 = with the per-row range check); 2 = short reads, 32 lanes
-// (k_poa_short.cu); 3..5 = SLIDE C=8,16,32 (k_poa.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
+// (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
 int poa_class_count();
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P);
 int poa_class_wider(int cls);    // -1: none

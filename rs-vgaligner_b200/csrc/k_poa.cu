@@ -510,25 +510,28 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
 
 // classes: 0 = short reads on the 16x2 kernel (k_poa_pair.cu: qlen < 246, default gap model, int16 absolute scores bounded
 // by the row count), 1 = the same kernel with a per-row range check for longer subgraphs, 2 = short reads with 32 lanes
-// (k_poa_short.cu, any gap model, reads < 256), 3..5 = SLIDE C = 8, 16, 32 (bands up to 256 / 512 / 1024 columns).
+// (k_poa_short.cu, any gap model, reads < 256), 3..7 = SLIDE C = 8, 12, 16, 24, 32 (bands up to 256 / 384 / 512 / 768 / 1024 columns).
 // An item that does not fit its class moves to the next.
 // VGA_POA_PAIR=0 restores the 8 / 16 / 32-lane kernels of k_poa_short.cu on classes 0..2 (A/B measurements).
 static int g_pair = getenv("VGA_POA_PAIR") ? atoi(getenv("VGA_POA_PAIR")) : 1;
 // off by default: measured slower than the SLIDE kernel on the few very long subgraphs of 17-DRB1-3123-smooth (one 8-lane group per item is a longer critical path than one warp per item)
 static int g_pair_chk = getenv("VGA_POA_CHK") ? atoi(getenv("VGA_POA_CHK")) : 0;
 static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
-int poa_class_count() { return 6; }
+int poa_class_count() { return 8; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
     if (g_pair) {
         if (poa_pair_ok(qlen, nrows, P)) return 0;
         if (g_pair_chk && poa_pair_checked_ok(qlen, nrows, P)) return 1;
         if (poa_short_ok(qlen, nrows, P)) return 2;
     } else if (poa_short_ok(qlen, nrows, P)) return west <= (i64)g_short_w8 ? 0 : west <= 160 ? 1 : 2;
+    // SLIDE instances compute all 32*C columns of every row, so an item goes to the narrowest one its estimate allows
     if (west <= 256 - 8) return 3;
-    if (west <= 512 - 16) return 4;
-    return 5;
+    if (west <= 384 - 12) return 4;
+    if (west <= 512 - 16) return 5;
+    if (west <= 768 - 24) return 6;
+    return 7;
 }
-int poa_class_wider(int cls) { return cls < 5 ? cls + 1 : -1; }
+int poa_class_wider(int cls) { return cls < 7 ? cls + 1 : -1; }
 
 template <int C, bool SLIDE>
 static void launch_fill(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
@@ -550,7 +553,9 @@ int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms,
         // fall through
         case 2: return launch_poa_fill_short(ix, b, cls, n_sms, st);
         case 3: launch_fill<8, true>(ix, b, n_sms, st); break;
-        case 4: launch_fill<16, true>(ix, b, n_sms, st); break;
+        case 4: launch_fill<12, true>(ix, b, n_sms, st); break;
+        case 5: launch_fill<16, true>(ix, b, n_sms, st); break;
+        case 6: launch_fill<24, true>(ix, b, n_sms, st); break;
         default: launch_fill<32, true>(ix, b, n_sms, st); break;
     }
     return 1;

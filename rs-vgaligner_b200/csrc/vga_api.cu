@@ -681,6 +681,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     std::vector<u32> trace_list;
     trace_list.reserve(NI);
     u64 pool_acc = warp_slack;                  // estimated words in use since the last traceback
+    u64 used_prev = 0;                          // pool counter after the previous wave (timeline print only)
     VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
     auto flush_trace = [&]() {
         if (!trace_list.empty()) {
@@ -699,6 +700,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         }
         VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
         pool_acc = warp_slack;
+        used_prev = 0;
     };
     for (int ci = 0; ci < NCLS; ci++) {
         std::vector<u32>& list = cls[ci];
@@ -714,7 +716,6 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             const u64 first = cost(list[pos]);
             if (pool_acc + first > pb.pool_words && pool_acc > warp_slack) flush_trace();
             const bool fresh_pool = pool_acc == warp_slack;
-            const u64 used_before = pool_acc - warp_slack;
             u64 acc = pool_acc, wave_est = 0;
             size_t end = pos;
             while (end < list.size() && (end == pos || acc + cost(list[end]) <= pb.pool_words)) {
@@ -742,7 +743,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             cudaEventElapsedTime(&a, w->ev[8], w->ev[9]);
             ms_fill += a;
             if (host_timeline()) fprintf(stderr, "[vga] poa fill class %d: %u items, %.3f ms (pool: %.2f of the estimate)\n", ci, nw, a,
-                                         wave_est ? (double)(used_now - used_before) / (double)wave_est : 0.0);
+                                         wave_est && used_now >= used_prev ? (double)(used_now - used_prev) / (double)wave_est : 0.0);
+            used_prev = used_now;
             pool_acc = acc;
             std::vector<u32> again;
             u32 done = 0;
