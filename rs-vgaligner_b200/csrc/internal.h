@@ -107,12 +107,14 @@ struct PoaBuffers {
 };
 // kernel classes: 0..1 = short reads on the 16x2 kernel (k_poa_pair.cu; 1 = with the per-row range check); 2 = short reads, 32 lanes
 // (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
+void poa_set_long_mode(u64 n_long_items, int n_sms);   // picks the long-read kernel family for the batch (k_poa.cu)
 int poa_class_count();
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P);
 int poa_class_wider(int cls);    // -1: none
 int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 int launch_poa_fill_short(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 bool poa_short_ok(i64 qlen, i64 nrows, const VgaParams& P);   // read short enough and scores within int16
+int launch_poa_fill_long(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st);              // k_poa_long.cu
 int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);   // k_poa_pair.cu
 bool poa_pair_checked_ok(i64 qlen, i64 nrows, const VgaParams& P);   // same, scores checked per row instead of bounded a priori
 bool poa_pair_ok(i64 qlen, i64 nrows, const VgaParams& P);    // 16x2 kernel: short read, int16 scores, default-sized gap model

@@ -1,0 +1,375 @@
+// K5 (long reads) — banded sequence-to-graph POA fill for reads of any length whose band stays within 1024 columns,
+// replacing the abPOA call at the reference's FFI seam (src/align.rs:190-202).  Same alignment definition, trace word
+// format (scores relative to ref(row) = maximum of the previous row), RowInfo / NodeState records and
+// work-queue protocol as k_poa.cu, so the traceback kernel is shared.
+//
+// The SLIDE instances of k_poa.cu keep the previous row in registers, C columns per lane, C fixed per kernel: every
+// row costs 32*C columns although the adaptive band of a 10 kb read covers a third of that on average, and an
+// alignment has to run on the instance its WIDEST row needs.  Here (the design of k_poa_short.cu, 32-bit):
+//   * one warp per (read, chain); the work of a row is proportional to ITS band: the row uses the smallest block size
+//     CR of {5,9,13,17,25,33} with 32 lanes x CR columns >= band, lane l computes columns [beg + l*CR, +CR) — CR is odd
+//     so that the 32 lanes, CR int32 words apart, hit 32 different shared-memory banks;
+//   * since that mapping moves from row to row, the previous row (H, E1', E2' as int32) lives in shared memory in a
+//     window of WIN columns that follows the band: buffer index = column - cbase + PAD.  The window is re-anchored
+//     (data moved to the front) when the band reaches its end, and re-built on rows whose predecessor is not the
+//     previous row.  Out-of-band cells hold -inf plus one guard cell per side, so readers need no band test;
+//   * the query bytes of the window are staged next to it (the band advances a column or two per row);
+//   * F1/F2 are prefix-max scans: serial inside the lane block, Kogge-Stone across the warp.
+// Roofline: INT32 ALU issue.  Algorithmic work = band cells.
+#include <climits>
+#include <cstdlib>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace vga {
+
+static const int PL_WARPS = 2;              // warps per CTA (17 KB of shared memory each)
+static const u64 LONG_POOL_CHUNK = 8192;    // trace words a warp takes from the pool per refill
+static const int LPAD = 8;                  // buffer index of column cbase (column cbase-1 .. are guards)
+static const int WIN = 1280;                // columns of the window (bands are at most 1024 + the odd block size slack)
+static const int LBUF = LPAD + WIN + 8;     // index of column beg + 32*CR + 1 stays below LPAD + WIN (re-anchoring rule below)
+static const u32 FULLW = 0xffffffffu;
+
+__device__ __forceinline__ i32 imax(i32 a, i32 b) { return a > b ? a : b; }
+__device__ __forceinline__ i32 imin(i32 a, i32 b) { return a < b ? a : b; }
+__device__ __forceinline__ i32 sext16(u32 w) { return (i32)(short)(w & 0xffffu); }
+
+struct LongSmem {
+    i32 h[LBUF], e1[LBUF], e2[LBUF];      // previous row; updated in place (loads precede the warp's scan, stores follow it)
+    i32 hh[LBUF];                         // Hhat of the row in progress (sweep 1 -> sweep 2)
+    u8 q[LBUF];                           // query byte of column j (base j-1) at the same index
+};
+
+struct LongConst { i32 e1, e2, oe1, oe2, o1, o2, smatch, smis; };
+struct LongRowOut { i32 mx, lpos, rpos, lmin; };
+
+// One DP row.  `x0` is the buffer index of column beg; lane l computes the CR columns from beg + l*CR.  Only in-band
+// cells are stored; the generator of F is masked outside the band, so an out-of-band H is an F that decays from the
+// last band cell and never reaches the row maximum (e1, e2 >= 1).  CR is a run-time value and the column loops are
+// NOT unrolled per block size: sweep 2 recomputes Hhat and the lane-local F scan of sweep 1 instead of keeping them in
+// per-column registers, so there is ONE small loop body for every band width (a version with an unrolled body per
+// block size spent 60 % of its cycles waiting for instruction fetch).
+__device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32 CR, i32 beg, i32 end, i32 x0, u32 base, i32 ref,
+                                               LongSmem& sm, u32* __restrict__ tr) {
+    const i32 j0 = beg + (i32)lane * CR;
+    const i32 idx = x0 + (i32)lane * CR;
+    const i32 thi = end - j0;                              // column t of the lane is in the band iff t <= thi
+    const i32* ph = sm.h + idx;
+    const i32* pe1 = sm.e1 + idx;
+    const i32* pe2 = sm.e2 + idx;
+    const u8* pq = sm.q + idx;
+    // ---- sweep 1: Hhat = max(M, E1, E2) (kept in the scratch plane) and the lane-local part of the F scans
+    i32* const shh = sm.hh + idx;
+    i32 run1 = POA_DEEP, run2 = POA_DEEP;
+    {
+        i32 hd = ph[-1];
+#pragma unroll 4
+        for (i32 t = 0; t < CR; t++) {
+            const i32 m = hd + ((u32)pq[t] == base ? K.smatch : K.smis);
+            const i32 hh = t <= thi ? __vimax3_s32(m, pe1[t], pe2[t]) : POA_DEEP;
+            hd = ph[t];
+            shh[t] = hh;
+            run1 = __viaddmax_s32(run1, -K.e1, hh - K.oe1);
+            run2 = __viaddmax_s32(run2, -K.e2, hh - K.oe2);
+        }
+    }
+    // carry of F1/F2 across the warp (Kogge-Stone; shfl_up leaves lanes < d unchanged, and max(v, v - c) = v)
+    i32 cin1 = run1, cin2 = run2;
+    {
+        const i32 s1 = K.e1 * CR, s2 = K.e2 * CR;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const i32 t1 = __shfl_up_sync(FULLW, cin1, d), t2 = __shfl_up_sync(FULLW, cin2, d);
+            cin1 = __viaddmax_s32(t1, -s1 * d, cin1);
+            cin2 = __viaddmax_s32(t2, -s2 * d, cin2);
+        }
+    }
+    cin1 = __shfl_up_sync(FULLW, cin1, 1); cin2 = __shfl_up_sync(FULLW, cin2, 1);
+    if (lane == 0) { cin1 = POA_DEEP; cin2 = POA_DEEP; }
+    // ---- sweep 2: H, E', trace words, row maximum keyed by column, smallest reachable H
+    i32 kl = INT_MIN, kr = INT_MIN;          // max of (H, -t) and (H, t): lane maximum with its leftmost / rightmost column
+    u32 lminu = 0xffffffffu;                 // min of H + 2^27 as unsigned: unreachable cells (H <= -2^27) wrap to huge values
+    i32 hprev_new = 0;                       // new H of column t-1
+    u32 w0 = 0; i32 f1_0 = 0, f2_0 = 0;      // column 0: its F fields need the left lane's last new H
+    u32* const trl = tr + lane * CR;
+    i32* const sh = sm.h + idx; i32* const s1p = sm.e1 + idx; i32* const s2p = sm.e2 + idx;
+    {
+        run1 = POA_DEEP; run2 = POA_DEEP;
+#pragma unroll 2
+        for (i32 t = 0; t < CR; t++) {
+            const i32 x1 = s1p[t], x2 = s2p[t];
+            const i32 hh = shh[t];
+            const i32 f1 = __viaddmax_s32(cin1, -K.e1 * t, run1), f2 = __viaddmax_s32(cin2, -K.e2 * t, run2);
+            const i32 h = imax(__vimax3_s32(hh, f1, f2), POA_DEEP);
+            run1 = __viaddmax_s32(run1, -K.e1, hh - K.oe1);
+            run2 = __viaddmax_s32(run2, -K.e2, hh - K.oe2);
+            const i32 d1 = __viaddmax_s32(x1, K.o1 - h, 0);          // E1' - (H - oe1) = max(E1 - e1 - H + oe1, 0)
+            const i32 d2 = __viaddmax_s32(x2, K.o2 - h, 0);
+            u32 hi = (u32)d2 * 8u + (u32)d1;
+            if (t > 0) {
+                hi = (u32)__viaddmax_s32(f1, 1 + K.oe1 - hprev_new, 0) * 256u + hi;
+                hi = (u32)__viaddmax_s32(f2, 1 + K.oe2 - hprev_new, 0) * 2048u + hi;
+            }
+            const u32 wd = __byte_perm((u32)imax(h - ref, -32768), hi, 0x5410);
+            if (t == 0) { w0 = wd; f1_0 = f1; f2_0 = f2; }
+            hprev_new = h;
+            if (t <= thi) {
+                sh[t] = h;
+                s1p[t] = d1 + h - K.oe1;
+                s2p[t] = d2 + h - K.oe2;
+                if (t > 0) trl[t] = wd;
+                const i32 hk = imax(h, -(1 << 24)) * 64;             // reachable scores are far above -2^24
+                kl = imax(kl, hk + 63 - t);
+                kr = imax(kr, hk + t);
+                lminu = min(lminu, (u32)(h + (1 << 27)));
+            }
+        }
+    }
+    {   // F fields of the lane's first column: relative to the left lane's last H
+        const i32 hl = __shfl_up_sync(FULLW, hprev_new, 1);
+        if (lane > 0) w0 += ((u32)imax(f1_0 + 1 + K.oe1 - hl, 0) << 24) + ((u32)imax(f2_0 + 1 + K.oe2 - hl, 0) << 27);
+        if (0 <= thi) trl[0] = w0;
+    }
+    // guards: H(beg-1) = -inf (diagonal of column beg in the next row), E'(end+1) = -inf (vertical of column end+1)
+    if (lane == 0) sm.h[x0 - 1] = POA_NEG_INF;
+    if (lane == 1) { sm.e1[x0 + (end - beg) + 1] = POA_NEG_INF; sm.e2[x0 + (end - beg) + 1] = POA_NEG_INF; }
+    // ---- row maximum and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i)
+    LongRowOut o;
+    const i32 lmax = kl == INT_MIN ? INT_MIN : (kl >> 6);
+    o.mx = __reduce_max_sync(FULLW, lmax);
+    o.lpos = __reduce_min_sync(FULLW, lmax == o.mx ? j0 + 63 - (kl & 63) : INT_MAX);
+    o.rpos = __reduce_max_sync(FULLW, lmax == o.mx ? j0 + (kr & 63) : -1);
+    const u32 mnu = __reduce_min_sync(FULLW, lminu);
+    o.lmin = mnu >= 0x80000000u ? INT_MAX : (i32)mnu - (1 << 27);       // no reachable cell in the row: nothing to check
+    return o;
+}
+
+__device__ __forceinline__ int long_pick_cr(i32 W) {
+    return W <= 160 ? 5 : W <= 288 ? 9 : W <= 416 ? 13 : W <= 544 ? 17 : W <= 800 ? 25 : W <= 1024 ? 33 : 0;
+}
+
+__global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex ix, PoaBuffers b) {
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    LongSmem& sm = ((LongSmem*)dyn_smem)[threadIdx.x >> 5];
+    const u32 lane = threadIdx.x & 31;
+    LongConst K;
+    K.e1 = b.e1; K.e2 = b.e2; K.oe1 = b.o1 + b.e1; K.oe2 = b.o2 + b.e2; K.o1 = b.o1; K.o2 = b.o2;
+    K.smatch = b.match; K.smis = -b.mismatch;
+    const i32 oe1 = K.oe1, oe2 = K.oe2;
+    u64 pool_cur = 0, pool_end = 0;                 // this warp's current chunk of the trace pool (words)
+    for (;;) {
+        // ---- next (read, chain) of the work list
+        u32 wi = 0;
+        if (lane == 0) wi = atomicAdd(b.work_ctr, 1u);
+        wi = __shfl_sync(FULLW, wi, 0);
+        if (wi >= b.n_items) break;
+        const u32 w = b.work[wi];
+        const AlignItem it = b.items[w];
+        const i32 qlen = (i32)it.qlen;
+        const u8* __restrict__ q = (const u8*)b.seqs + it.q_off;
+        const i32 wband = b.wb + (i32)(b.wf * (float)qlen);
+        const u32 nb = it.node_base, S = it.S, row_base = it.row_base, pred_base = it.pred_base, nrows = it.nrows;
+        u32 status = VGA_ALN_OK;
+        u64 cells = 0;
+        u32 s = 0, o = 0, metas = 0;
+        i32 beg = 0, end = 0, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
+        i32 cbase = 0;                               // column at buffer index LPAD
+        i32 qfill = -1;                              // query bytes of columns cbase .. qfill are staged
+        i32 end0 = 0;
+        if (S == 0 || nrows == 0) status = VGA_ALN_EMPTY;
+        else {
+            const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
+            end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+        }
+        for (u32 row = 0; row < nrows && status == VGA_ALN_OK; row++) {
+            if ((row & 31) == 0) metas = (row + lane < nrows) ? b.row_meta[row_base + row + lane] : 0u;
+            const u32 meta = __shfl_sync(FULLW, metas, row & 31);
+            const u32 base = meta & 0xffu, kind = (meta >> 8) & 3u;
+            // predecessor row: the previous row unless this is a first row with other predecessors
+            i32 mpl = lpos + 1, mpr = rpos + 1, min_pb = ppb, max_pe = ppe, ref = mxrow;
+            u32 prow = row - 1, np = 1, po = 0;
+            if (kind == 1) { mpl = 1; mpr = 1; min_pb = 0; max_pe = end0; np = 0; prow = 0; ref = 0; }      // virtual source row
+            else if (kind == 2) {
+                __syncwarp();       // NodeState / RowInfo / trace words of earlier rows were written by other lanes
+                po = b.nd_pred_off[nb + s];
+                np = b.nd_pred_off[nb + s + 1] - po;
+                const u32* __restrict__ pl = b.nd_pred + pred_base + po;
+                mpl = INT_MAX; mpr = 0; min_pb = INT_MAX; max_pe = -1; ref = INT_MIN;
+                for (u32 x = 0; x < np; x++) {
+                    const NodeState ns = b.nd_state[nb + pl[x]];
+                    mpl = imin(mpl, ns.lpos + 1); mpr = imax(mpr, ns.rpos + 1);
+                    min_pb = imin(min_pb, ns.beg); max_pe = imax(max_pe, ns.end);
+                    ref = imax(ref, ns.mx);
+                }
+                prow = b.nd_row_start[nb + pl[0] + 1] - 1;
+            }
+            // adaptive band (abPOA GET_AD_DP_BEGIN/END + clipping to the predecessors' bands)
+            const i32 r = qlen - (i32)(meta >> 11);
+            beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
+            end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
+            const i32 W = end - beg + 1;
+            const int cr = long_pick_cr(W);
+            if (beg > end) status = VGA_ALN_BAND_ERR;
+            else if (cr == 0) status = VGA_ALN_TOO_WIDE;
+            // pool space: one trace word per band cell, rows stored from an 8-column boundary (trace_col0)
+            const u64 need = (u64)((W + (beg & 7) + 3) & ~3);
+            if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
+                unsigned long long got = 0;
+                const u64 take = need > LONG_POOL_CHUNK ? need : LONG_POOL_CHUNK;
+                if (lane == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
+                got = __shfl_sync(FULLW, got, 0);
+                if (got + take > b.pool_words) status = IT_RETRY_POOL;
+                else { pool_cur = got; pool_end = got + take; }
+            }
+            if (status != VGA_ALN_OK) break;
+            u32* __restrict__ tr = b.pool + pool_cur + (beg & 7);
+            if (lane == 0) {
+                uint4* dst = (uint4*)(b.rows + row_base + row);
+                dst[0] = make_uint4((u32)beg, (u32)end, (u32)(pool_cur >> 2), (u32)ref);
+                dst[1] = make_uint4(prow, (np < 0xffffffu ? np : 0xffffffu) | (base << 24), s, o);
+            }
+            pool_cur += need;
+            cells += (u64)W;
+            // ---- the window: columns beg-1 .. end+1 (+ the last lane's block) must lie inside the buffer
+            __syncwarp();
+            if (kind != 0) {
+                // the predecessor row is not the one in shared memory: anchor the window at this band and build it there
+                cbase = imax(beg - 1, 0) & ~3;
+                qfill = cbase - 1;
+                const i32 jlo = imax(beg - 1, 0);
+                if (lane == 0 && cbase == 0) sm.h[LPAD - 1] = POA_NEG_INF;           // column -1: M(i,0) does not exist
+                if (kind == 1) {          // virtual source row
+                    for (i32 j = jlo + (i32)lane; j <= end + 1; j += 32) {
+                        const bool in0 = j <= end0;
+                        const int x = j - cbase + LPAD;
+                        sm.h[x] = !in0 ? POA_NEG_INF : j == 0 ? 0 : imax(-(b.o1 + b.e1 * j), -(b.o2 + b.e2 * j));
+                        sm.e1[x] = j == 0 ? -oe1 : POA_NEG_INF;
+                        sm.e2[x] = j == 0 ? -oe2 : POA_NEG_INF;
+                    }
+                } else {                  // merge of the predecessors' last rows, decoded from their trace words
+                    const u32* __restrict__ pl = b.nd_pred + pred_base + po;
+                    for (u32 x = 0; x < np; x++) {
+                        const u32 p = pl[x];
+                        const int2 pbe = *(const int2*)(b.nd_state + nb + p);
+                        const RowInfo pri = b.rows[row_base + b.nd_row_start[nb + p + 1] - 1];
+                        const u32* __restrict__ tw = b.pool + (u64)pri.toff * 4;
+                        const i32 pc0 = trace_col0(pbe.x);
+                        for (i32 j = jlo + (i32)lane; j <= end + 1; j += 32) {
+                            i32 hv = POA_NEG_INF, e1v = POA_NEG_INF, e2v = POA_NEG_INF;
+                            if (j >= pbe.x && j <= pbe.y) {
+                                const u32 v = tw[j - pc0];
+                                hv = pri.ref + sext16(v);
+                                e1v = hv - oe1 + (i32)((v >> 16) & 7u);
+                                e2v = hv - oe2 + (i32)((v >> 19) & 31u);
+                            }
+                            const int xx = j - cbase + LPAD;
+                            if (x > 0) { hv = imax(hv, sm.h[xx]); e1v = imax(e1v, sm.e1[xx]); e2v = imax(e2v, sm.e2[xx]); }
+                            sm.h[xx] = hv; sm.e1[xx] = e1v; sm.e2[xx] = e2v;
+                        }
+                    }
+                }
+                __syncwarp();
+            } else if (beg + 32 * cr + 2 - cbase > WIN) {        // lane blocks reach up to column beg + 32*CR - 1
+                // the band reached the end of the window: move columns beg-1 .. ppe+1 (the previous row and its guards) to the front
+                const i32 nbase = imax(beg - 1, 0) & ~3;
+                const i32 shift = nbase - cbase;                 // > 0
+                const i32 lo = imax(beg - 1, 0), hiq = ppe + 1;
+                const i32 hi_all = imax(hiq, qfill);
+                for (i32 j0 = lo; j0 <= hi_all; j0 += 32) {
+                    const i32 j = j0 + (i32)lane;
+                    const int xs = j - cbase + LPAD;
+                    i32 a = 0, c = 0, d = 0; u32 qq = 0;
+                    if (j <= hiq) { a = sm.h[xs]; c = sm.e1[xs]; d = sm.e2[xs]; }
+                    if (j <= qfill) qq = sm.q[xs];
+                    __syncwarp();
+                    if (j <= hiq) { sm.h[xs - shift] = a; sm.e1[xs - shift] = c; sm.e2[xs - shift] = d; }
+                    if (j <= qfill) sm.q[xs - shift] = (u8)qq;
+                    __syncwarp();
+                }
+                cbase = nbase;
+                if (qfill < lo - 1) qfill = lo - 1;
+            }
+            // query bytes of the columns this row can touch (lane blocks may reach past end; those cells are masked).  Staged
+            // 128 columns ahead, so the global loads are off the critical path of all but one row in ~100
+            {
+                const i32 need_q = imin(end + 1, qlen);
+                if (need_q > qfill) {
+                    const i32 upto = imin(imin(need_q + 128, qlen), cbase + WIN - 1);
+                    for (i32 j = qfill + 1 + (i32)lane; j <= upto; j += 32) sm.q[j - cbase + LPAD] = j >= 1 ? q[j - 1] : (u8)0;
+                    qfill = upto;
+                }
+            }
+            __syncwarp();
+            const i32 x0 = beg - cbase + LPAD;
+            LongRowOut ro;
+            ro = long_row(K, lane, cr, beg, end, x0, base, ref, sm, tr);
+            // a reachable cell further than int16 below the row reference cannot be encoded
+            if (ro.lmin != INT_MAX && ro.lmin - ref < -32000) { status = VGA_ALN_UNSUPPORTED; break; }
+            lpos = ro.lpos; rpos = ro.rpos; mxrow = ro.mx;
+            ppb = beg; ppe = end;
+            if (meta & 0x400u) {
+                // last row of its node: it may be a predecessor of later nodes' first rows
+                if (lane == 0) {
+                    int4* dst = (int4*)(b.nd_state + nb + s);
+                    dst[0] = make_int4(beg, end, lpos, rpos);
+                    dst[1] = make_int4(mxrow, 0, 0, 0);
+                }
+                s++; o = 0;
+            } else o++;
+        }
+        // ---- result record
+        i32 best = INT_MIN;
+        u32 bs = 0xffffffffu;
+        if (status == VGA_ALN_OK) {
+            // global end: sink predecessors (nodes without successors, ascending) that reach column qlen
+            const u32* __restrict__ rs = b.nd_row_start + nb;
+            const RowInfo* __restrict__ rows = b.rows + row_base;
+            __syncwarp();
+            for (u32 s0 = 0; s0 < S; s0 += 32) {
+                const u32 sx = s0 + lane;
+                i32 h = INT_MIN;
+                if (sx < S && b.nd_first_succ[nb + sx] < 0) {
+                    const RowInfo ri = rows[rs[sx + 1] - 1];
+                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - trace_col0(ri.beg))]);
+                }
+                const i32 mx = __reduce_max_sync(FULLW, h);
+                if (mx > best) {                             // strict: the first node wins ties
+                    best = mx;
+                    bs = (u32)__reduce_min_sync(FULLW, h == mx ? (i32)sx : INT_MAX);
+                }
+            }
+            if (bs == 0xffffffffu) status = VGA_ALN_EMPTY;
+        }
+        if (lane == 0) {
+            AlignItem* out = b.items + w;
+            out->status = status;
+            out->score = status == VGA_ALN_OK ? best : 0;
+            out->end_node = bs;
+            out->cells = cells;
+            out->n_runs = 0; out->n_path = 0; out->path_len = 0; out->start_off = 0; out->end_off = 0; out->n_aligned = 0;
+        }
+        __syncwarp();
+    }
+}
+
+int launch_poa_fill_long(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
+    if (b.n_items == 0) return 0;
+    int per_sm = 0;
+    const size_t smem_bytes = (size_t)PL_WARPS * sizeof(LongSmem);
+    static bool attr_set = false;
+    if (!attr_set) {
+        VGA_CUDA(cudaFuncSetAttribute(poa_fill_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        attr_set = true;
+    }
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, poa_fill_long_kernel, PL_WARPS * 32, smem_bytes);
+    if (per_sm < 1) per_sm = 1;
+    long long ctas = (long long)n_sms * per_sm;
+    const long long need = ((long long)b.n_items + PL_WARPS - 1) / PL_WARPS;
+    if (ctas > need) ctas = need;
+    if (ctas < 1) ctas = 1;
+    poa_fill_long_kernel<<<(unsigned)ctas, PL_WARPS * 32, smem_bytes, st>>>(ix, b);
+    return 1;
+}
+
+}  // namespace vga

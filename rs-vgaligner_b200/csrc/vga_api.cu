@@ -631,13 +631,19 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u64 est_total = 0;
     u64 sum_rows = 0, sum_q = 0;
     {
+        u64 n_long = 0;
+        for (u32 i = 0; i < NI; i++) n_long += poa_short_ok(h_meta[NI + i], h_meta[i], P) ? 0 : 1;
+        poa_set_long_mode(n_long, w->n_sms);
+    }
+    {
         const int NB = 48;
         std::vector<u32> key(NI), cnt((size_t)NCLS * NB + 1, 0);
         for (u32 i = 0; i < NI; i++) {
             const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
             const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
             const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
-            est[i] = (u64)(nrows * (west + 12));           // rows are stored from an 8-column boundary (trace_col0)
+            // rows are stored from an 8-column boundary (trace_col0); no kernel computes a band wider than 1024 columns
+            est[i] = (u64)(nrows * (std::min<i64>(west, 1024) + 12));
             if (qlen < 256) { if (qlen > (i64)pb.qmax_short) pb.qmax_short = (i32)qlen; sum_rows += (u64)nrows; sum_q += (u64)qlen; }
             est_total += est[i];
             const int ci = poa_class_for(qlen, nrows, west, P);

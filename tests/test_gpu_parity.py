@@ -155,6 +155,20 @@ def test_synthetic_long_reads(synth):
     assert (g.aln_status == vg.ALN_OK).sum() >= 12
 
 
+@pytest.mark.parametrize("family", ["0", "1"])
+def test_long_read_kernel_families(synth, monkeypatch, family):
+    """Both fill kernels for alignments outside the short-read classes — register-resident SLIDE instances (0) and the
+    shared-memory kernel with work proportional to the band (1) — on 10 kb, 3 kb and 1 kb reads (incl. several chains
+    per read); the library picks one per batch by item count, the test forces each."""
+    monkeypatch.setenv("VGA_POA_LONG", family)
+    for n, length, err, kw in ((16, 10000, (0.04, 0.03, 0.03), {}), (60, 3000, (0.03, 0.02, 0.02), {}),
+                               (200, 1000, (0.03, 0.01, 0.01), dict(best_n=3, min_anchors=2))):
+        reads = vg.simulate_reads(synth, n, length, *err, 0.1, 11)
+        g, o = both(synth, reads, **kw)
+        check_all(g, o)
+        assert (g.aln_status == vg.ALN_OK).sum() >= n // 3
+
+
 def test_medium_reads_and_best_n(synth):
     reads = vg.simulate_reads(synth, 300, 1000, 0.03, 0.01, 0.01, 0.0, 9)
     g, o = both(synth, reads, best_n=3, min_anchors=2)
