@@ -9,7 +9,7 @@
 //   * one warp per (read, chain); the work of a row is proportional to ITS band: the row uses the smallest block size
 //     CR of {5,9,13,17,25,33} with 32 lanes x CR columns >= band, lane l computes columns [beg + l*CR, +CR) — CR is odd
 //     so that the 32 lanes, CR int32 words apart, hit 32 different shared-memory banks;
-//   * since that mapping moves from row to row, the previous row (H, E1', E2' as int32) lives in shared memory in a
+//   * since that mapping moves from row to row, the previous row (H as int32, E1'/E2' as one byte of deltas to H) lives in shared memory in a
 //     window of WIN columns that follows the band: buffer index = column - cbase + PAD.  The window is re-anchored
 //     (data moved to the front) when the band reaches its end, and re-built on rows whose predecessor is not the
 //     previous row.  Out-of-band cells hold -inf plus one guard cell per side, so readers need no band test;
@@ -24,7 +24,7 @@
 
 namespace vga {
 
-static const int PL_WARPS = 2;              // warps per CTA (17 KB of shared memory each)
+static const int PL_WARPS = 2;              // warps per CTA (7.8 KB of shared memory each)
 static const u64 LONG_POOL_CHUNK = 8192;    // trace words a warp takes from the pool per refill
 static const int LPAD = 8;                  // buffer index of column cbase (column cbase-1 .. are guards)
 static const int WIN = 1280;                // columns of the window (bands are at most 1024 + the odd block size slack)
@@ -36,8 +36,9 @@ __device__ __forceinline__ i32 imin(i32 a, i32 b) { return a < b ? a : b; }
 __device__ __forceinline__ i32 sext16(u32 w) { return (i32)(short)(w & 0xffffu); }
 
 struct LongSmem {
-    i32 h[LBUF], e1[LBUF], e2[LBUF];      // previous row; updated in place (loads precede the warp's scan, stores follow it)
-    i32 hh[LBUF];                         // Hhat of the row in progress (sweep 1 -> sweep 2)
+    i32 h[LBUF];                          // H of the previous row; updated in place (loads precede the warp's scan, stores follow it)
+    u8 dd[LBUF];                          // E1' - (H - oe1) in bits 0..2 and E2' - (H - oe2) in bits 3..7 of the same cell: both
+                                          // are in [0, o] for every reachable cell, also after a predecessor merge
     u8 q[LBUF];                           // query byte of column j (base j-1) at the same index
 };
 
@@ -49,27 +50,39 @@ struct LongRowOut { i32 mx, lpos, rpos, lmin; };
 // last band cell and never reaches the row maximum (e1, e2 >= 1).  CR is a run-time value and the column loops are
 // NOT unrolled per block size: sweep 2 recomputes Hhat and the lane-local F scan of sweep 1 instead of keeping them in
 // per-column registers, so there is ONE small loop body for every band width (a version with an unrolled body per
-// block size spent 60 % of its cycles waiting for instruction fetch).
+// block size spent 60 % of its cycles waiting for instruction fetch) and 6 bytes of shared memory per window column.
+// SRC: the previous row is the virtual source row, whose E is -inf except in column 0 (not expressible as H + delta).
+template <bool SRC>
 __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32 CR, i32 beg, i32 end, i32 x0, u32 base, i32 ref,
                                                LongSmem& sm, u32* __restrict__ tr) {
     const i32 j0 = beg + (i32)lane * CR;
     const i32 idx = x0 + (i32)lane * CR;
     const i32 thi = end - j0;                              // column t of the lane is in the band iff t <= thi
-    const i32* ph = sm.h + idx;
-    const i32* pe1 = sm.e1 + idx;
-    const i32* pe2 = sm.e2 + idx;
-    const u8* pq = sm.q + idx;
-    // ---- sweep 1: Hhat = max(M, E1, E2) (kept in the scratch plane) and the lane-local part of the F scans
-    i32* const shh = sm.hh + idx;
+    i32* const sh = sm.h + idx;
+    u8* const sd = sm.dd + idx;
+    const u8* const pq = sm.q + idx;
+    const i32 hleft = sh[-1];
+    // E1, E2 arriving from the previous row at column t: H_old - oe + delta
+    auto e_of = [&](i32 ho, u32 dv, i32 t, i32& x1, i32& x2) {
+        if (SRC) {
+            const bool c0 = j0 + t == 0;
+            x1 = c0 ? -K.oe1 : POA_NEG_INF; x2 = c0 ? -K.oe2 : POA_NEG_INF;
+        } else {
+            x1 = ho - K.oe1 + (i32)(dv & 7u); x2 = ho - K.oe2 + (i32)(dv >> 3);
+        }
+    };
+    // ---- sweep 1: lane-local part of the F scans over Hhat = max(M, E1, E2)
     i32 run1 = POA_DEEP, run2 = POA_DEEP;
     {
-        i32 hd = ph[-1];
+        i32 hd = hleft;
 #pragma unroll 4
         for (i32 t = 0; t < CR; t++) {
+            const i32 ho = sh[t];
+            i32 x1, x2;
+            e_of(ho, sd[t], t, x1, x2);
             const i32 m = hd + ((u32)pq[t] == base ? K.smatch : K.smis);
-            const i32 hh = t <= thi ? __vimax3_s32(m, pe1[t], pe2[t]) : POA_DEEP;
-            hd = ph[t];
-            shh[t] = hh;
+            const i32 hh = t <= thi ? __vimax3_s32(m, x1, x2) : POA_DEEP;
+            hd = ho;
             run1 = __viaddmax_s32(run1, -K.e1, hh - K.oe1);
             run2 = __viaddmax_s32(run2, -K.e2, hh - K.oe2);
         }
@@ -93,13 +106,17 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
     i32 hprev_new = 0;                       // new H of column t-1
     u32 w0 = 0; i32 f1_0 = 0, f2_0 = 0;      // column 0: its F fields need the left lane's last new H
     u32* const trl = tr + lane * CR;
-    i32* const sh = sm.h + idx; i32* const s1p = sm.e1 + idx; i32* const s2p = sm.e2 + idx;
     {
+        i32 hd = hleft;
         run1 = POA_DEEP; run2 = POA_DEEP;
 #pragma unroll 2
         for (i32 t = 0; t < CR; t++) {
-            const i32 x1 = s1p[t], x2 = s2p[t];
-            const i32 hh = shh[t];
+            const i32 ho = sh[t];
+            i32 x1, x2;
+            e_of(ho, sd[t], t, x1, x2);
+            const i32 m = hd + ((u32)pq[t] == base ? K.smatch : K.smis);
+            const i32 hh = t <= thi ? __vimax3_s32(m, x1, x2) : POA_DEEP;
+            hd = ho;
             const i32 f1 = __viaddmax_s32(cin1, -K.e1 * t, run1), f2 = __viaddmax_s32(cin2, -K.e2 * t, run2);
             const i32 h = imax(__vimax3_s32(hh, f1, f2), POA_DEEP);
             run1 = __viaddmax_s32(run1, -K.e1, hh - K.oe1);
@@ -107,6 +124,7 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
             const i32 d1 = __viaddmax_s32(x1, K.o1 - h, 0);          // E1' - (H - oe1) = max(E1 - e1 - H + oe1, 0)
             const i32 d2 = __viaddmax_s32(x2, K.o2 - h, 0);
             u32 hi = (u32)d2 * 8u + (u32)d1;
+            const u32 dnew = hi;
             if (t > 0) {
                 hi = (u32)__viaddmax_s32(f1, 1 + K.oe1 - hprev_new, 0) * 256u + hi;
                 hi = (u32)__viaddmax_s32(f2, 1 + K.oe2 - hprev_new, 0) * 2048u + hi;
@@ -116,8 +134,7 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
             hprev_new = h;
             if (t <= thi) {
                 sh[t] = h;
-                s1p[t] = d1 + h - K.oe1;
-                s2p[t] = d2 + h - K.oe2;
+                sd[t] = (u8)dnew;
                 if (t > 0) trl[t] = wd;
                 const i32 hk = imax(h, -(1 << 24)) * 64;             // reachable scores are far above -2^24
                 kl = imax(kl, hk + 63 - t);
@@ -131,9 +148,10 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
         if (lane > 0) w0 += ((u32)imax(f1_0 + 1 + K.oe1 - hl, 0) << 24) + ((u32)imax(f2_0 + 1 + K.oe2 - hl, 0) << 27);
         if (0 <= thi) trl[0] = w0;
     }
-    // guards: H(beg-1) = -inf (diagonal of column beg in the next row), E'(end+1) = -inf (vertical of column end+1)
+    // guards: H(beg-1) = -inf (diagonal of column beg in the next row) and H(end+1) = -inf (E'(end+1) = H - oe + delta, the
+    // vertical of column end+1; as a diagonal it only serves column end+2, which is outside the next band)
     if (lane == 0) sm.h[x0 - 1] = POA_NEG_INF;
-    if (lane == 1) { sm.e1[x0 + (end - beg) + 1] = POA_NEG_INF; sm.e2[x0 + (end - beg) + 1] = POA_NEG_INF; }
+    if (lane == 1) sm.h[x0 + (end - beg) + 1] = POA_NEG_INF;
     // ---- row maximum and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i)
     LongRowOut o;
     const i32 lmax = kl == INT_MIN ? INT_MIN : (kl >> 6);
@@ -156,7 +174,6 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
     LongConst K;
     K.e1 = b.e1; K.e2 = b.e2; K.oe1 = b.o1 + b.e1; K.oe2 = b.o2 + b.e2; K.o1 = b.o1; K.o2 = b.o2;
     K.smatch = b.match; K.smis = -b.mismatch;
-    const i32 oe1 = K.oe1, oe2 = K.oe2;
     u64 pool_cur = 0, pool_end = 0;                 // this warp's current chunk of the trace pool (words)
     for (;;) {
         // ---- next (read, chain) of the work list
@@ -239,13 +256,12 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
                 qfill = cbase - 1;
                 const i32 jlo = imax(beg - 1, 0);
                 if (lane == 0 && cbase == 0) sm.h[LPAD - 1] = POA_NEG_INF;           // column -1: M(i,0) does not exist
-                if (kind == 1) {          // virtual source row
+                if (kind == 1) {          // virtual source row: H only, its E is handled by the SRC instance of the row body
                     for (i32 j = jlo + (i32)lane; j <= end + 1; j += 32) {
                         const bool in0 = j <= end0;
                         const int x = j - cbase + LPAD;
                         sm.h[x] = !in0 ? POA_NEG_INF : j == 0 ? 0 : imax(-(b.o1 + b.e1 * j), -(b.o2 + b.e2 * j));
-                        sm.e1[x] = j == 0 ? -oe1 : POA_NEG_INF;
-                        sm.e2[x] = j == 0 ? -oe2 : POA_NEG_INF;
+                        sm.dd[x] = 0;
                     }
                 } else {                  // merge of the predecessors' last rows, decoded from their trace words
                     const u32* __restrict__ pl = b.nd_pred + pred_base + po;
@@ -256,16 +272,24 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
                         const u32* __restrict__ tw = b.pool + (u64)pri.toff * 4;
                         const i32 pc0 = trace_col0(pbe.x);
                         for (i32 j = jlo + (i32)lane; j <= end + 1; j += 32) {
-                            i32 hv = POA_NEG_INF, e1v = POA_NEG_INF, e2v = POA_NEG_INF;
+                            // H = max over predecessors, E' = max over predecessors: kept as H and E' - (H - oe), which stays in
+                            // [0, o] (every predecessor has E' >= its H - oe, and E' - (H_max - oe) <= E' - (its H - oe) <= o)
+                            i32 hv = POA_NEG_INF, a1 = 0, a2 = 0;
                             if (j >= pbe.x && j <= pbe.y) {
                                 const u32 v = tw[j - pc0];
                                 hv = pri.ref + sext16(v);
-                                e1v = hv - oe1 + (i32)((v >> 16) & 7u);
-                                e2v = hv - oe2 + (i32)((v >> 19) & 31u);
+                                a1 = (i32)((v >> 16) & 7u); a2 = (i32)((v >> 19) & 31u);
                             }
                             const int xx = j - cbase + LPAD;
-                            if (x > 0) { hv = imax(hv, sm.h[xx]); e1v = imax(e1v, sm.e1[xx]); e2v = imax(e2v, sm.e2[xx]); }
-                            sm.h[xx] = hv; sm.e1[xx] = e1v; sm.e2[xx] = e2v;
+                            if (x > 0) {
+                                const i32 ho = sm.h[xx];
+                                const u32 dv = sm.dd[xx];
+                                const i32 hm = imax(ho, hv);
+                                // absolute E' of both sides relative to hm - oe (the oe cancels)
+                                const i32 n1 = imax(ho + (i32)(dv & 7u), hv + a1) - hm, n2 = imax(ho + (i32)(dv >> 3), hv + a2) - hm;
+                                hv = hm; a1 = imax(n1, 0); a2 = imax(n2, 0);
+                            }
+                            sm.h[xx] = hv; sm.dd[xx] = (u8)((u32)a1 | ((u32)a2 << 3));
                         }
                     }
                 }
@@ -279,11 +303,11 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
                 for (i32 j0 = lo; j0 <= hi_all; j0 += 32) {
                     const i32 j = j0 + (i32)lane;
                     const int xs = j - cbase + LPAD;
-                    i32 a = 0, c = 0, d = 0; u32 qq = 0;
-                    if (j <= hiq) { a = sm.h[xs]; c = sm.e1[xs]; d = sm.e2[xs]; }
+                    i32 a = 0; u32 c = 0, qq = 0;
+                    if (j <= hiq) { a = sm.h[xs]; c = sm.dd[xs]; }
                     if (j <= qfill) qq = sm.q[xs];
                     __syncwarp();
-                    if (j <= hiq) { sm.h[xs - shift] = a; sm.e1[xs - shift] = c; sm.e2[xs - shift] = d; }
+                    if (j <= hiq) { sm.h[xs - shift] = a; sm.dd[xs - shift] = (u8)c; }
                     if (j <= qfill) sm.q[xs - shift] = (u8)qq;
                     __syncwarp();
                 }
@@ -303,7 +327,8 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
             __syncwarp();
             const i32 x0 = beg - cbase + LPAD;
             LongRowOut ro;
-            ro = long_row(K, lane, cr, beg, end, x0, base, ref, sm, tr);
+            if (kind == 1) ro = long_row<true>(K, lane, cr, beg, end, x0, base, ref, sm, tr);
+            else ro = long_row<false>(K, lane, cr, beg, end, x0, base, ref, sm, tr);
             // a reachable cell further than int16 below the row reference cannot be encoded
             if (ro.lmin != INT_MAX && ro.lmin - ref < -32000) { status = VGA_ALN_UNSUPPORTED; break; }
             lpos = ro.lpos; rpos = ro.rpos; mxrow = ro.mx;

@@ -712,10 +712,12 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         std::vector<u32>& list = cls[ci];
         size_t pos = 0;
         int stall = 0;
-        // Waves are admitted on the a-priori estimate (widest band on every row).  Tried and dropped: scaling the estimate by
-        // the measured pool use of earlier waves (overflows and reruns cost more than fuller waves gain) and accounting the
-        // real use instead of the estimate (leaves room for tiny follow-up waves that cannot fill the machine).
-        const double scale = 1.0;
+        // Waves are admitted on the a-priori estimate (widest band on every row).  Long-read classes: measured pool use is
+        // 0.43-0.52 of that estimate wave after wave (C5), so they are admitted at 0.62 of it — fuller waves, fewer
+        // tracebacks; an overflow is handled like any other (IT_RETRY_POOL: trace, start the pool over, rerun).  Tried and
+        // dropped: learning the factor from the previous wave (overflows and reruns cost more than fuller waves gain) and
+        // accounting the real use instead of the estimate (leaves room for tiny follow-up waves that cannot fill the machine).
+        const double scale = ci >= 3 ? 0.62 : 1.0;
         auto cost = [&](u32 it) { return (u64)((double)(est[it] + est[it] / 4) * scale) + 64; };
         while (pos < list.size()) {
             // take a wave whose estimate fits what is left of the pool
