@@ -58,6 +58,7 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
     const i32 j0 = beg + (i32)lane * CR;
     const i32 idx = x0 + (i32)lane * CR;
     const i32 thi = end - j0;                              // column t of the lane is in the band iff t <= thi
+    const i32 n = imin(CR, thi + 1);                       // the lane's band columns (<= 0: none); only those are computed
     i32* const sh = sm.h + idx;
     u8* const sd = sm.dd + idx;
     const u8* const pq = sm.q + idx;
@@ -76,12 +77,12 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
     {
         i32 hd = hleft;
 #pragma unroll 4
-        for (i32 t = 0; t < CR; t++) {
+        for (i32 t = 0; t < n; t++) {
             const i32 ho = sh[t];
             i32 x1, x2;
             e_of(ho, sd[t], t, x1, x2);
             const i32 m = hd + ((u32)pq[t] == base ? K.smatch : K.smis);
-            const i32 hh = t <= thi ? __vimax3_s32(m, x1, x2) : POA_DEEP;
+            const i32 hh = __vimax3_s32(m, x1, x2);
             hd = ho;
             run1 = __viaddmax_s32(run1, -K.e1, hh - K.oe1);
             run2 = __viaddmax_s32(run2, -K.e2, hh - K.oe2);
@@ -110,12 +111,12 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
         i32 hd = hleft;
         run1 = POA_DEEP; run2 = POA_DEEP;
 #pragma unroll 2
-        for (i32 t = 0; t < CR; t++) {
+        for (i32 t = 0; t < n; t++) {
             const i32 ho = sh[t];
             i32 x1, x2;
             e_of(ho, sd[t], t, x1, x2);
             const i32 m = hd + ((u32)pq[t] == base ? K.smatch : K.smis);
-            const i32 hh = t <= thi ? __vimax3_s32(m, x1, x2) : POA_DEEP;
+            const i32 hh = __vimax3_s32(m, x1, x2);
             hd = ho;
             const i32 f1 = __viaddmax_s32(cin1, -K.e1 * t, run1), f2 = __viaddmax_s32(cin2, -K.e2 * t, run2);
             const i32 h = imax(__vimax3_s32(hh, f1, f2), POA_DEEP);
@@ -129,24 +130,23 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
                 hi = (u32)__viaddmax_s32(f1, 1 + K.oe1 - hprev_new, 0) * 256u + hi;
                 hi = (u32)__viaddmax_s32(f2, 1 + K.oe2 - hprev_new, 0) * 2048u + hi;
             }
-            const u32 wd = __byte_perm((u32)imax(h - ref, -32768), hi, 0x5410);
+            const i32 hrel = imax(h - ref, -32768);
+            const u32 wd = __byte_perm((u32)hrel, hi, 0x5410);
             if (t == 0) { w0 = wd; f1_0 = f1; f2_0 = f2; }
             hprev_new = h;
-            if (t <= thi) {
-                sh[t] = h;
-                sd[t] = (u8)dnew;
-                if (t > 0) trl[t] = wd;
-                const i32 hk = imax(h, -(1 << 24)) * 64;             // reachable scores are far above -2^24
-                kl = imax(kl, hk + 63 - t);
-                kr = imax(kr, hk + t);
-                lminu = min(lminu, (u32)(h + (1 << 27)));
-            }
+            sh[t] = h;
+            sd[t] = (u8)dnew;
+            if (t > 0) trl[t] = wd;
+            const i32 hk = hrel * 64;                                // the row maximum is far above ref - 32768
+            kl = imax(kl, hk + 63 - t);
+            kr = imax(kr, hk + t);
+            lminu = min(lminu, (u32)(h + (1 << 27)));
         }
     }
     {   // F fields of the lane's first column: relative to the left lane's last H
         const i32 hl = __shfl_up_sync(FULLW, hprev_new, 1);
         if (lane > 0) w0 += ((u32)imax(f1_0 + 1 + K.oe1 - hl, 0) << 24) + ((u32)imax(f2_0 + 1 + K.oe2 - hl, 0) << 27);
-        if (0 <= thi) trl[0] = w0;
+        if (n > 0) trl[0] = w0;
     }
     // guards: H(beg-1) = -inf (diagonal of column beg in the next row) and H(end+1) = -inf (E'(end+1) = H - oe + delta, the
     // vertical of column end+1; as a diagonal it only serves column end+2, which is outside the next band)
@@ -154,17 +154,18 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
     if (lane == 1) sm.h[x0 + (end - beg) + 1] = POA_NEG_INF;
     // ---- row maximum and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i)
     LongRowOut o;
-    const i32 lmax = kl == INT_MIN ? INT_MIN : (kl >> 6);
-    o.mx = __reduce_max_sync(FULLW, lmax);
-    o.lpos = __reduce_min_sync(FULLW, lmax == o.mx ? j0 + 63 - (kl & 63) : INT_MAX);
-    o.rpos = __reduce_max_sync(FULLW, lmax == o.mx ? j0 + (kr & 63) : -1);
+    const i32 lmax = kl == INT_MIN ? INT_MIN : (kl >> 6);                // relative to ref
+    o.mx = __reduce_max_sync(FULLW, lmax) + ref;
+    o.lpos = __reduce_min_sync(FULLW, lmax == o.mx - ref ? j0 + 63 - (kl & 63) : INT_MAX);
+    o.rpos = __reduce_max_sync(FULLW, lmax == o.mx - ref ? j0 + (kr & 63) : -1);
     const u32 mnu = __reduce_min_sync(FULLW, lminu);
     o.lmin = mnu >= 0x80000000u ? INT_MAX : (i32)mnu - (1 << 27);       // no reachable cell in the row: nothing to check
     return o;
 }
 
 __device__ __forceinline__ int long_pick_cr(i32 W) {
-    return W <= 160 ? 5 : W <= 288 ? 9 : W <= 416 ? 13 : W <= 544 ? 17 : W <= 800 ? 25 : W <= 1024 ? 33 : 0;
+    // columns per lane: the smallest odd count that covers the band (odd: lane stride of the int32 plane without bank conflicts)
+    return W > 1024 ? 0 : (((W + 31) >> 5) | 1) < 3 ? 3 : (((W + 31) >> 5) | 1);
 }
 
 __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex ix, PoaBuffers b) {
