@@ -52,7 +52,7 @@ enum {
 struct vga_workspace {
     cudaStream_t st = nullptr, st2 = nullptr;   // st2: result copies overlapped with the POA stage
     cudaEvent_t ev[12];
-    cudaEvent_t ev_copy = nullptr;
+    cudaEvent_t ev_copy = nullptr, ev_fork = nullptr, ev_join = nullptr;
     DBuf b[B_COUNT];
     int n_sms = 148;
     u32 scratch_words = 0;      // BFS scratch per warp currently allocated
@@ -67,6 +67,8 @@ void free_workspace(vga_index* ix) {
     for (auto& d : ix->ws->b) d.release();
     for (auto& e : ix->ws->ev) cudaEventDestroy(e);
     if (ix->ws->ev_copy) cudaEventDestroy(ix->ws->ev_copy);
+    if (ix->ws->ev_fork) cudaEventDestroy(ix->ws->ev_fork);
+    if (ix->ws->ev_join) cudaEventDestroy(ix->ws->ev_join);
     if (ix->ws->st2) cudaStreamDestroy(ix->ws->st2);
     if (ix->ws->st) cudaStreamDestroy(ix->ws->st);
     delete ix->ws;
@@ -80,6 +82,8 @@ static vga_workspace* workspace(vga_index* ix) {
     VGA_CUDA(cudaStreamCreate(&w->st));
     VGA_CUDA(cudaStreamCreateWithFlags(&w->st2, cudaStreamNonBlocking));
     VGA_CUDA(cudaEventCreateWithFlags(&w->ev_copy, cudaEventDisableTiming));
+    VGA_CUDA(cudaEventCreateWithFlags(&w->ev_fork, cudaEventDisableTiming));
+    VGA_CUDA(cudaEventCreateWithFlags(&w->ev_join, cudaEventDisableTiming));
     for (auto& e : w->ev) VGA_CUDA(cudaEventCreate(&e));
     cudaDeviceProp prop;
     VGA_CUDA(cudaGetDeviceProperties(&prop, ix->device));
@@ -215,6 +219,14 @@ __global__ void item_bases_kernel(AlignItem* items, u32 n, const u64* o0, const 
 __global__ void item_status_kernel(const AlignItem* items, const u32* work, u32 n, u32* status) {
     u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) status[i] = items[work[i]].status;
+}
+
+// total DP cells over all alignment items of a chunk (the GCUPS numerator), one atomic per warp
+__global__ void cells_sum_kernel(const AlignItem* items, u32 n, unsigned long long* total) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long v = i < n ? items[i].cells : 0ull;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(total, v);
 }
 
 // best_alignment_for_query (src/align.rs:34-55): stable sort by path_length descending, first wins.
@@ -441,20 +453,26 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     cb.n_chains = w->b[B_NCH].get<u32>(n); cb.n_members = w->b[B_NMEM].get<u32>(n);
     cb.clen = w->b[B_CLEN].get<u32>((u64)A + n); cb.cmem = w->b[B_CMEM].get<u32>(2ull * A + 2ull * n);
     cb.k = dv.k; cb.bandwidth = P.bandwidth; cb.max_gap = P.max_gap; cb.min_anchors = P.min_anchors;
-    if (n_big < n) c.launches += launch_chain(cb, true, st);
-    stage_check(st, "chain (fused)");
-    VGA_CUDA(cudaEventRecord(w->ev[2], st));
+    // The few reads with more anchors than the fused kernel takes are a long serial tail on a handful of warps: their CUB
+    // sort + DP go to the second stream FIRST (it is idle here) and run beside the fused kernel, which skips those reads.
     if (n_big > 0) {
+        VGA_CUDA(cudaEventRecord(w->ev_fork, st));
+        VGA_CUDA(cudaStreamWaitEvent(st2, w->ev_fork, 0));
         size_t tb = 0;
         cub::DeviceSegmentedSort::StableSortPairs(nullptr, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out, (int)A,
-                                                  (int)n_big, big_list + n, big_list + 2ull * n, st);
+                                                  (int)n_big, big_list + n, big_list + 2ull * n, st2);
         void* tmp = w->b[B_CUB].ensure(tb);
         VGA_CUDA(cub::DeviceSegmentedSort::StableSortPairs(tmp, tb, sb.sort_key_in, key_out, sb.sort_val_in, val_out,
-                                                           (int)A, (int)n_big, big_list + n, big_list + 2ull * n, st));
+                                                           (int)A, (int)n_big, big_list + n, big_list + 2ull * n, st2));
         c.launches += 3;
-        c.launches += launch_chain(cb, false, st);
-        stage_check(st, "chain (big reads)");
+        c.launches += launch_chain(cb, false, st2);
+        stage_check(st2, "chain (big reads)");
+        VGA_CUDA(cudaEventRecord(w->ev_join, st2));
     }
+    if (n_big < n) c.launches += launch_chain(cb, true, st);
+    stage_check(st, "chain (fused)");
+    if (n_big > 0) VGA_CUDA(cudaStreamWaitEvent(st, w->ev_join, 0));
+    VGA_CUDA(cudaEventRecord(w->ev[2], st));
     tl_mark("sort+chain queued");
     u64* chain_off = w->b[B_CHOFF].get<u64>(n + 1);
     u64* member_off = w->b[B_MEMOFF].get<u64>(n + 1);
@@ -821,18 +839,20 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         d2h_into(O.dbg_edges, (const u32*)d_edges, 2 * tots[3], st);
     }
     tl_mark("aln d2h queued");
-    // total cells over all items (GCUPS numerator)
+    // total cells over all items (GCUPS numerator): reduced on the device, 8 bytes come back
+    unsigned long long h_cells_total = 0;
     {
-        std::vector<u64> h_cells(NI);
-        VGA_CUDA(cudaMemcpy2DAsync(h_cells.data(), 8, (const char*)items + offsetof(AlignItem, cells), sizeof(AlignItem), 8, NI,
-                                   cudaMemcpyDeviceToHost, st));
-        VGA_CUDA(cudaStreamSynchronize(st));
-        for (u64 v : h_cells) R.stats.poa_cells += v;
+        unsigned long long* d_total = (unsigned long long*)(ctr + 6);
+        VGA_CUDA(cudaMemsetAsync(d_total, 0, 8, st));
+        cells_sum_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, d_total);
+        c.launches++;
+        VGA_CUDA(cudaMemcpyAsync(&h_cells_total, d_total, 8, cudaMemcpyDeviceToHost, st));
     }
     VGA_CUDA(cudaEventRecord(w->ev[7], st));
     VGA_CUDA(cudaStreamSynchronize(st2));
     VGA_CUDA(cudaStreamSynchronize(st));
     tl_mark("chunk done");
+    R.stats.poa_cells += h_cells_total;
     R.stats.n_alignments += NI;
     R.stats.ms_poa += ms_fill; R.stats.ms_trace += ms_trace;
     return true;

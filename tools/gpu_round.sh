@@ -20,3 +20,6 @@ timeout 600 ncu --set full --clock-control none --import-source on -k regex:poa_
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:seed_ -c 2 -o $O/${TAG}_full_seed_C4 -f \
   python bench.py --steps 1 --warmup 1 --workload C4 --reads 400000 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_full_seed.log 2>&1; echo "ncu seed rc=$?"
 cat $O/${TAG}_bench_C2.json | head -c 3000
+echo
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:poa_fill_long -c 1 -o $O/${TAG}_full_poa_long_C5 -f \
+  python bench.py --steps 1 --warmup 0 --workload C5 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_full_long.log 2>&1; echo "ncu long rc=$?"
