@@ -348,6 +348,7 @@ struct TCell { i32 h, e1, e2; bool ok; };
 // `spread` = threads per alignment (a power of two <= 32): only the first of them works.  With few, long
 // alignments a warp of 32 different tracebacks would serialise its divergent steps; spreading them over
 // warps trades idle lanes (there are plenty) for independent progress.
+template <bool FAST>
 __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffers b, u32 spread) {
     const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid & (spread - 1)) return;
@@ -415,6 +416,27 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
         const bool ismatch = q[j - 1] == (u8)(ri.meta >> 24);
         const i32 sc = ismatch ? b.match : -b.mismatch;
         const i32 jc = j;
+        // ---- the common step, on its own short path: a row with one predecessor, unrestricted state, and the diagonal cell
+        // explains H (an M op — the first test of the general path below, which stays the definition).  Its two loads, the
+        // diagonal word and the RowInfo one row further up, depend only on what the previous step left in registers, so
+        // the step costs ONE memory round trip; lanes that miss fall through to the general path.  Only when a warp holds few
+        // tracebacks (FAST, spread >= 4): with 16 or 32 per warp some lane misses on almost every step, and the warp then
+        // pays for both paths (measured: C5 62 -> 50 ms with it, C2 3.4 -> 4.2 ms when it was unconditional).
+        if (FAST && np == 1 && cur == ALL_OP && have_p && jc - 1 >= rip.beg && jc - 1 <= rip.end) {
+            const u32 wdf = word_at(rip, jc - 1);
+            const bool p1 = (rip.meta & 0xffffffu) == 1u;
+            RowInfo rnx = rip;
+            if (p1) rnx = rows[rip.prow];
+            if (rip.ref + sext16(wdf) + sc == hij) {
+                push(ismatch ? 0u : 1u);
+                n_aligned++; path_len++; j--;
+                if (ri.node != last_node) { path[--ppos] = ri.node; last_node = ri.node; }
+                if (!have_row) { end_off = ri.off; have_row = true; }
+                start_off = ri.off;
+                ri = rip; rip = rnx; have_p = p1; vij = wdf;
+                continue;
+            }
+        }
         // ---- issue every load of this step together
         if (np == 1 && !have_p) { rip = rows[ri.prow]; have_p = true; }
         u32 wl = 0, wd = 0, wv = 0;
@@ -578,8 +600,10 @@ int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st)
     // enough tracebacks to fill the machine: one per thread; otherwise spread them out (up to one per warp)
     u32 spread = 1;
     while (spread < 32 && (u64)b.n_items * spread * 2 <= 148ull * 2048) spread <<= 1;
+    if (const char* e = getenv("VGA_TRACE_SPREAD")) { const int v = atoi(e); if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) spread = (u32)v; }
     const u64 threads = (u64)b.n_items * spread;
-    poa_trace_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
+    if (spread >= 4) poa_trace_kernel<true><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
+    else poa_trace_kernel<false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
     return 1;
 }
 

@@ -478,7 +478,10 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u64* member_off = w->b[B_MEMOFF].get<u64>(n + 1);
     scan_to_offsets(c, cb.n_chains, chain_off, n);
     scan_to_offsets(c, cb.n_members, member_off, n);
-    const u64 NC = d2h_one(chain_off + n, st), NM = d2h_one(member_off + n, st);
+    u64 NC = 0, NM = 0;
+    VGA_CUDA(cudaMemcpyAsync(&NC, chain_off + n, 8, cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaMemcpyAsync(&NM, member_off + n, 8, cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaStreamSynchronize(st));
     ChainGather cg;
     cg.n_reads = n; cg.read_aoff = sb.read_aoff; cg.a_qb = sb.a_qb; cg.a_tb = sb.a_tb; cg.a_te = sb.a_te; cg.sidx = val_out;
     cg.f = cb.f; cg.n_chains = cb.n_chains; cg.clen = cb.clen; cg.cmem = cb.cmem; cg.chain_off = chain_off;
@@ -595,10 +598,9 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     item_sizes_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, sz, sz + NI, sz + 2ull * NI, sz + 3ull * NI);
     c.launches++;
     u64 tot[4];
-    for (int q = 0; q < 4; q++) {
-        scan_to_offsets(c, sz + (u64)q * NI, szo + (u64)q * (NI + 1), NI);
-        tot[q] = d2h_one(szo + (u64)q * (NI + 1) + NI, st);
-    }
+    for (int q = 0; q < 4; q++) scan_to_offsets(c, sz + (u64)q * NI, szo + (u64)q * (NI + 1), NI);
+    for (int q = 0; q < 4; q++) VGA_CUDA(cudaMemcpyAsync(&tot[q], szo + (u64)q * (NI + 1) + NI, 8, cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaStreamSynchronize(st));
     for (int q = 0; q < 4; q++)
         if (tot[q] >= (1ull << 32)) { set_error("alignment batch exceeds 32-bit offsets; use smaller batches"); throw CudaFail{VGA_ERR_UNSUPPORTED}; }
     tl_mark("sizes scanned");
@@ -606,22 +608,25 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     item_bases_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, szo, szo + (NI + 1), szo + 2ull * (NI + 1), szo + 3ull * (NI + 1),
                                                         d_nrows, d_nrows + NI, d_nrows + 2ull * NI);
     c.launches++;
-    sub.nd_handle = w->b[B_NDH].get<u32>(tot[0]); sub.nd_row_start = w->b[B_NDRS].get<u32>(tot[0]);
-    sub.nd_src = w->b[B_NDSRC].get<u32>(tot[0]); sub.nd_pred_off = w->b[B_NDPO].get<u32>(tot[0]);
-    sub.nd_pred = w->b[B_NDPRED].get<u32>(tot[1]); sub.nd_first_succ = w->b[B_NDFS].get<i32>(tot[0]);
-    sub.nd_remain_last = w->b[B_NDRL].get<i32>(tot[0]);
-    c.launches += launch_sub_fill(dv, sub, st);
-    u32* d_row_meta = w->b[B_ROWMETA].get<u32>(tot[2]);
-    c.launches += launch_sub_rowmeta(dv, sub, d_row_meta, st);
-    stage_check(st, "sub_fill");
+    // rows / read length / size class of every item go to the host now: the classification below runs on the host while
+    // sub_fill and sub_rowmeta run on the device
     HArr<u32> h_meta_pin;
     h_meta_pin.alloc(3ull * NI);
     struct PinGuard { HArr<u32>& a; ~PinGuard() { a.release(); } } h_meta_guard{h_meta_pin};
     const u32* h_meta = h_meta_pin.data();
     VGA_CUDA(cudaMemcpyAsync(h_meta_pin.data(), d_nrows, 12ull * NI, cudaMemcpyDeviceToHost, st));
-    VGA_CUDA(cudaEventRecord(w->ev[4], st));
+    sub.nd_handle = w->b[B_NDH].get<u32>(tot[0]); sub.nd_row_start = w->b[B_NDRS].get<u32>(tot[0]);
+    sub.nd_src = w->b[B_NDSRC].get<u32>(tot[0]); sub.nd_pred_off = w->b[B_NDPO].get<u32>(tot[0]);
+    sub.nd_pred = w->b[B_NDPRED].get<u32>(tot[1]); sub.nd_first_succ = w->b[B_NDFS].get<i32>(tot[0]);
+    sub.nd_remain_last = w->b[B_NDRL].get<i32>(tot[0]);
+    u32* d_row_meta = w->b[B_ROWMETA].get<u32>(tot[2]);
     VGA_CUDA(cudaStreamSynchronize(st));
-    tl_mark("sub_fill done, meta on host");
+    tl_mark("meta on host");
+    c.launches += launch_sub_fill(dv, sub, st);
+    c.launches += launch_sub_rowmeta(dv, sub, d_row_meta, st);
+    stage_check(st, "sub_fill");
+    VGA_CUDA(cudaEventRecord(w->ev[4], st));
+    tl_mark("sub_fill queued");
     // ---- K5 POA in waves
     PoaBuffers pb;
     memset(&pb, 0, sizeof(pb));
@@ -698,7 +703,9 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u32* d_work = w->b[B_WORK].get<u32>(NI);
     u32* d_twork = w->b[B_TWORK].get<u32>(NI);
     u32* d_status = w->b[B_STATUS].get<u32>(NI);
-    std::vector<u32> h_status(NI);
+    HArr<u32> h_status;                          // pinned: the per-wave status read is on the critical path between fill and traceback
+    h_status.alloc(NI);
+    PinGuard h_status_guard{h_status};
     float ms_fill = 0, ms_trace = 0;
     // Fill launches of all classes share the trace pool; the traceback of everything filled so far runs as ONE
     // launch when the pool is about to run out (or at the end), after which the pool starts over.
@@ -808,10 +815,9 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     c.launches++;
     const int nscan = dbg ? 4 : 2;
     u64 tots[4] = {0, 0, 0, 0};
-    for (int q = 0; q < nscan; q++) {
-        scan_to_offsets(c, cnts + (u64)q * n, offs + (u64)q * (n + 1), n);
-        tots[q] = d2h_one(offs + (u64)q * (n + 1) + n, st);
-    }
+    for (int q = 0; q < nscan; q++) scan_to_offsets(c, cnts + (u64)q * n, offs + (u64)q * (n + 1), n);
+    for (int q = 0; q < nscan; q++) VGA_CUDA(cudaMemcpyAsync(&tots[q], offs + (u64)q * (n + 1) + n, 8, cudaMemcpyDeviceToHost, st));
+    VGA_CUDA(cudaStreamSynchronize(st));
     u32* d_runs = w->b[B_RUNS].get<u32>(tots[0]);
     u64* d_path = w->b[B_PATH].get<u64>(tots[1]);
     gather_kernel<<<std::min<u32>((n + 7) / 8, 148 * 16), 256, 0, st>>>(items, sel, n, offs, offs + (n + 1), tbuf.out_runs,
