@@ -433,7 +433,8 @@ def main():
                      "counts": {k: s[k] for k in ("n_probes", "n_anchors", "n_chains", "n_alignments", "poa_cells", "lookup_bytes")}})
         if e2e:
             line["e2e"] = {"value": total_reads * K / (ms_e2e_max * 1e-3), "unit": "reads/s",
-                           "h2d_bytes_per_step": int(e2e[1]), "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": ms_e2e_max / K, "stage_ms": e2e[3]}
+                           "h2d_bytes_per_step": int(e2e[1]), "d2h_bytes_per_step": int(e2e[2]), "ms_per_step": ms_e2e_max / K, "stage_ms": e2e[3],
+                           "ms_steps": [round(x["ms_total"], 3) for x in acc_h]}
         if not args.no_cpu_baseline:
             from oracle import binding as orc       # CPU baseline leg: the one place bench.py executes oracle/
             n_sample = pick_cpu_sample(vg, orc, ix, reads, threads, args.cpu_seconds)

@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "common.cuh"
@@ -653,43 +654,84 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     std::vector<std::vector<u32>> cls(NCLS);
     u64 est_total = 0;
     u64 sum_rows = 0, sum_q = 0;
-    {
-        u64 n_long = 0;
-        for (u32 i = 0; i < NI; i++) n_long += poa_short_ok(h_meta[NI + i], h_meta[i], P) ? 0 : 1;
-        poa_set_long_mode(n_long, w->n_sms);
-    }
+    // Host side of the classification, spread over a few threads for big batches (1.2 M items took 11 ms on one thread —
+    // longer than the sub_fill kernels it hides behind).  Every thread owns a contiguous item range; per-thread
+    // histograms turn into per-thread write positions, so the lists come out exactly as the serial loop built them.
     {
         const int NB = 48;
-        std::vector<u32> key(NI), cnt((size_t)NCLS * NB + 1, 0);
-        for (u32 i = 0; i < NI; i++) {
-            const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
-            const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
-            const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
-            // rows are stored from an 8-column boundary (trace_col0); no kernel computes a band wider than 1024 columns
-            est[i] = (u64)(nrows * (std::min<i64>(west, 1024) + 12));
-            if (qlen < 256) { if (qlen > (i64)pb.qmax_short) pb.qmax_short = (i32)qlen; sum_rows += (u64)nrows; sum_q += (u64)qlen; }
-            est_total += est[i];
-            const int ci = poa_class_for(qlen, nrows, west, P);
-            const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
-            key[i] = (u32)(ci * NB + (NB - 1 - std::min(lb, NB - 1)));
-            cnt[key[i] + 1]++;
+        const size_t NK = (size_t)NCLS * NB;
+        const u32 NT = NI >= 200000 ? std::min<u32>(8, std::max<u32>(1, std::thread::hardware_concurrency())) : 1;
+        auto par = [&](auto&& fn) {
+            if (NT == 1) { fn(0u, 0u, NI); return; }
+            std::vector<std::thread> th;
+            for (u32 t = 0; t < NT; t++)
+                th.emplace_back([&fn, t, NT, NI]() { fn(t, (u32)((u64)NI * t / NT), (u32)((u64)NI * (t + 1) / NT)); });
+            for (auto& x : th) x.join();
+        };
+        std::vector<u64> part((size_t)NT * 8, 0);               // per thread: n_long, est_total, sum_rows, sum_q, qmax
+        par([&](u32 t, u32 i0, u32 i1) {
+            u64 nl = 0;
+            for (u32 i = i0; i < i1; i++) nl += poa_short_ok(h_meta[NI + i], h_meta[i], P) ? 0 : 1;
+            part[(size_t)t * 8] = nl;
+        });
+        u64 n_long = 0;
+        for (u32 t = 0; t < NT; t++) n_long += part[(size_t)t * 8];
+        poa_set_long_mode(n_long, w->n_sms);
+        std::vector<u32> key(NI), hist((size_t)NT * NK, 0);
+        par([&](u32 t, u32 i0, u32 i1) {
+            u32* h = hist.data() + (size_t)t * NK;
+            u64 et = 0, sr = 0, sq = 0, qm = 0;
+            for (u32 i = i0; i < i1; i++) {
+                const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
+                const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
+                const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
+                // rows are stored from an 8-column boundary (trace_col0); no kernel computes a band wider than 1024 columns
+                est[i] = (u64)(nrows * (std::min<i64>(west, 1024) + 12));
+                if (qlen < 256) { if ((u64)qlen > qm) qm = (u64)qlen; sr += (u64)nrows; sq += (u64)qlen; }
+                et += est[i];
+                const int ci = poa_class_for(qlen, nrows, west, P);
+                const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
+                key[i] = (u32)(ci * NB + (NB - 1 - std::min(lb, NB - 1)));
+                h[key[i]]++;
+            }
+            u64* pt = part.data() + (size_t)t * 8;
+            pt[1] = et; pt[2] = sr; pt[3] = sq; pt[4] = qm;
+        });
+        for (u32 t = 0; t < NT; t++) {
+            const u64* pt = part.data() + (size_t)t * 8;
+            est_total += pt[1]; sum_rows += pt[2]; sum_q += pt[3];
+            if ((i64)pt[4] > (i64)pb.qmax_short) pb.qmax_short = (i32)pt[4];
         }
-        for (size_t q = 1; q < cnt.size(); q++) cnt[q] += cnt[q - 1];
-        for (int ci = 0; ci < NCLS; ci++) cls[ci].resize(cnt[(size_t)(ci + 1) * NB] - cnt[(size_t)ci * NB]);
-        std::vector<u32> fill(cnt.begin(), cnt.end() - 1);
-        for (u32 i = 0; i < NI; i++) {
-            const u32 ci = key[i] / NB;
-            cls[ci][fill[key[i]]++ - cnt[(size_t)ci * NB]] = i;
+        // position of thread t's first item of key k inside its class list: items of smaller keys of the class, then the
+        // same key in the threads before t
+        std::vector<u32> start((size_t)NT * NK);
+        for (int ci = 0; ci < NCLS; ci++) {
+            u32 run = 0;
+            for (int kb = 0; kb < NB; kb++)
+                for (u32 t = 0; t < NT; t++) {
+                    const size_t k = (size_t)ci * NB + kb;
+                    start[(size_t)t * NK + k] = run;
+                    run += hist[(size_t)t * NK + k];
+                }
+            cls[ci].resize(run);
         }
+        par([&](u32 t, u32 i0, u32 i1) {
+            u32* st_t = start.data() + (size_t)t * NK;
+            for (u32 i = i0; i < i1; i++) cls[key[i] / NB][st_t[key[i]]++] = i;
+        });
     }
     // subgraphs much longer than their reads spend most rows at full band width: worth the 3-block step body (more registers)
     pb.nb_hint = sum_rows >= 3 * sum_q ? 3 : 2;
-    size_t free_b = 0, total_b = 0;
-    VGA_CUDA(cudaMemGetInfo(&free_b, &total_b));
     const u64 warp_slack = (u64)w->n_sms * 64 * 8192;
     u64 want_words = est_total + est_total / 4 + warp_slack;
-    u64 max_words = (u64)((free_b + w->b[B_POOL].cap) * 0.6) / 4;
-    if (want_words > max_words) want_words = max_words;
+    // The free-memory query only when the pool has to grow: cudaMemGetInfo takes a driver lock that NVML queries of
+    // another thread (a clock sampler, a monitoring agent) also take — measured as sporadic 10-90 ms stalls of this call.
+    if (want_words * 4 > w->b[B_POOL].cap) {
+        size_t free_b = 0, total_b = 0;
+        VGA_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        const u64 max_words = (u64)((free_b + w->b[B_POOL].cap) * 0.6) / 4;
+        if (want_words > max_words) want_words = max_words;
+    }
     if (want_words > (1ull << 34) - (1u << 20)) want_words = (1ull << 34) - (1u << 20);   // RowInfo.toff: u32 in 4-word units
     if (want_words < (1ull << 22)) want_words = 1ull << 22;
     // VGA_POOL_MAX_WORDS caps the pool (tests: forces several waves and the pool-overflow path on small inputs)
@@ -765,6 +807,17 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             stage_check(st, "poa_fill");
             R.stats.poa_launches++;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
+            // A wave that holds everything there is to align (the usual short-read batch) is traced right behind its fill,
+            // from the same work list, without the host round trip in between: the traceback skips every item whose status is
+            // not OK, and items a retry brings back are traced by the final flush as before.
+            bool traced_here = trace_list.empty() && pos == 0 && end == list.size();
+            for (int cj = ci + 1; cj < NCLS && traced_here; cj++) traced_here = cls[cj].empty();
+            if (traced_here) {
+                tbuf.n_items = nw; tbuf.work = d_work;
+                c.launches += launch_poa_trace(dv, tbuf, st);
+                stage_check(st, "poa_trace");
+                VGA_CUDA(cudaEventRecord(w->ev[10], st));
+            }
             item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
             c.launches++;
             queue_chain_d2h();          // host-side queueing (and any pinned allocation) hides behind the fill kernel
@@ -775,6 +828,12 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             float a = 0;
             cudaEventElapsedTime(&a, w->ev[8], w->ev[9]);
             ms_fill += a;
+            if (traced_here) {
+                float t = 0;
+                cudaEventElapsedTime(&t, w->ev[9], w->ev[10]);
+                ms_trace += t;
+                if (host_timeline()) fprintf(stderr, "[vga] poa trace (behind the fill): %u items, %.3f ms\n", nw, t);
+            }
             if (host_timeline()) fprintf(stderr, "[vga] poa fill class %d: %u items, %.3f ms (pool: %.2f of the estimate)\n", ci, nw, a,
                                          wave_est && used_now >= used_prev ? (double)(used_now - used_prev) / (double)wave_est : 0.0);
             used_prev = used_now;
@@ -785,7 +844,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                 const u32 it = list[pos + x];
                 if (h_status[x] == IT_RETRY_WIDER) { const int nc = poa_class_wider(ci); if (nc >= 0) cls[nc].push_back(it); else done++; }
                 else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
-                else { done++; if (h_status[x] == VGA_ALN_OK) trace_list.push_back(it); }
+                else { done++; if (h_status[x] == VGA_ALN_OK && !traced_here) trace_list.push_back(it); }
             }
             pos = end;
             if (!again.empty()) {

@@ -23,3 +23,10 @@ cat $O/${TAG}_bench_C2.json | head -c 3000
 echo
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:poa_fill_long -c 1 -o $O/${TAG}_full_poa_long_C5 -f \
   python bench.py --steps 1 --warmup 0 --workload C5 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_full_long.log 2>&1; echo "ncu long rc=$?"
+for W in C2 C4; do
+  env VGA_HOST_TIMELINE=1 timeout 300 python bench.py --steps 1 --warmup 2 --workload $W --no-cpu-baseline --no-e2e 2>&1 >/dev/null | grep "^\[vga" | tail -22 > $O/${TAG}_timeline_$W.txt
+done
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:chain_kernel -c 1 -o $O/${TAG}_full_chain_C2 -f \
+  python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_full_chain.log 2>&1; echo "ncu chain rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:poa_trace -c 1 -o $O/${TAG}_full_trace_C2 -f \
+  python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_full_trace.log 2>&1; echo "ncu trace rc=$?"
