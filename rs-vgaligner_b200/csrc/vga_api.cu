@@ -59,6 +59,7 @@ struct vga_workspace {
     u32 scratch_words = 0;      // BFS scratch per warp currently allocated
     u32 sub_warps = 0;
     bool scratch_zeroed = false;
+    u64 pool_capped_words = 0;  // size the trace pool was cut to by free memory (0: never cut)
     double gap_k = -1, gap_max = -1;
 };
 
@@ -726,11 +727,13 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u64 want_words = est_total + est_total / 4 + warp_slack;
     // The free-memory query only when the pool has to grow: cudaMemGetInfo takes a driver lock that NVML queries of
     // another thread (a clock sampler, a monitoring agent) also take — measured as sporadic 10-90 ms stalls of this call.
-    if (want_words * 4 > w->b[B_POOL].cap) {
+    // A pool that was already cut to what the device can spare keeps that size.
+    if (w->pool_capped_words && want_words >= w->pool_capped_words) want_words = w->pool_capped_words;
+    else if (want_words * 4 > w->b[B_POOL].cap) {
         size_t free_b = 0, total_b = 0;
         VGA_CUDA(cudaMemGetInfo(&free_b, &total_b));
         const u64 max_words = (u64)((free_b + w->b[B_POOL].cap) * 0.6) / 4;
-        if (want_words > max_words) want_words = max_words;
+        if (want_words > max_words) { want_words = max_words; w->pool_capped_words = max_words; }
     }
     if (want_words > (1ull << 34) - (1u << 20)) want_words = (1ull << 34) - (1u << 20);   // RowInfo.toff: u32 in 4-word units
     if (want_words < (1ull << 22)) want_words = 1ull << 22;
