@@ -97,6 +97,8 @@ seed_emit_kernel(DevIndex ix, u32 n, const u64* __restrict__ read_koff, const u3
         const u32 nk = (u32)(read_koff[r + 1] - kb);
         const u32 abase = read_aoff[r];
         if (read_aoff[r + 1] == abase) continue;
+        // (te, id) sort pairs only for the reads the CUB segmented sort handles; the fused chain kernel builds its own keys
+        const bool big = read_aoff[r + 1] - abase > CHAIN_SMAX;
         u32 carry = 0;
         for (u32 i0 = 0; i0 < nk; i0 += 32) {
             const u32 i = i0 + lane;
@@ -115,8 +117,7 @@ seed_emit_kernel(DevIndex ix, u32 n, const u64* __restrict__ read_koff, const u3
                 a_qb[abase + id] = i;                      // query_begin = i, query_end = i + k
                 a_tb[abase + id] = tb;
                 a_te[abase + id] = te;
-                sort_key[abase + id] = te;
-                sort_val[abase + id] = id;
+                if (big) { sort_key[abase + id] = te; sort_val[abase + id] = id; }
             }
             carry += __shfl_sync(0xffffffffu, incl, 31);
         }
