@@ -661,7 +661,9 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     {
         const int NB = 48;
         const size_t NK = (size_t)NCLS * NB;
-        const u32 NT = NI >= 200000 ? std::min<u32>(8, std::max<u32>(1, std::thread::hardware_concurrency())) : 1;
+        u32 NT = NI >= 200000 ? std::min<u32>(8, std::max<u32>(1, std::thread::hardware_concurrency())) : 1;
+        if (const char* e = getenv("VGA_CLASSIFY_THREADS")) { const int v = atoi(e); if (v >= 1 && v <= 64) NT = (u32)v; }   // tests
+        if (NT > NI) NT = 1;
         auto par = [&](auto&& fn) {
             if (NT == 1) { fn(0u, 0u, NI); return; }
             std::vector<std::thread> th;

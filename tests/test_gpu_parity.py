@@ -126,6 +126,20 @@ def test_small_trace_pool_waves_and_overflow(monkeypatch):
     assert g.stats["poa_launches"] >= 3
 
 
+@pytest.mark.gpu
+def test_threaded_item_classification(monkeypatch):
+    """Batches of >= 200 k alignments are classified on several host threads (per-thread histograms); forced here on a
+    small batch, with a pool small enough that the class lists are cut into waves: results must be those of the oracle."""
+    ix = vg.Index.build(fixture_path("graphs/2-DRB1-3123.gfa"), 11)
+    reads = vg.simulate_reads(ix, 3000, 150, 0.01, 0.0005, 0.0005, 0.1, 11)
+    monkeypatch.setenv("VGA_CLASSIFY_THREADS", "5")
+    monkeypatch.setenv("VGA_POOL_MAX_WORDS", str(148 * 64 * 8192 + 40_000_000))
+    g, o = both(ix, reads)
+    monkeypatch.delenv("VGA_CLASSIFY_THREADS")
+    monkeypatch.delenv("VGA_POOL_MAX_WORDS")
+    check_all(g, o)
+
+
 def test_cyclic_inverting_graph():
     """5-B3106 has back links and '-' orientations (reverse handles in the extension)."""
     ix = vg.Index.build(fixture_path("graphs/5-B3106.gfa"), 11)
