@@ -349,7 +349,7 @@ struct TCell { i32 h, e1, e2; bool ok; };
 // alignments a warp of 32 different tracebacks would serialise its divergent steps; spreading them over
 // warps trades idle lanes (there are plenty) for independent progress.
 template <bool FAST>
-__global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffers b, u32 spread, int pf) {
+__global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffers b, u32 spread) {
     const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid & (spread - 1)) return;
     const u32 idx = tid / spread;
@@ -409,23 +409,7 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     u32 vij = word_at(ri, j);
     RowInfo rip = ri;
     bool have_p = false;
-    // Software prefetch into L2.  A traceback is a chain of dependent DRAM reads (L2 hit rate 13 %: the trace pool is tens of
-    // GB); but consecutive DP rows of an alignment lie back to back in the pool chunk their fill warp took, so while the
-    // path climbs one row per step the pool index of the cell it visits moves by a nearly constant negative stride.  Every
-    // step that moved up a row prefetches the line `pf` strides further on, and the RowInfo records (contiguous per
-    // alignment) a few lines ahead.  A wrong guess (chunk boundary, bubble, gap run) costs one useless line.
-    long long last_ci = -1;
     while (!at_source && j > 0) {
-        if (pf > 0) {
-            const long long ci = (long long)((u64)ri.toff * 4 + (u32)(j - trace_col0(ri.beg)));
-            const long long dl = ci - last_ci;
-            if (last_ci >= 0 && dl < 0 && dl > -4096) {
-                const long long pi = ci + (long long)pf * dl;
-                if (pi >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(pool + pi));
-                if (ri.prow >= 16u && (ri.meta & 0xffffffu) == 1u) asm volatile("prefetch.global.L2 [%0];" ::"l"(rows + (ri.prow - 16u)));
-            }
-            last_ci = ci;
-        }
         const u32 np = ri.meta & 0xffffffu;
         const i32 hij = ri.ref + sext16(vij);
         const i32 e1ij = hij - oe1 + (i32)((vij >> 16) & 7u), e2ij = hij - oe2 + (i32)((vij >> 19) & 31u);
@@ -618,10 +602,10 @@ int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st)
     while (spread < 32 && (u64)b.n_items * spread * 2 <= 148ull * 2048) spread <<= 1;
     if (const char* e = getenv("VGA_TRACE_SPREAD")) { const int v = atoi(e); if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) spread = (u32)v; }
     const u64 threads = (u64)b.n_items * spread;
-    int pf = 4;                                   // rows of look-ahead of the L2 prefetch; VGA_TRACE_PF=0 turns it off (A/B)
-    if (const char* e = getenv("VGA_TRACE_PF")) { const int v = atoi(e); if (v >= 0 && v <= 64) pf = v; }
-    if (spread >= 4) poa_trace_kernel<true><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread, pf);
-    else poa_trace_kernel<false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread, pf);
+    // Tried and dropped: L2 prefetch of the diagonal trace word 2-8 rows ahead (consecutive rows lie back to back in a pool
+    // chunk, so the stride is predictable): C2 3.44 -> 3.55-3.70 ms, C4 14.0 -> 18.6-19.8 ms, C5 unchanged (gpurun_out/ab13).
+    if (spread >= 4) poa_trace_kernel<true><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
+    else poa_trace_kernel<false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
     return 1;
 }
 
