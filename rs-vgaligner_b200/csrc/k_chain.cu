@@ -10,6 +10,7 @@
 // CPU evaluation, not merely within a tolerance.
 #include <cfloat>
 #include <climits>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "internal.h"
@@ -42,6 +43,27 @@ __device__ __forceinline__ i32 score_pair(u32 qb_a, u32 tb_a, u32 te_a, double f
     return __double2int_rn(round(x));                                 // f64::round: half away from zero
 }
 
+// The same function without branches, for the two-pass body below: an invalid pair (or a lane without a predecessor,
+// `live` false) still runs the arithmetic on whatever it loaded — the gap is clamped into the table, F2I saturates — and
+// is replaced by INT_MIN at the end, so two evaluations can be interleaved by the scheduler.
+__device__ __forceinline__ i32 score_pair_nb(bool live, u32 qb_a, u32 tb_a, u32 te_a, double f_a, u32 qb_b, u32 tb_b, u32 te_b,
+                                             u32 k, u32 max_gap, const double* __restrict__ gapcost) {
+    live = live && qb_a < qb_b && te_a < te_b;
+    const u32 ql = qb_b - qb_a;
+    const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
+    const u32 ted = te_b - te_a;
+    const u32 tl = min(tbd, ted);
+    const u32 g = ql > tl ? ql - tl : tl - ql;
+    live = live && g <= max_gap;
+    const double gc = __ldg(gapcost + min(g, max_gap));
+    const u32 ml = min(min(ql, tl), k);
+    double x = __dadd_rn(f_a, (double)ml);
+    x = __dsub_rn(x, gc);
+    x = __dmul_rn(x, 1000.0);
+    const i32 r = __double2int_rn(round(x));
+    return live ? r : INT_MIN;
+}
+
 // r / 1000.0 correctly rounded, for an integer score r, without the division subroutine on the DP's critical path:
 // q0 = RN(r * RN(1/1000)), one FMA for the exact remainder, one FMA for the correction.  Equal to the IEEE quotient for
 // EVERY r in [-1e6, 2^31) — checked exhaustively on the host (tests/test_host.py::test_div1000_identity runs a stride of it).
@@ -57,7 +79,7 @@ __device__ __forceinline__ double div1000(i32 r) {
 // and the integer scores / predecessor distances of the whole read stay in shared memory for the
 // backtracking.  !FUSED: the reads of big_list (more anchors than that), already sorted by CUB.
 template <bool FUSED>
-__global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b) {
+__global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b, bool two_pass_on) {
     __shared__ u32 s_q[CHAIN_WARPS][RING], s_tb[CHAIN_WARPS][RING], s_te[CHAIN_WARPS][RING];
     __shared__ double s_f[CHAIN_WARPS][RING];
     __shared__ unsigned long long s_key[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
@@ -73,6 +95,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
     u8* pd = s_pd[FUSED ? wl : 0];
     const i32 rk = (i32)b.k * 1000;                                       // Anchor::new: max_chain_score = k
     const u32 n_work = FUSED ? b.n_reads : b.n_big;
+    const bool two_pass = two_pass_on && b.bandwidth > 32 && b.bandwidth <= 64;
     for (u32 x = warp; x < n_work; x += n_warps) {
         const u32 r = FUSED ? x : b.big_list[x];
         const u32 base = b.read_aoff[r];
@@ -119,6 +142,16 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b)
             const u32 qb_i = rq[si], tb_i = rtb[si], te_i = rte[si];
             i32 best = INT_MIN;
             u32 bestd = 0x7fffffffu;
+            if (two_pass) {
+                // bandwidth in (32, 64] (map_main.rs:103 passes 50): both halves of the window as straight-line code
+                const u32 d1 = lane + 1, d2 = lane + 33;
+                const u32 s1 = (i - d1) % RING, s2 = (i - d2) % RING;
+                const i32 a1 = score_pair_nb(d1 <= i, rq[s1], rtb[s1], rte[s1], rf[s1], qb_i, tb_i, te_i, b.k, b.max_gap, b.gapcost);
+                const i32 a2 = score_pair_nb(d2 <= b.bandwidth && d2 <= i, rq[s2], rtb[s2], rte[s2], rf[s2], qb_i, tb_i, te_i, b.k,
+                                             b.max_gap, b.gapcost);
+                if (a1 > best) { best = a1; bestd = d1; }
+                if (a2 > best) { best = a2; bestd = d2; }
+            } else
             for (u32 d0 = 0; d0 < b.bandwidth; d0 += 32) {               // j = i-1 down to max(0, i-bandwidth) :404-417
                 const u32 d = d0 + lane + 1;
                 if (d <= b.bandwidth && d <= i) {
@@ -255,8 +288,12 @@ int launch_chain_prep(const u64* aoff64, u32 n, u32* aoff32, u32* big_ctr, u32* 
 }
 
 int launch_chain(const ChainBuffers& b, bool fused, cudaStream_t st) {
-    if (fused) chain_kernel<true><<<grid_for_warps(b.n_reads, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b);
-    else if (b.n_big) chain_kernel<false><<<grid_for_warps(b.n_big, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b);
+    // the straight-line two-pass window body for bandwidths in (32, 64]: C2 chain 4.66 -> 4.08 ms, C4 35.0 -> 31.3 ms, parity
+    // green (gpurun_out/ab16); VGA_CHAIN_TWO_PASS=0 restores the generic loop (A/B)
+    const char* e = getenv("VGA_CHAIN_TWO_PASS");
+    const bool tp = e ? atoi(e) != 0 : true;
+    if (fused) chain_kernel<true><<<grid_for_warps(b.n_reads, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
+    else if (b.n_big) chain_kernel<false><<<grid_for_warps(b.n_big, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
     else return 0;
     return 1;
 }
