@@ -28,8 +28,9 @@ $(PKG)/libvgaligner_gpu.so: $(GPU_OBJS)
 
 # ---- host library (index build, reads, GAF writer) ----
 host: $(PKG)/libvga_host.so
-$(PKG)/libvga_host.so: $(HOST)/index_build.cpp $(HOST)/host_api.cpp $(HOST)/flat_index.h $(HOST)/vga_host.h include/vga.h
-	$(CXX) $(CXXFLAGS) -shared -o $@ $(HOST)/index_build.cpp $(HOST)/host_api.cpp
+HOST_SRC  := $(HOST)/index_build.cpp $(HOST)/host_api.cpp $(HOST)/gaf_writer.cpp
+$(PKG)/libvga_host.so: $(HOST_SRC) $(HOST)/flat_index.h $(HOST)/vga_host.h include/vga.h
+	$(CXX) $(CXXFLAGS) -O3 -pthread -shared -o $@ $(HOST_SRC)
 
 # ---- harness CLI mirroring `vgaligner index` / `vgaligner map` ----
 cli: $(PKG)/vga_map

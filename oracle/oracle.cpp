@@ -343,6 +343,9 @@ void nodes_edges(const Index& ix, const std::vector<u64>& handles, std::vector<s
 // the CUDA path must reproduce.
 // ---------------------------------------------------------------------------------------------
 const int32_t NEG_INF = -(1 << 29);
+// ORC_BAND_DUMP=<file>: one line per DP row (row, beg, end, #pred rows, pred is the previous row, qlen) — band statistics for
+// kernel design; single-threaded runs only
+static FILE* g_band_dump = getenv("ORC_BAND_DUMP") ? fopen(getenv("ORC_BAND_DUMP"), "w") : nullptr;
 
 struct AlnResult {
     uint8_t status = ST_PLACEHOLDER;
@@ -447,6 +450,7 @@ void poa_align(const std::vector<std::string>& labels, const std::vector<std::pa
                 if (h >= mx) rpos = beg + t;
             }
             R.cells += W;
+            if (g_band_dump) fprintf(g_band_dump, "%d %d %d %d %d %d\n", i, beg, end, (int)pr.size(), pr[0] == i - 1 ? 1 : 0, qlen);
             // adaptive band hints for the out rows (abPOA simd_abpoa_ada_max_i)
             auto hint = [&](int32_t t) {
                 mpr[t] = std::max(mpr[t], rpos + 1);

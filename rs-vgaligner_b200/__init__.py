@@ -97,6 +97,9 @@ def host_lib():
         L.vgah_reads_from_file.argtypes = [C.c_char_p]
         L.vgah_reads_simulate.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double,
                                           C.c_double, C.c_uint64]
+        L.vgah_reads_simulate_mt.restype = C.c_void_p
+        L.vgah_reads_simulate_mt.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double,
+                                             C.c_double, C.c_uint64, C.c_int]
         L.vgah_reads_free.argtypes = [C.c_void_p]
         L.vgah_reads_count.argtypes = [C.c_void_p]
         L.vgah_reads_count.restype = C.c_uint32
@@ -112,6 +115,9 @@ def host_lib():
         L.vgah_free_str.argtypes = [C.c_void_p]
         L.vgah_gaf.argtypes = [C.c_void_p, C.POINTER(VgaResultsView), C.c_void_p, C.c_int, u64p]
         L.vgah_gaf.restype = C.c_void_p
+        L.vgah_gaf_raw.argtypes = [C.c_void_p, C.POINTER(VgaResultsView), C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int,
+                                   C.c_int, u64p, u64p]
+        L.vgah_gaf_raw.restype = C.c_void_p
         _host = L
     return _host
 
@@ -282,8 +288,22 @@ class Reads:
         self.n = L.vgah_reads_count(self._h)
         self.offsets = _arr(L.vgah_reads_offsets(self._h), self.n + 1, np.uint64)
         nb = int(self.offsets[-1]) if self.n else 0
-        self.seqs = np.frombuffer(C.string_at(L.vgah_reads_seqs(self._h), nb), dtype=np.uint8).copy() if nb else np.zeros(0, np.uint8)
-        self.names = L.vgah_reads_names(self._h).decode().split("\n") if self.n else []
+        if nb:
+            self.seqs = np.ctypeslib.as_array(C.cast(L.vgah_reads_seqs(self._h), u8p), shape=(nb,)).copy()
+        else:
+            self.seqs = np.zeros(0, np.uint8)
+        self._names = None
+
+    @property
+    def names(self):
+        """read names (materialised on first use: simulated sets of millions of reads never need them as a list)"""
+        if self._names is None:
+            self._names = host_lib().vgah_reads_names(self._h).decode().split("\n") if self.n else []
+        return self._names
+
+    @names.setter
+    def names(self, value):
+        self._names = list(value)
 
     def seq(self, i):
         return self.seqs[int(self.offsets[i]):int(self.offsets[i + 1])].tobytes().decode()
@@ -308,6 +328,11 @@ def simulate_reads(index, n, length, sub=0.01, ins=0.0005, dele=0.0005, rev_frac
     return Reads(host_lib().vgah_reads_simulate(index._h, n, length, sub, ins, dele, rev_frac, seed))
 
 
+def simulate_reads_mt(index, n, length, sub=0.01, ins=0.0005, dele=0.0005, rev_frac=0.1, seed=77, first_id=0, threads=0):
+    """Same generator with one RNG stream per read (any sub-range reproducible on any rank), on all host cores."""
+    return Reads(host_lib().vgah_reads_simulate_mt(index._h, first_id, n, length, sub, ins, dele, rev_frac, seed, threads))
+
+
 def synth_gfa(backbone_len, site_every=100, seed=1):
     n = C.c_uint64()
     p = host_lib().vgah_synth_gfa(backbone_len, site_every, seed, C.byref(n))
@@ -324,6 +349,46 @@ _FIELDS = {
     "aln_start_off": ("n", np.uint32), "aln_end_off": ("n", np.uint32), "aln_n_aligned": ("n", np.uint32),
     "aln_score": ("n", np.int32), "aln_cells": ("n", np.uint64),
 }
+
+
+_VIEW_PTR = {"n_anchors": u32p, "chain_off": u64p, "chain_anchor_off": u64p, "ca_id": u32p, "ca_qb": u32p, "ca_tb": u32p,
+             "ca_te": u32p, "ca_score": f64p, "aln_status": u8p, "aln_chain": u32p, "aln_path_off": u64p, "aln_path": u64p,
+             "aln_run_off": u64p, "aln_runs": u32p, "aln_path_len": u32p, "aln_start_off": u32p, "aln_end_off": u32p,
+             "aln_n_aligned": u32p, "aln_score": i32p, "aln_cells": u64p}
+
+
+def view_from_arrays(res, n_reads):
+    """A VgaResultsView over numpy arrays carrying the C ABI's field names (e.g. results gathered from several ranks).
+    The arrays must stay alive while the view is used."""
+    v = VgaResultsView()
+    v.n_reads = n_reads
+    keep = []
+    for name, pt in _VIEW_PTR.items():
+        a = getattr(res, name, None)
+        if a is None or a.size == 0:
+            continue
+        a = np.ascontiguousarray(a)
+        keep.append(a)
+        setattr(v, name, a.ctypes.data_as(pt))
+    v.n_chains = max(0, len(res.chain_anchor_off) - 1)
+    v.n_chain_anchors = len(res.ca_qb)
+    v._keep = keep
+    return v
+
+
+def gaf_text(index, view, which, seqs, offsets, names=None, name_base=0, threads=0):
+    """GAF text of a result view (which=0 chains file, 1 alignments file) -> (text bytes, reads whose alignment failed)."""
+    n, nf = C.c_uint64(), C.c_uint64()
+    seqs = np.ascontiguousarray(seqs)
+    offsets = np.ascontiguousarray(offsets)
+    joined = None if names is None else "\n".join(names).encode()
+    p = host_lib().vgah_gaf_raw(index._h, C.byref(view), joined, name_base, seqs.ctypes.data_as(C.c_void_p),
+                                offsets.ctypes.data_as(C.c_void_p), which, threads, C.byref(n), C.byref(nf))
+    if not p:
+        raise VgaError("gaf: " + host_lib().vgah_last_error().decode())
+    s = C.string_at(p, n.value)
+    host_lib().vgah_free_str(p)
+    return s, nf.value
 
 
 class MapResults:
@@ -358,11 +423,8 @@ class MapResults:
 
     def gaf(self, which):
         """GAF text: which=0 `<prefix>-chains.gaf`, which=1 `<prefix>-alignments.gaf` (src/map.rs:135-184)."""
-        n = C.c_uint64()
-        p = host_lib().vgah_gaf(self.index._h, C.byref(self.view), self.reads._h, which, C.byref(n))
-        s = C.string_at(p, n.value).decode()
-        host_lib().vgah_free_str(p)
-        return s
+        s, self.n_failed = gaf_text(self.index, self.view, which, self.reads.seqs, self.reads.offsets, self.reads.names)
+        return s.decode()
 
     def free(self):
         if self._h is not None:

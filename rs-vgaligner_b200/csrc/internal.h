@@ -1,5 +1,6 @@
 // Internal declarations shared by the translation units of libvgaligner_gpu.so.
 #pragma once
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -7,6 +8,7 @@
 struct vga_workspace;
 
 struct vga_index {
+    std::mutex mu;           // one call per index at a time (the workspace is per index)
     int device = 0;
     void* d_blob = nullptr;
     vga::IndexHeader hdr;
@@ -16,7 +18,7 @@ struct vga_index {
 
 namespace vga {
 
-extern int g_device;
+extern thread_local int g_device;   // device selected by vga_init on this host thread
 void free_workspace(vga_index* ix);
 
 // ---- stage launchers (each returns the number of kernels it launched) -----------------------
@@ -103,14 +105,15 @@ struct PoaBuffers {
     u32* work_ctr;
     i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
     i32 nb_hint;             // pair kernel: blocks per lane and step worth instantiating (2 or 3), from rows per query base
+    i32 long_mode;           // kernel family of class 3 for this call (poa_long_mode)
     i32 qmax_short;          // longest read among the items of the short-read classes (sizes the pair kernel's shared memory)
 };
 // kernel classes: 0..1 = short reads on the 16x2 kernel (k_poa_pair.cu; 1 = with the per-row range check); 2 = short reads, 32 lanes
 // (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
-void poa_set_long_mode(u64 n_long_items, int n_sms);   // picks the long-read kernel family for the batch (k_poa.cu)
+int poa_long_mode(u64 n_long_items, int n_sms);   // long-read kernel family for the batch: 1 = shared-memory kernel, 0 = SLIDE (k_poa.cu)
 int poa_class_count();
-int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P);
-int poa_class_wider(int cls);    // -1: none
+int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode);
+int poa_class_wider(int cls, int long_mode);    // -1: none
 int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 int launch_poa_fill_short(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 bool poa_short_ok(i64 qlen, i64 nrows, const VgaParams& P);   // read short enough and scores within int16

@@ -540,23 +540,23 @@ static int g_pair = getenv("VGA_POA_PAIR") ? atoi(getenv("VGA_POA_PAIR")) : 1;
 static int g_pair_chk = getenv("VGA_POA_CHK") ? atoi(getenv("VGA_POA_CHK")) : 0;
 // long reads (and everything else that is not a short-read class) run on the shared-memory kernel of k_poa_long.cu as
 // class 3; VGA_POA_LONG=0 restores the register-resident SLIDE instances on classes 3..7 (A/B measurements)
-static int g_long = 1;
 // The shared-memory kernel wins on throughput (work proportional to the band, 64 registers), the register-resident
 // SLIDE instances on the latency of one alignment: a batch with only a few long alignments (the very long subgraphs of
-// 17-DRB1-3123-smooth: 1.5 k items, ~100 ms tail) stays on SLIDE.  Called once per batch before classification.
-void poa_set_long_mode(u64 n_long_items, int n_sms) {
+// 17-DRB1-3123-smooth: 1.5 k items, ~100 ms tail) stays on SLIDE.  Decided once per batch before classification and
+// carried in the call's PoaBuffers (no process-wide state: two host threads may map on two indexes at once).
+int poa_long_mode(u64 n_long_items, int n_sms) {
     const char* e = getenv("VGA_POA_LONG");            // read per batch: tests force either family
-    g_long = e ? atoi(e) : (n_long_items >= (u64)n_sms * 24 ? 1 : 0);
+    return e ? atoi(e) : (n_long_items >= (u64)n_sms * 24 ? 1 : 0);
 }
 static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
 int poa_class_count() { return 8; }
-int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
+int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode) {
     if (g_pair) {
         if (poa_pair_ok(qlen, nrows, P)) return 0;
         if (g_pair_chk && poa_pair_checked_ok(qlen, nrows, P)) return 1;
         if (poa_short_ok(qlen, nrows, P)) return 2;
     } else if (poa_short_ok(qlen, nrows, P)) return west <= (i64)g_short_w8 ? 0 : west <= 160 ? 1 : 2;
-    if (g_long) return 3;
+    if (long_mode) return 3;
     // SLIDE instances compute all 32*C columns of every row, so an item goes to the narrowest one its estimate allows
     if (west <= 256 - 8) return 3;
     if (west <= 384 - 12) return 4;
@@ -564,7 +564,7 @@ int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P) {
     if (west <= 768 - 24) return 6;
     return 7;
 }
-int poa_class_wider(int cls) { return (g_long && cls >= 3) ? -1 : cls < 7 ? cls + 1 : -1; }
+int poa_class_wider(int cls, int long_mode) { return (long_mode && cls >= 3) ? -1 : cls < 7 ? cls + 1 : -1; }
 
 template <int C, bool SLIDE>
 static void launch_fill(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
@@ -585,7 +585,7 @@ int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms,
         case 0: case 1: if (g_pair) return launch_poa_fill_pair(ix, b, cls, n_sms, st);
         // fall through
         case 2: return launch_poa_fill_short(ix, b, cls, n_sms, st);
-        case 3: if (g_long) return launch_poa_fill_long(ix, b, n_sms, st);
+        case 3: if (b.long_mode) return launch_poa_fill_long(ix, b, n_sms, st);
                 launch_fill<8, true>(ix, b, n_sms, st); break;
         case 4: launch_fill<12, true>(ix, b, n_sms, st); break;
         case 5: launch_fill<16, true>(ix, b, n_sms, st); break;

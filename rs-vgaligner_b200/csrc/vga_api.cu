@@ -679,7 +679,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         });
         u64 n_long = 0;
         for (u32 t = 0; t < NT; t++) n_long += part[(size_t)t * 8];
-        poa_set_long_mode(n_long, w->n_sms);
+        pb.long_mode = poa_long_mode(n_long, w->n_sms);
         std::vector<u32> key(NI), hist((size_t)NT * NK, 0);
         par([&](u32 t, u32 i0, u32 i1) {
             u32* h = hist.data() + (size_t)t * NK;
@@ -692,7 +692,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                 est[i] = (u64)(nrows * (std::min<i64>(west, 1024) + 12));
                 if (qlen < 256) { if ((u64)qlen > qm) qm = (u64)qlen; sr += (u64)nrows; sq += (u64)qlen; }
                 et += est[i];
-                const int ci = poa_class_for(qlen, nrows, west, P);
+                const int ci = poa_class_for(qlen, nrows, west, P, pb.long_mode);
                 const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
                 key[i] = (u32)(ci * NB + (NB - 1 - std::min(lb, NB - 1)));
                 h[key[i]]++;
@@ -847,7 +847,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             u32 done = 0;
             for (u32 x = 0; x < nw; x++) {
                 const u32 it = list[pos + x];
-                if (h_status[x] == IT_RETRY_WIDER) { const int nc = poa_class_wider(ci); if (nc >= 0) cls[nc].push_back(it); else done++; }
+                if (h_status[x] == IT_RETRY_WIDER) { const int nc = poa_class_wider(ci, pb.long_mode); if (nc >= 0) cls[nc].push_back(it); else done++; }
                 else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
                 else { done++; if (h_status[x] == VGA_ALN_OK && !traced_here) trace_list.push_back(it); }
             }
@@ -1033,6 +1033,7 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
         }
     }
     vga_results* R = new vga_results();
+    std::lock_guard<std::mutex> index_lock(ix->mu);      // calls on the same index are serialised (vga.h)
     try {
         VGA_CUDA(cudaSetDevice(ix->device));
         Ctx c;
@@ -1052,7 +1053,9 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
         if (n_reads > 0) {
             if (!d_seqs_in) {
                 for (u32 i = 0; i < n_reads; i++)
-                    if (seq_off[i + 1] < seq_off[i]) { set_error("seq_off not monotone"); delete R; return VGA_ERR_INVALID; }
+                    if (seq_off[i + 1] < seq_off[i] || seq_off[i + 1] - seq_off[i] >= (1ull << 32)) {
+                        set_error("seq_off not monotone (or a read of 2^32 bases or more)"); delete R; return VGA_ERR_INVALID;
+                    }
                 const u64 nb = seq_off[n_reads] - seq_off[0];
                 char* ds = c.ws->b[B_SEQS].get<char>(nb + 16);
                 u64* doff = c.ws->b[B_SEQOFF].get<u64>(n_reads + 1);
@@ -1066,7 +1069,11 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
                 h_off.resize(n_reads + 1);
                 VGA_CUDA(cudaMemcpyAsync(h_off.data(), d_off_in, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, c.st));
                 VGA_CUDA(cudaStreamSynchronize(c.st));
-                (void)n_bases_in;
+                for (u32 i = 0; i < n_reads; i++)
+                    if (h_off[i + 1] < h_off[i] || h_off[i + 1] - h_off[i] >= (1ull << 32)) {
+                        set_error("dev_seq_off not monotone (or a read of 2^32 bases or more)"); delete R; return VGA_ERR_INVALID;
+                    }
+                if (h_off[n_reads] > n_bases_in) { set_error("dev_seq_off runs past n_bases"); delete R; return VGA_ERR_INVALID; }
             }
             VGA_CUDA(cudaEventRecord(c.ws->ev[0], c.st));
             float th2d = 0;

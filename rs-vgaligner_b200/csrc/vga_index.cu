@@ -3,6 +3,7 @@
 // (src/index.rs:319-320): open addressing keyed by the 2-bit packed k-mer, exact membership,
 // identical positions in identical (table) order.  Only forward/forward positions are kept because
 // map_reads hard-codes only_forward=true (src/map.rs:62, src/chain.rs:154-156).
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -16,7 +17,10 @@ static thread_local std::string g_err;
 void set_error(const std::string& msg) { g_err = msg; }
 const char* get_error() { return g_err.c_str(); }
 
-int g_device = -1;
+// vga_init selects the device for the calling host thread (like cudaSetDevice) and records it as the process default for
+// threads that never called it.
+thread_local int g_device = -1;
+static std::atomic<int> g_default_device{-1};
 
 static inline u64 align_up(u64 x, u64 a) { return (x + a - 1) / a * a; }
 
@@ -70,7 +74,7 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
             u64 s = v->tab_start[p], e = v->tab_end[p];
             if (s == VGA_POS_DELIM && e == VGA_POS_DELIM) break;
             if (!(s & VGA_POS_REV) && !(e & VGA_POS_REV)) {
-                if (s >= L || e > L + 0 || e == 0) { set_error("k-mer position outside the linearisation"); return VGA_ERR_INVALID; }
+                if (s >= L || e > L || s >= e) { set_error("k-mer position outside the linearisation (or start >= end)"); return VGA_ERR_INVALID; }
                 ptb.push_back((u32)s); pte.push_back((u32)e); cnt++;
             }
             p++;
@@ -116,7 +120,10 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
         eidx[i] = (u32)v->node_ref[3 * i + 1];
         ein[i] = (u32)v->node_ref[3 * i + 2];
         if (i > 0 && (sidx[i] <= sidx[i - 1] || eidx[i] < eidx[i - 1])) { set_error("node_ref not increasing"); return VGA_ERR_INVALID; }
+        // incoming edges are the first edges_to_node entries of the node's run (src/index.rs:559-606)
+        if (i > 0 && ein[i - 1] > eidx[i] - eidx[i - 1]) { set_error("node_ref: edges_to_node exceeds the node's edge run"); return VGA_ERR_INVALID; }
     }
+    if (sidx[0] != 0 || eidx[0] != 0) { set_error("node_ref[0] must start at sequence / edge offset 0"); return VGA_ERR_INVALID; }
     if (sidx[N] != L || eidx[N] != v->n_edges) { set_error("node_ref end marker mismatch"); return VGA_ERR_INVALID; }
     u32* ed = (u32*)(b + hdr.off_edges);
     for (u64 i = 0; i < v->n_edges; i++) {
@@ -169,12 +176,14 @@ int vga_init(int device) {
     if (device < 0 || device >= n) { set_error("vga_init: device ordinal out of range"); return VGA_ERR_INVALID; }
     if (cudaSetDevice(device) != cudaSuccess) { set_error("cudaSetDevice failed"); return VGA_ERR_CUDA; }
     g_device = device;
+    g_default_device = device;
     return VGA_OK;
 }
 
 static int require_device() {
     if (g_device < 0) {
-        int rc = vga_init(0);
+        const int d = g_default_device.load();
+        int rc = vga_init(d < 0 ? 0 : d);
         if (rc != VGA_OK) return rc;
     }
     if (cudaSetDevice(g_device) != cudaSuccess) { set_error("cudaSetDevice failed"); return VGA_ERR_CUDA; }

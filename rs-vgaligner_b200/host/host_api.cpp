@@ -2,9 +2,12 @@
 #include "vga_host.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <fstream>
+#include <mutex>
+#include <thread>
 #include <sstream>
 #include <stdexcept>
 #include <string>
@@ -14,21 +17,34 @@
 
 using namespace vga;
 
+namespace vga {
+struct GafTables;
+const GafTables* gaf_tables_new(const FlatIndex& ix);
+void gaf_tables_free(const GafTables* t);
+char* gaf_format(const FlatIndex& ix, const GafTables& tb, const VgaResultsView* R, const char* names_joined, uint64_t name_base,
+                 const char* seqs, const uint64_t* off, int which, int threads, uint64_t* len, uint64_t* n_failed);
+}
+
 static thread_local std::string g_err;
 static void set_err(const std::string& s) { g_err = s; }
 
 struct vgah_index {
     FlatIndex ix;
     std::string keys;            // n_keys * k bytes
+    mutable std::once_flag gaf_once;
+    mutable const GafTables* gaf_tables = nullptr;     // position -> node tables of the GAF writer, built on first use
+    ~vgah_index() { if (gaf_tables) gaf_tables_free(gaf_tables); }
 };
 
 struct vgah_reads {
+    bool auto_names = false;     // names are "read<i>" and are not materialised (simulated sets of millions of reads)
     std::vector<std::string> names;
     std::string seqs;
     std::vector<uint64_t> off;   // n+1
     std::string names_joined;
     void finish() {
         names_joined.clear();
+        if (auto_names) return;
         for (size_t i = 0; i < names.size(); i++) { if (i) names_joined += '\n'; names_joined += names[i]; }
     }
 };
@@ -144,63 +160,79 @@ vgah_reads_t* vgah_reads_from_file(const char* path) {
     } catch (std::exception& e) { set_err(e.what()); return nullptr; }
 }
 
+// one simulated read: forward random walk from a uniform start base, error model, optional reverse complement.
+// Returns false when no long enough walk was found in 1000 attempts.
+static bool simulate_one(const FlatIndex& ix, const std::vector<uint32_t>& p2n, Rng& rng, uint32_t len, double sub, double ins,
+                         double del, double rev_frac, std::string& tmpl, std::string& read) {
+    const char* ACGT = "ACGT";
+    const uint64_t want_src = (uint64_t)len + len / 2 + 16;    // template long enough to survive deletions
+    for (int attempt = 0;; attempt++) {
+        if (attempt > 1000) return false;
+        tmpl.clear();
+        uint64_t pos = rng.below(ix.seq_len);
+        uint64_t id = p2n[pos];
+        bool dead = false;
+        while (tmpl.size() < want_src) {
+            uint64_t end = ix.seq_idx(id);
+            uint64_t take = std::min<uint64_t>(end - pos, want_src - tmpl.size());
+            tmpl.append(ix.seq_fwd, pos, take);
+            if (tmpl.size() >= want_src) break;
+            // forward out-edges of the forward handle that lead to forward handles
+            uint64_t b = ix.edge_idx(id - 1) + ix.edges_in(id - 1), e = ix.edge_idx(id);
+            uint64_t n_out = 0;
+            for (uint64_t x = b; x < e; x++) n_out += !(ix.edges[x] & 1);
+            if (n_out == 0) { dead = true; break; }
+            uint64_t pick = rng.below(n_out);
+            for (uint64_t x = b; x < e; x++)
+                if (!(ix.edges[x] & 1) && pick-- == 0) { id = ix.edges[x] >> 1; break; }
+            pos = ix.seq_idx(id - 1);
+        }
+        if (dead && tmpl.size() < (uint64_t)len) continue;
+        if (tmpl.find('N') != std::string::npos) continue;
+        // error model
+        read.clear();
+        size_t t = 0;
+        while (read.size() < len && t < tmpl.size()) {
+            double u = rng.uni();
+            if (u < ins) { read.push_back(ACGT[rng.below(4)]); continue; }
+            if (u < ins + del) { t++; continue; }
+            char c = tmpl[t++];
+            if (u < ins + del + sub) { char d; do { d = ACGT[rng.below(4)]; } while (d == c); c = d; }
+            read.push_back(c);
+        }
+        if (read.size() < len) continue;
+        break;
+    }
+    if (rng.uni() < rev_frac) {
+        std::string rc(read.size(), 'N');
+        for (size_t x = 0; x < read.size(); x++) {
+            char c = read[read.size() - 1 - x];
+            rc[x] = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : 'N';
+        }
+        read.swap(rc);
+    }
+    return true;
+}
+
+static void pos_to_node(const FlatIndex& ix, std::vector<uint32_t>& p2n) {
+    p2n.resize(ix.seq_len);
+    for (uint64_t id = 1; id <= ix.n_nodes; id++)
+        for (uint64_t p = ix.seq_idx(id - 1); p < ix.seq_idx(id); p++) p2n[p] = (uint32_t)id;
+}
+
 vgah_reads_t* vgah_reads_simulate(const vgah_index_t* h, uint32_t n, uint32_t len, double sub, double ins, double del,
                                   double rev_frac, uint64_t seed) {
     const FlatIndex& ix = h->ix;
     if (ix.seq_len == 0) { set_err("empty graph"); return nullptr; }
-    // position -> node id
-    std::vector<uint32_t> p2n(ix.seq_len);
-    for (uint64_t id = 1; id <= ix.n_nodes; id++)
-        for (uint64_t p = ix.seq_idx(id - 1); p < ix.seq_idx(id); p++) p2n[p] = (uint32_t)id;
-    Rng rng(seed * 0x9E3779B97F4A7C15ull + 12345);
+    std::vector<uint32_t> p2n;
+    pos_to_node(ix, p2n);
+    Rng rng(seed * 0x9E3779B97F4A7C15ull + 12345);       // ONE stream for the whole set (read i depends on reads < i)
     vgah_reads* r = new vgah_reads();
     r->off.push_back(0);
-    const char* ACGT = "ACGT";
-    const uint64_t want_src = (uint64_t)len + len / 2 + 16;    // template long enough to survive deletions
     std::string tmpl, read;
     for (uint32_t i = 0; i < n; i++) {
-        for (int attempt = 0;; attempt++) {
-            if (attempt > 1000) { set_err("read simulation cannot find a long enough walk"); delete r; return nullptr; }
-            tmpl.clear();
-            uint64_t pos = rng.below(ix.seq_len);
-            uint64_t id = p2n[pos];
-            bool dead = false;
-            while (tmpl.size() < want_src) {
-                uint64_t end = ix.seq_idx(id);
-                uint64_t take = std::min<uint64_t>(end - pos, want_src - tmpl.size());
-                tmpl.append(ix.seq_fwd, pos, take);
-                if (tmpl.size() >= want_src) break;
-                // forward out-edges of the forward handle that lead to forward handles
-                uint64_t b = ix.edge_idx(id - 1) + ix.edges_in(id - 1), e = ix.edge_idx(id);
-                std::vector<uint64_t> outs;
-                for (uint64_t x = b; x < e; x++) if (!(ix.edges[x] & 1)) outs.push_back(ix.edges[x] >> 1);
-                if (outs.empty()) { dead = true; break; }
-                id = outs[rng.below(outs.size())];
-                pos = ix.seq_idx(id - 1);
-            }
-            if (dead && tmpl.size() < (uint64_t)len) continue;
-            if (tmpl.find('N') != std::string::npos) continue;
-            // error model
-            read.clear();
-            size_t t = 0;
-            while (read.size() < len && t < tmpl.size()) {
-                double u = rng.uni();
-                if (u < ins) { read.push_back(ACGT[rng.below(4)]); continue; }
-                if (u < ins + del) { t++; continue; }
-                char c = tmpl[t++];
-                if (u < ins + del + sub) { char d; do { d = ACGT[rng.below(4)]; } while (d == c); c = d; }
-                read.push_back(c);
-            }
-            if (read.size() < len) continue;
-            break;
-        }
-        if (rng.uni() < rev_frac) {
-            std::string rc(read.size(), 'N');
-            for (size_t x = 0; x < read.size(); x++) {
-                char c = read[read.size() - 1 - x];
-                rc[x] = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : 'N';
-            }
-            read.swap(rc);
+        if (!simulate_one(ix, p2n, rng, len, sub, ins, del, rev_frac, tmpl, read)) {
+            set_err("read simulation cannot find a long enough walk"); delete r; return nullptr;
         }
         r->names.push_back("read" + std::to_string(i));
         r->seqs += read;
@@ -210,17 +242,59 @@ vgah_reads_t* vgah_reads_simulate(const vgah_index_t* h, uint32_t n, uint32_t le
     return r;
 }
 
+// Same generator with one RNG stream PER READ (seeded by (seed, first_id + i)), so that any sub-range of a read set can be
+// produced by any thread or rank: used for the multi-million-read workloads (10 M x 150 bp, 100 k x 10 kb).  Every read has
+// exactly `len` bases; names are "read<i>" and are not materialised.
+vgah_reads_t* vgah_reads_simulate_mt(const vgah_index_t* h, uint64_t first_id, uint32_t n, uint32_t len, double sub, double ins,
+                                     double del, double rev_frac, uint64_t seed, int threads) {
+    const FlatIndex& ix = h->ix;
+    if (ix.seq_len == 0) { set_err("empty graph"); return nullptr; }
+    std::vector<uint32_t> p2n;
+    pos_to_node(ix, p2n);
+    vgah_reads* r = new vgah_reads();
+    r->auto_names = true;
+    r->seqs.assign((size_t)n * len, 'N');
+    r->off.resize((size_t)n + 1);
+    for (uint64_t i = 0; i <= n; i++) r->off[i] = i * len;
+    int T = threads > 0 ? threads : (int)std::max(1u, std::thread::hardware_concurrency());
+    if (n < 4096) T = 1;
+    std::atomic<bool> failed{false};
+    auto work = [&](int t) {
+        std::string tmpl, read;
+        const uint32_t a = (uint32_t)((uint64_t)n * t / T), b = (uint32_t)((uint64_t)n * (t + 1) / T);
+        for (uint32_t i = a; i < b && !failed; i++) {
+            Rng rng((seed * 0x9E3779B97F4A7C15ull + 12345) ^ ((first_id + i + 1) * 0xD6E8FEB86659FD93ull));
+            if (!simulate_one(ix, p2n, rng, len, sub, ins, del, rev_frac, tmpl, read)) { failed = true; return; }
+            memcpy(&r->seqs[(size_t)i * len], read.data(), len);
+        }
+    };
+    if (T == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < T; t++) th.emplace_back(work, t);
+        for (auto& x : th) x.join();
+    }
+    if (failed) { set_err("read simulation cannot find a long enough walk"); delete r; return nullptr; }
+    return r;
+}
+
 void vgah_reads_free(vgah_reads_t* r) { delete r; }
-uint32_t vgah_reads_count(const vgah_reads_t* r) { return (uint32_t)r->names.size(); }
+uint32_t vgah_reads_count(const vgah_reads_t* r) { return (uint32_t)(r->off.size() - 1); }
 const char* vgah_reads_seqs(const vgah_reads_t* r) { return r->seqs.data(); }
 const uint64_t* vgah_reads_offsets(const vgah_reads_t* r) { return r->off.data(); }
-const char* vgah_reads_names(const vgah_reads_t* r) { return r->names_joined.c_str(); }
+const char* vgah_reads_names(const vgah_reads_t* r) {
+    if (r->auto_names && r->names_joined.empty() && r->off.size() > 1) {      // materialise on demand
+        vgah_reads* w = const_cast<vgah_reads*>(r);
+        for (size_t i = 0; i + 1 < r->off.size(); i++) { if (i) w->names_joined += '\n'; w->names_joined += "read" + std::to_string(i); }
+    }
+    return r->names_joined.c_str();
+}
 
 int vgah_reads_write_fasta(const vgah_reads_t* r, const char* path) {
     std::ofstream o(path);
     if (!o) { set_err(std::string("cannot write ") + path); return -1; }
-    for (size_t i = 0; i < r->names.size(); i++)
-        o << '>' << r->names[i] << '\n' << r->seqs.substr(r->off[i], r->off[i + 1] - r->off[i]) << '\n';
+    for (size_t i = 0; i + 1 < r->off.size(); i++)
+        o << '>' << (r->auto_names ? "read" + std::to_string(i) : r->names[i]) << '\n' << r->seqs.substr(r->off[i], r->off[i + 1] - r->off[i]) << '\n';
     return 0;
 }
 
@@ -269,69 +343,26 @@ char* vgah_synth_gfa(uint64_t backbone_len, uint32_t site_every, uint64_t seed, 
 
 void vgah_free_str(char* s) { free(s); }
 
-// ---- GAF writer ---------------------------------------------------------------------------------
+// ---- GAF writer (gaf_writer.cpp) ---------------------------------------------------------------------
+static const GafTables* tables_of(const vgah_index_t* h) {
+    std::call_once(h->gaf_once, [h]() { h->gaf_tables = gaf_tables_new(h->ix); });
+    return h->gaf_tables;
+}
+
+char* vgah_gaf_raw(const vgah_index_t* h, const VgaResultsView* R, const char* names_joined, uint64_t name_base, const char* seqs,
+                   const uint64_t* seq_off, int which, int threads, uint64_t* len, uint64_t* n_failed) {
+    if (!h || !R || !seq_off || (which != 0 && which != 1)) { set_err("vgah_gaf: bad argument"); return nullptr; }
+    try {
+        char* c = gaf_format(h->ix, *tables_of(h), R, names_joined, name_base, seqs, seq_off, which, threads, len, n_failed);
+        if (!c) set_err("vgah_gaf: out of memory");
+        return c;
+    } catch (std::exception& e) { set_err(e.what()); return nullptr; }
+}
+
 char* vgah_gaf(const vgah_index_t* h, const VgaResultsView* R, const vgah_reads_t* reads, int which, uint64_t* len) {
-    const FlatIndex& ix = h->ix;
-    std::string out;
-    // rank / select over seq_bv (src/index.rs:427-480) from the node table
-    std::vector<uint64_t> starts(ix.n_nodes);
-    for (uint64_t i = 0; i < ix.n_nodes; i++) starts[i] = ix.seq_idx(i);
-    auto node_of = [&](uint64_t pos) { return (uint64_t)(std::upper_bound(starts.begin(), starts.end(), pos) - starts.begin()); };
-    auto label = [&](uint64_t hd) {
-        uint64_t id = hd >> 1, b = ix.seq_idx(id - 1), e = ix.seq_idx(id);
-        return (hd & 1) ? ix.seq_rev.substr(ix.seq_len - e, e - b) : ix.seq_fwd.substr(b, e - b);
-    };
-    for (uint32_t r = 0; r < R->n_reads; r++) {
-        const std::string& name = reads->names[r];
-        const uint64_t qlen = reads->off[r + 1] - reads->off[r];
-        auto placeholder = [&]() { out += name + "\t" + std::to_string(qlen) + "\t*\t*\t*\t*\t*\t*\t*\t*\t*\t0\t*\n"; };
-        if (which == 0) {
-            if (R->chain_off[r] == R->chain_off[r + 1]) { placeholder(); continue; }
-            for (uint64_t c = R->chain_off[r]; c < R->chain_off[r + 1]; c++) {
-                const uint64_t b = R->chain_anchor_off[c], e = R->chain_anchor_off[c + 1];
-                std::string path;
-                for (uint64_t a = b; a < e; a++) {
-                    const uint64_t tb = R->ca_tb[a], tei = (uint64_t)R->ca_te[a] - 1;
-                    const uint64_t n1 = node_of(tb), n2 = node_of(tei);
-                    path += "(>" + std::to_string(n1) + ":" + std::to_string(tb - starts[n1 - 1]) + ",>" + std::to_string(n2) +
-                            ":" + std::to_string(tei - starts[n2 - 1]) + "),";
-                }
-                out += name + "\t" + std::to_string(qlen) + "\t" + std::to_string(R->ca_qb[b]) + "\t" +
-                       std::to_string(R->ca_qb[e - 1] + ix.k) + "\t+\t" + path + "\t0\t0\t0\t0\t0\t0\t" +
-                       "ta:Z:chain,n_anchors: " + std::to_string(e - b) + "\n";
-            }
-        } else {
-            if (R->aln_status[r] == VGA_ALN_PLACEHOLDER) { placeholder(); continue; }
-            std::string path, cs = "cs:Z:", cg;
-            for (uint64_t p = R->aln_path_off[r]; p < R->aln_path_off[r + 1]; p++)
-                path += ((R->aln_path[p] & 1) ? "<" : ">") + std::to_string(R->aln_path[p] >> 1);
-            const char* q = reads->seqs.data() + reads->off[r];
-            uint64_t pi = R->aln_path_off[r], qi = 0, off = R->aln_start_off[r];
-            std::string node_seq = pi < R->aln_path_off[r + 1] ? label(R->aln_path[pi]) : std::string();
-            auto next_base = [&]() -> char {
-                while (off >= node_seq.size()) { pi++; node_seq = label(R->aln_path[pi]); off = 0; }
-                return node_seq[off++];
-            };
-            uint32_t mrun = 0;
-            auto flush_m = [&]() { if (mrun) { cg += std::to_string(mrun) + "M"; mrun = 0; } };
-            for (uint64_t t = R->aln_run_off[r]; t < R->aln_run_off[r + 1]; t++) {
-                const uint32_t op = R->aln_runs[t] >> 28, n = R->aln_runs[t] & 0x0fffffffu;
-                if (op == 0) { cs += ":" + std::to_string(n); for (uint32_t x = 0; x < n; x++) { next_base(); qi++; } mrun += n; }
-                else if (op == 1) { for (uint32_t x = 0; x < n; x++) { cs += "*"; cs += (char)tolower(next_base()); cs += (char)tolower(q[qi++]); } mrun += n; }
-                else if (op == 2) { flush_m(); cs += "-"; for (uint32_t x = 0; x < n; x++) cs += (char)tolower(next_base()); cg += std::to_string(n) + "D"; }
-                else { flush_m(); cs += "+"; for (uint32_t x = 0; x < n; x++) cs += (char)tolower(q[qi++]); cg += std::to_string(n) + "I"; }
-            }
-            flush_m();
-            out += name + "\t" + std::to_string(qlen) + "\t0\t" + std::to_string(qlen) + "\t+\t" + path + "\t" +
-                   std::to_string(R->aln_path_len[r]) + "\t" + std::to_string(R->aln_start_off[r]) + "\t" +
-                   std::to_string(R->aln_end_off[r]) + "\t0\t" + std::to_string(R->aln_n_aligned[r]) + "\t255\t" + "as:i:-30 " +
-                   cs + ",cg:Z:" + cg + "\n";
-        }
-    }
-    char* c = (char*)malloc(out.size() + 1);
-    memcpy(c, out.data(), out.size() + 1);
-    if (len) *len = out.size();
-    return c;
+    if (!reads) { set_err("vgah_gaf: bad argument"); return nullptr; }
+    return vgah_gaf_raw(h, R, reads->auto_names ? nullptr : reads->names_joined.c_str(), 0, reads->seqs.data(), reads->off.data(), which, 0,
+                        len, nullptr);
 }
 
 }  // extern "C"

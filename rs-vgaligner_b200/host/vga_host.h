@@ -31,6 +31,10 @@ vgah_reads_t* vgah_reads_from_file(const char* path);
  * deletions, a fraction reverse-complemented (SURVEY.md §8d inputs) */
 vgah_reads_t* vgah_reads_simulate(const vgah_index_t*, uint32_t n, uint32_t len, double sub, double ins, double del,
                                   double rev_frac, uint64_t seed);
+/* the same generator with one RNG stream per read (seeded by seed and first_id + i), spread over `threads` host threads
+ * (0 = all cores): any sub-range of a read set can be produced independently.  Names are "read<i>". */
+vgah_reads_t* vgah_reads_simulate_mt(const vgah_index_t*, uint64_t first_id, uint32_t n, uint32_t len, double sub, double ins,
+                                     double del, double rev_frac, uint64_t seed, int threads);
 void vgah_reads_free(vgah_reads_t*);
 uint32_t vgah_reads_count(const vgah_reads_t*);
 const char* vgah_reads_seqs(const vgah_reads_t*);        /* concatenated */
@@ -47,6 +51,11 @@ void vgah_free_str(char*);
  * to_string} (src/align.rs:762-1027) and generate_alignment (src/align.rs:1096-1168).
  * which: 0 = chains file, 1 = alignments file. */
 char* vgah_gaf(const vgah_index_t*, const VgaResultsView* res, const vgah_reads_t* reads, int which, uint64_t* len);
+/* Same from plain arrays, formatted on `threads` host threads (0 = all cores): names_joined is '\n' separated or NULL
+ * ("read<name_base+i>"); *n_failed counts reads whose device alignment did not complete (status other than OK or
+ * PLACEHOLDER) — they are written as placeholder records, the reference has no record type for them. */
+char* vgah_gaf_raw(const vgah_index_t*, const VgaResultsView* res, const char* names_joined, uint64_t name_base, const char* seqs,
+                   const uint64_t* seq_off, int which, int threads, uint64_t* len, uint64_t* n_failed);
 
 #ifdef __cplusplus
 }

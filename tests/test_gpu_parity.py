@@ -277,3 +277,63 @@ def test_c2_full_size_parity_and_repeatability():
     assert g3.ca_id.size == 0 and g3.ca_score.size == 0
     assert_same(g3, g, ["ca_qb", "ca_tb", "ca_te"] + ALN)
     assert (g.aln_status == vg.ALN_OK).mean() > 0.9
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# BASELINE configs at their real sizes (the 5 Mbp index, whose table leaves L2, was never parity-checked)
+# ---------------------------------------------------------------------------------------------------------------
+FULL = ["n_anchors", "chain_off", "chain_anchor_off", "ca_qb", "ca_tb", "ca_te"] + ALN
+
+
+@pytest.fixture(scope="module")
+def synth5m():
+    """the 5 Mbp synthetic graph of configs C4 / C5, k=15 (same generator and seed as bench.py)"""
+    return vg.Index.build_from_text(vg.synth_gfa(5000000, 100, 1), 15)
+
+
+def test_c4_real_index_short_reads(synth5m):
+    """C4 on the real 5 Mbp index (≈10 M keys, table far larger than L2, 5 M pos2node entries): 50 k reads."""
+    reads = vg.simulate_reads_mt(synth5m, 50000, 150, 0.01, 0.0005, 0.0005, 0.1, 2)
+    g = vg.map_reads(synth5m, reads)
+    o = orc.OracleIndex(synth5m).map_reads(reads, orc.default_params(), n_threads=32)
+    assert_same(g, o, FULL)
+    assert (g.aln_status == vg.ALN_OK).mean() > 0.8
+
+
+def test_c5_real_index_long_reads_multi_wave(synth5m, monkeypatch):
+    """C5 on the real index: 64 reads of 10 kb at 10 % error, with the trace pool capped so that the alignments run in
+    several waves (the full-size run admits waves by the same rule against a 54 GB pool)."""
+    reads = vg.simulate_reads_mt(synth5m, 64, 10000, 0.04, 0.03, 0.03, 0.1, 3)
+    o = orc.OracleIndex(synth5m).map_reads(reads, orc.default_params(), n_threads=32)
+    g = vg.map_reads(synth5m, reads)
+    assert_same(g, o, FULL)
+    monkeypatch.setenv("VGA_POOL_MAX_WORDS", str(148 * 64 * 8192 + 40_000_000))
+    g2 = vg.map_reads(synth5m, reads)
+    monkeypatch.delenv("VGA_POOL_MAX_WORDS")
+    assert_same(g2, o, FULL)
+    assert g2.stats["poa_launches"] > g.stats["poa_launches"]
+    assert (g.aln_status == vg.ALN_OK).sum() >= 40
+
+
+@pytest.mark.parametrize("graph,n", [("graphs/17-DRB1-3123-smooth.gfa", 125000), ("graphs/19-MICB-4227-smooth.gfa", 125000)])
+def test_c3_full_shard_size(graph, n):
+    """C3 at the per-GPU size of the 8-GPU configuration (1 M reads / 8): every array against the oracle."""
+    ix = vg.Index.build(fixture_path(graph), 11)
+    reads = vg.simulate_reads_mt(ix, n, 150, 0.01, 0.0005, 0.0005, 0.1, 77)
+    g = vg.map_reads(ix, reads)
+    o = orc.OracleIndex(ix).map_reads(reads, orc.default_params(), n_threads=32)
+    assert_same(g, o, FULL)
+
+
+def test_failed_alignment_status_reaches_the_gaf_text(synth, monkeypatch):
+    """A device alignment that did not complete (status other than OK / PLACEHOLDER; patched into real results here, the
+    inputs of this suite never produce one) is written as a placeholder line and counted, never as a well-formed record."""
+    reads = vg.simulate_reads(synth, 50, 150, 0.01, 0.0005, 0.0005, 0.0, 4)
+    g = vg.map_reads(synth, reads)
+    ok = np.flatnonzero(g.aln_status == vg.ALN_OK)
+    assert ok.size > 10
+    g.aln_status[ok[0]] = vg.ALN_TOO_WIDE
+    view = vg.view_from_arrays(g, reads.n)
+    text, failed = vg.gaf_text(synth, view, 1, reads.seqs, reads.offsets, reads.names)
+    line = text.decode().split("\n")[ok[0]]
+    assert failed == 1 and line.split("\t")[2:] == ["*"] * 9 + ["0", "*"]
