@@ -72,7 +72,7 @@ typedef struct {
 #define VGA_ALN_TRACE_ERR 3
 #define VGA_ALN_BAND_ERR 4
 #define VGA_ALN_UNSUPPORTED 5    /* Reverse/Both node range (src/align.rs:365-387), unreachable from map_reads */
-#define VGA_ALN_TOO_WIDE 6       /* adaptive band wider than the widest kernel instance (1024 columns) */
+#define VGA_ALN_TOO_WIDE 6       /* adaptive band wider than 1024 columns on a read too long for the shared-memory row of the wide kernel (~38 k bases) */
 
 /* Flat, library-owned (pinned host) result arrays for one batch of n reads; valid until
  * vga_results_free().  A read with no chain (the reference's placeholder chain, src/chain.rs:644-649)

@@ -107,9 +107,10 @@ struct PoaBuffers {
     i32 nb_hint;             // pair kernel: blocks per lane and step worth instantiating (2 or 3), from rows per query base
     i32 long_mode;           // kernel family of class 3 for this call (poa_long_mode)
     i32 qmax_short;          // longest read among the items of the short-read classes (sizes the pair kernel's shared memory)
+    i32 qmax_wide;           // longest read among the items of a wide-class launch (sizes its shared-memory row)
 };
 // kernel classes: 0..1 = short reads on the 16x2 kernel (k_poa_pair.cu; 1 = with the per-row range check); 2 = short reads, 32 lanes
-// (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
+// (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu); 8 = bands wider than 1024 columns (k_poa_wide.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
 int poa_long_mode(u64 n_long_items, int n_sms);   // long-read kernel family for the batch: 1 = shared-memory kernel, 0 = SLIDE (k_poa.cu)
 int poa_class_count();
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode);
@@ -118,6 +119,7 @@ int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms,
 int launch_poa_fill_short(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 bool poa_short_ok(i64 qlen, i64 nrows, const VgaParams& P);   // read short enough and scores within int16
 int launch_poa_fill_long(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st);              // k_poa_long.cu
+int launch_poa_fill_wide(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st);              // k_poa_wide.cu
 int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);   // k_poa_pair.cu
 bool poa_pair_checked_ok(i64 qlen, i64 nrows, const VgaParams& P);   // same, scores checked per row instead of bounded a priori
 bool poa_pair_ok(i64 qlen, i64 nrows, const VgaParams& P);    // 16x2 kernel: short read, int16 scores, default-sized gap model

@@ -532,7 +532,8 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
 
 // classes: 0 = short reads on the 16x2 kernel (k_poa_pair.cu: qlen < 246, default gap model, int16 absolute scores bounded
 // by the row count), 1 = the same kernel with a per-row range check for longer subgraphs, 2 = short reads with 32 lanes
-// (k_poa_short.cu, any gap model, reads < 256), 3..7 = SLIDE C = 8, 12, 16, 24, 32 (bands up to 256 / 384 / 512 / 768 / 1024 columns).
+// (k_poa_short.cu, any gap model, reads < 256), 3..7 = SLIDE C = 8, 12, 16, 24, 32 (bands up to 256 / 384 / 512 / 768 / 1024 columns),
+// 8 = bands of any width (k_poa_wide.cu).
 // An item that does not fit its class moves to the next.
 // VGA_POA_PAIR=0 restores the 8 / 16 / 32-lane kernels of k_poa_short.cu on classes 0..2 (A/B measurements).
 static int g_pair = getenv("VGA_POA_PAIR") ? atoi(getenv("VGA_POA_PAIR")) : 1;
@@ -549,8 +550,9 @@ int poa_long_mode(u64 n_long_items, int n_sms) {
     return e ? atoi(e) : (n_long_items >= (u64)n_sms * 24 ? 1 : 0);
 }
 static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
-int poa_class_count() { return 8; }
+int poa_class_count() { return 9; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode) {
+    if (const char* e = getenv("VGA_POA_WIDE")) { if (atoi(e) == 1) return 8; }      // tests: every alignment on the CTA-per-alignment kernel
     if (g_pair) {
         if (poa_pair_ok(qlen, nrows, P)) return 0;
         if (g_pair_chk && poa_pair_checked_ok(qlen, nrows, P)) return 1;
@@ -564,7 +566,8 @@ int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mo
     if (west <= 768 - 24) return 6;
     return 7;
 }
-int poa_class_wider(int cls, int long_mode) { return (long_mode && cls >= 3) ? -1 : cls < 7 ? cls + 1 : -1; }
+// class 8 = bands wider than 1024 columns, one CTA per alignment (k_poa_wide.cu)
+int poa_class_wider(int cls, int long_mode) { return cls >= 8 ? -1 : (long_mode && cls >= 3) ? 8 : cls + 1; }
 
 template <int C, bool SLIDE>
 static void launch_fill(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
@@ -590,7 +593,8 @@ int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms,
         case 4: launch_fill<12, true>(ix, b, n_sms, st); break;
         case 5: launch_fill<16, true>(ix, b, n_sms, st); break;
         case 6: launch_fill<24, true>(ix, b, n_sms, st); break;
-        default: launch_fill<32, true>(ix, b, n_sms, st); break;
+        case 7: launch_fill<32, true>(ix, b, n_sms, st); break;
+        default: return launch_poa_fill_wide(ix, b, n_sms, st);
     }
     return 1;
 }

@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
             const i32 W = end - beg + 1;
             const int cr = long_pick_cr(W);
             if (beg > end) status = VGA_ALN_BAND_ERR;
-            else if (cr == 0) status = VGA_ALN_TOO_WIDE;
+            else if (cr == 0) status = IT_RETRY_WIDER;       // wider than 1024 columns: the CTA-per-alignment kernel (k_poa_wide.cu)
             // pool space: one trace word per band cell, rows stored from an 8-column boundary (trace_col0)
             const u64 need = (u64)((W + (beg & 7) + 3) & ~3);
             if (status == VGA_ALN_OK && pool_cur + need > pool_end) {

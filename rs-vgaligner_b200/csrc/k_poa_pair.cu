@@ -14,8 +14,13 @@
 //     halves): the left neighbour of pair t is pair t-1 for BOTH halves, so the diagonal operand and the serial
 //     part of the F1/F2 prefix-max scans need no per-pair shuffling.  Chains are stitched per lane in scalar code
 //     (2 chains per block), lanes by Kogge-Stone over the group.
-//   * The previous row (H, E1', E2') and the query profile live in shared memory in exactly this layout: one
-//     LDS.128 / STS.128 per plane and block.
+//   * The previous row (H, E1', E2') lives in shared memory in exactly this layout: one LDS.128 / STS.128 per plane
+//     and block.  The substitution scores are NOT stored per base: the read is kept as one plane of 16-bit PRMT
+//     selectors per column pair (nibbles: code of column t, code | 8, code of column t+4, code | 8; code = A0 C1 T2 G3,
+//     4 = anything else), and a row turns a selector into the pair of scores with ONE byte permute of an 8-byte
+//     look-up register pair (byte c = score of the row's base against code c; a selector nibble with bit 3 set
+//     replicates the sign, which makes the int8 score an int16).  8 bytes of shared memory per block instead of 80:
+//     1.3 KB per alignment instead of 2.7, so twice the groups fit an SM.
 //   * A GROUP of G lanes owns one (read, chain).  A row is computed in SPANS of G*NB blocks (lane l: NB consecutive
 //     blocks); a warp step advances every group of the warp by one span, so a group with a narrow band moves on to
 //     its next row while a group with a wide band works on the next span of the same row — nobody computes columns
@@ -52,6 +57,18 @@ __device__ __forceinline__ i32 imin(i32 a, i32 b) { return a < b ? a : b; }
 __device__ __forceinline__ i32 sext16(u32 w) { return (i32)(short)(w & 0xffffu); }
 __device__ __forceinline__ u32 pair16(i32 lo, i32 hi) { return __byte_perm((u32)lo, (u32)hi, 0x5410); }
 __device__ __forceinline__ u32 both16(i32 v) { return __byte_perm((u32)v, (u32)v, 0x1010); }
+// generic byte permute (selector nibbles with bit 3 set replicate the sign of the selected byte; only bits 0..15 of c are used)
+__device__ __forceinline__ u32 prmt(u32 a, u32 b, u32 c) {
+    u32 d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// selector code of a read byte: A 0, C 1, T 2, G 3 (bits 1..2 of the ASCII code), anything else 4
+__device__ __forceinline__ u32 base_code(u32 c) {
+    const u32 cc = (c >> 1) & 3u;
+    return c == ((0x47544341u >> (8 * cc)) & 0xffu) ? cc : 4u;
+}
+__device__ __forceinline__ u32 sel16_of(u32 clo, u32 chi) { return clo | ((clo | 8u) << 4) | (chi << 8) | ((chi | 8u) << 12); }
 // half-word index of query column j (j >= -8) inside a plane
 __device__ __forceinline__ int hw_index(i32 j) {
     const i32 c = j + 8;
@@ -76,7 +93,7 @@ template <int G> __device__ __forceinline__ u32 pair_group_mask(u32 lane) {
 // row count does not prove a priori that every reachable score fits the int16 planes.
 template <int G, int NB, bool CHK>
 __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone, bool live, bool last, SpanCarry& cy,
-                                             uint4* __restrict__ planes, int nblk, const uint4* __restrict__ prof,
+                                             uint4* __restrict__ planes, int nblk, const uint2* __restrict__ sel, u32 lutA, u32 lutB,
                                              const uint4* __restrict__ vtab, u32* __restrict__ tr) {
     const u32 FULLM = 0xffffffffu;
     const i32 b0 = (beg + 8) >> 3, bend = (end + 8) >> 3;
@@ -96,12 +113,13 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
 #pragma unroll
     for (int k = 0; k < NB; k++) {
         const int bk = imin(bme + k, nblk - 1);         // lanes right of the band read the spare block (all their cells are masked)
-        const uint4 hv = Hpl[bk], e1v = E1pl[bk], e2v = E2pl[bk], pv = prof[bk];
+        const uint4 hv = Hpl[bk], e1v = E1pl[bk], e2v = E2pl[bk];
+        const uint2 sv = sel[bk];
         const i32 a = __viaddmax_s32(D, -8 * k, 0);                    // invalid cells at the block's left  (0..7)
         const i32 z = imin(__viaddmax_s32(Eo, -8 * k, 0), 8);          // cells r < z are left of end+1      (0..8)
         const uint4 V = vtab[a * 9 + z];
         const u32 hw[4] = {hv.x, hv.y, hv.z, hv.w};
-        const u32 pw[4] = {pv.x, pv.y, pv.z, pv.w};
+        const u32 pw[4] = {prmt(lutA, lutB, sv.x), prmt(lutA, lutB, sv.x >> 16), prmt(lutA, lutB, sv.y), prmt(lutA, lutB, sv.y >> 16)};
         const u32 vw[4] = {V.x, V.y, V.z, V.w};
         x1[k][0] = e1v.x; x1[k][1] = e1v.y; x1[k][2] = e1v.z; x1[k][3] = e1v.w;
         x2[k][0] = e2v.x; x2[k][1] = e2v.y; x2[k][2] = e2v.z; x2[k][3] = e2v.w;
@@ -262,7 +280,9 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     const u32 FULLM = 0xffffffffu;
     uint4* const vtab = (uint4*)dyn_smem;
-    uint4* const planes = vtab + VT_WORDS + (size_t)(threadIdx.x / G) * 8 * nblk;     // H, E1', E2', 5 profile planes
+    uint4* const planes = vtab + VT_WORDS + (size_t)(threadIdx.x / G) * 4 * nblk;     // H, E1', E2' (nblk uint4 each), read selectors and custom-base selectors (nblk uint2 each)
+    uint2* const selq = (uint2*)(planes + 3 * nblk);
+    uint2* const selc = selq + nblk;
     short* const Hs = (short*)planes;
     short* const E1s = (short*)(planes + nblk);
     short* const E2s = (short*)(planes + 2 * nblk);
@@ -278,6 +298,8 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
     }
     __syncthreads();
     const i32 smatch = b.match, smis = -b.mismatch;
+    const u32 mis4 = ((u32)smis & 0xffu) * 0x01010101u;                 // look-up bytes: every code mismatches ...
+    const u32 lutB = ((u32)smis & 0xffu) | (((u32)smatch & 0xffu) << 8);   // ... code 4 = other, code 5 = equal to a custom base
     if (gl == 0) Hs[hw_index(-1)] = (short)NEG16;       // column -1: M(i,0) does not exist
     const int ncols = (nblk - 1) * 8;                   // columns -8 .. ncols-9 are backed by real blocks
     // ---- group-uniform state of the alignment in flight
@@ -292,7 +314,8 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
     u32 status = VGA_ALN_OK, custom_base = 0xffffffffu;
     u64 pool_cur = 0, pool_end = 0;                 // this group's current chunk of the trace pool (words)
     u32* tr = b.pool;
-    const uint4* pr = planes + 3 * nblk;
+    const uint2* pr = selq;
+    u32 lutA = mis4;
     SpanCarry cy;
     cy.fc1 = NEG16; cy.fc2 = NEG16; cy.hq = 0;
 
@@ -365,15 +388,13 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                         const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
                         end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
                     }
-                    // query profile: score of column j (query base j-1) against A, C, T, G (order of the 2-bit code (c >> 1) & 3)
+                    // selectors of the read: pair p = (block p / 4, word p % 4) holds columns 8*blk - 8 + word and + 4 (query base j-1)
                     __syncwarp(gm);
-                    for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G) {
-                        const u32 c = (j >= 1 && j <= qlen) ? q[j - 1] : 0u;
-                        const int x = hw_index(j);
-                        ((short*)(planes + 3 * nblk))[x] = (short)(c == 'A' ? smatch : smis);
-                        ((short*)(planes + 4 * nblk))[x] = (short)(c == 'C' ? smatch : smis);
-                        ((short*)(planes + 5 * nblk))[x] = (short)(c == 'T' ? smatch : smis);
-                        ((short*)(planes + 6 * nblk))[x] = (short)(c == 'G' ? smatch : smis);
+                    for (int p = (int)gl; p < 4 * nblk; p += G) {
+                        const i32 j = 8 * (p >> 2) - 8 + (p & 3);
+                        const u32 clo = (j >= 1 && j <= qlen) ? base_code(q[j - 1]) : 4u;
+                        const u32 chi = (j + 4 >= 1 && j + 4 <= qlen) ? base_code(q[j + 3]) : 4u;
+                        ((u16*)selq)[p] = (u16)sel16_of(clo, chi);
                     }
                 }
             }
@@ -473,18 +494,25 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                         }
                     }
                 }
-                // substitution profile row of this graph base
-                u32 code = (base >> 1) & 3u;
-                if (base != ((0x47544341u >> (8 * code)) & 0xffu)) {          // not A, C, T, G: custom row
-                    code = 4;
+                // substitution scores of this graph base: look-up bytes for the read's selectors
+                const u32 code = (base >> 1) & 3u;
+                if (base == ((0x47544341u >> (8 * code)) & 0xffu)) {
+                    lutA = mis4 ^ ((((u32)smis ^ (u32)smatch) & 0xffu) << (8 * code));
+                    pr = selq;
+                } else {                                                     // not A, C, T, G: selectors 5 = equal to this base, 4 = not
+                    lutA = mis4;
                     if (base != custom_base) {
                         __syncwarp(gm);
-                        for (i32 j = -8 + (i32)gl; j < ncols - 8; j += G)
-                            ((short*)(planes + 7 * nblk))[hw_index(j)] = (short)((j >= 1 && j <= qlen && q[j - 1] == base) ? smatch : smis);
+                        for (int p = (int)gl; p < 4 * nblk; p += G) {
+                            const i32 j = 8 * (p >> 2) - 8 + (p & 3);
+                            const u32 clo = (j >= 1 && j <= qlen && q[j - 1] == base) ? 5u : 4u;
+                            const u32 chi = (j + 4 >= 1 && j + 4 <= qlen && q[j + 3] == base) ? 5u : 4u;
+                            ((u16*)selc)[p] = (u16)sel16_of(clo, chi);
+                        }
                         custom_base = base;
                     }
+                    pr = selc;
                 }
-                pr = planes + (3 + code) * nblk;
                 bdone = 0;
                 nblocks_row = nblocks;
                 cy.fc1 = NEG16; cy.fc2 = NEG16; cy.hq = 0;
@@ -499,11 +527,11 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
         const int nbw = __reduce_max_sync(FULLM, (u32)imin((left + G - 1) / G, NBMAX));     // blocks per lane of this step
         SpanOut so;
         if (NBMAX >= 3 && nbw == 3)
-            so = span_step<G, (NBMAX >= 3 ? 3 : 1), CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 3, cy, planes, nblk, pr, vtab, tr);
+            so = span_step<G, (NBMAX >= 3 ? 3 : 1), CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 3, cy, planes, nblk, pr, lutA, lutB, vtab, tr);
         else if (NBMAX >= 2 && nbw == 2)
-            so = span_step<G, (NBMAX >= 2 ? 2 : 1), CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 2, cy, planes, nblk, pr, vtab, tr);
+            so = span_step<G, (NBMAX >= 2 ? 2 : 1), CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G * 2, cy, planes, nblk, pr, lutA, lutB, vtab, tr);
         else
-            so = span_step<G, 1, CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G, cy, planes, nblk, pr, vtab, tr);
+            so = span_step<G, 1, CHK>(gl, live ? beg : 0, live ? end : -1, live ? bdone : 0, live, live && left <= G, cy, planes, nblk, pr, lutA, lutB, vtab, tr);
         // ---- D: row epilogue
         if (live) {
             // a band cell below the int16 range of this class: the alignment is redone by the 32-bit kernel
@@ -539,7 +567,7 @@ static void launch_pair(const DevIndex& ix, const PoaBuffers& b, int n_sms, cuda
     const int groups_per_cta = PP_WARPS * 32 / G;
     int qmax = b.qmax_short < 16 ? 16 : b.qmax_short > 255 ? 255 : b.qmax_short;
     const int nblk = ((qmax + 9) >> 3) + 2;         // columns -8 .. qmax+1, plus the spare block
-    const size_t smem_bytes = ((size_t)VT_WORDS + (size_t)groups_per_cta * 8 * nblk) * sizeof(uint4);
+    const size_t smem_bytes = ((size_t)VT_WORDS + (size_t)groups_per_cta * 4 * nblk) * sizeof(uint4);
     static size_t attr_bytes = 0;
     if (smem_bytes > attr_bytes) {
         VGA_CUDA(cudaFuncSetAttribute(poa_fill_pair_kernel<G, NBMAX, MINB, CHK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
@@ -560,8 +588,12 @@ static void launch_pair(const DevIndex& ix, const PoaBuffers& b, int n_sms, cuda
 int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st) {
     if (b.n_items == 0) return 0;
     static const int nbenv = getenv("VGA_POA_NBMAX") ? atoi(getenv("VGA_POA_NBMAX")) : 0;     // A/B measurements
+    static const int genv = getenv("VGA_POA_G") ? atoi(getenv("VGA_POA_G")) : 0;
     const int nbmax = nbenv ? nbenv : b.nb_hint;
+    const int g = genv ? genv : 8;
     if (cls == 1) { if (nbmax <= 2) launch_pair<8, 2, 4, true>(ix, b, n_sms, st); else launch_pair<8, 3, 4, true>(ix, b, n_sms, st); }
+    else if (g == 4) { if (nbmax <= 2) launch_pair<4, 2, 4, false>(ix, b, n_sms, st); else launch_pair<4, 3, 4, false>(ix, b, n_sms, st); }
+    else if (g == 2) { if (nbmax <= 2) launch_pair<2, 2, 4, false>(ix, b, n_sms, st); else launch_pair<2, 3, 4, false>(ix, b, n_sms, st); }
     else if (nbmax == 1) launch_pair<8, 1, 4, false>(ix, b, n_sms, st);
     else if (nbmax == 2) launch_pair<8, 2, 4, false>(ix, b, n_sms, st);
     else launch_pair<8, 3, 4, false>(ix, b, n_sms, st);

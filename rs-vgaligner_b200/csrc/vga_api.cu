@@ -804,6 +804,10 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                 end++;
             }
             const u32 nw = (u32)(end - pos);
+            if (ci == 8) {
+                pb.qmax_wide = 0;
+                for (size_t x = pos; x < end; x++) pb.qmax_wide = std::max<i32>(pb.qmax_wide, (i32)h_meta[NI + list[x]]);
+            }
             VGA_CUDA(cudaMemcpyAsync(d_work, list.data() + pos, 4ull * nw, cudaMemcpyHostToDevice, st));
             VGA_CUDA(cudaMemsetAsync(ctr + 2, 0, 4, st));
             pb.n_items = nw; pb.work = d_work;
@@ -847,7 +851,16 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             u32 done = 0;
             for (u32 x = 0; x < nw; x++) {
                 const u32 it = list[pos + x];
-                if (h_status[x] == IT_RETRY_WIDER) { const int nc = poa_class_wider(ci, pb.long_mode); if (nc >= 0) cls[nc].push_back(it); else done++; }
+                if (h_status[x] == IT_RETRY_WIDER) {
+                    const int nc = poa_class_wider(ci, pb.long_mode);
+                    if (nc == 8) {
+                        // the band left the 1024 columns of the warp kernels: nothing bounds it but the read.  Measured on C5's
+                        // reverse-strand reads (random k-mer hits chained): 0.07-0.1 of rows x read length
+                        const u64 nr = h_meta[it], ql = h_meta[NI + it];
+                        est[it] = std::max<u64>(est[it], nr * (ql / 4 + 1024));
+                    }
+                    if (nc >= 0) cls[nc].push_back(it); else done++;
+                }
                 else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
                 else { done++; if (h_status[x] == VGA_ALN_OK && !traced_here) trace_list.push_back(it); }
             }

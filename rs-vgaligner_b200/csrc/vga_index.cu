@@ -74,7 +74,8 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
             u64 s = v->tab_start[p], e = v->tab_end[p];
             if (s == VGA_POS_DELIM && e == VGA_POS_DELIM) break;
             if (!(s & VGA_POS_REV) && !(e & VGA_POS_REV)) {
-                if (s >= L || e > L || s >= e) { set_error("k-mer position outside the linearisation (or start >= end)"); return VGA_ERR_INVALID; }
+                // start > end is legal: a forward/forward k-mer may cross reverse handles (17-DRB1-3123-smooth has such links)
+                if (s >= L || e > L || e == 0) { set_error("k-mer position outside the linearisation"); return VGA_ERR_INVALID; }
                 ptb.push_back((u32)s); pte.push_back((u32)e); cnt++;
             }
             p++;

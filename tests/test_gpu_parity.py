@@ -149,6 +149,12 @@ def test_cyclic_inverting_graph():
 
 
 @pytest.fixture(scope="module")
+def synth5m():
+    """the 5 Mbp synthetic graph of configs C4 / C5, k=15 (same generator and seed as bench.py)"""
+    return vg.Index.build_from_text(vg.synth_gfa(5000000, 100, 1), 15)
+
+
+@pytest.fixture(scope="module")
 def synth():
     return vg.Index.build_from_text(vg.synth_gfa(200000, 100, 1), 15)
 
@@ -181,6 +187,33 @@ def test_long_read_kernel_families(synth, monkeypatch, family):
         g, o = both(synth, reads, **kw)
         check_all(g, o)
         assert (g.aln_status == vg.ALN_OK).sum() >= n // 3
+
+
+def test_wide_band_kernel_on_every_shape(synth, monkeypatch):
+    """The CTA-per-alignment kernel for bands beyond 1024 columns (k_poa_wide.cu), forced on alignments of every shape:
+    150 bp reads on an HLA graph with merges, 1 kb reads with several chains, 10 kb reads."""
+    monkeypatch.setenv("VGA_POA_WIDE", "1")
+    ix = vg.Index.build(fixture_path("graphs/17-DRB1-3123-smooth.gfa"), 11)
+    reads = vg.simulate_reads(ix, 600, 150, 0.01, 0.0005, 0.0005, 0.1, 5)
+    g, o = both(ix, reads)
+    check_all(g, o)
+    for n, length, err, kw in ((12, 10000, (0.04, 0.03, 0.03), {}), (100, 1000, (0.03, 0.01, 0.01), dict(best_n=3, min_anchors=2))):
+        reads = vg.simulate_reads(synth, n, length, *err, 0.1, 13)
+        g, o = both(synth, reads, **kw)
+        check_all(g, o)
+        assert (g.aln_status == vg.ALN_OK).sum() >= n // 3
+
+
+def test_bands_wider_than_1024_columns(synth5m):
+    """Reverse-strand 10 kb reads on the 5 Mbp index still chain a few random k-mer hits; their global alignment has rows
+    thousands of columns wide.  abPOA has no band limit, so neither has the CUDA path: the warp kernels hand such an
+    alignment to the wide kernel (found by bench.py's parity sample on C5)."""
+    reads = vg.simulate_reads_mt(synth5m, 160, 10000, 0.04, 0.03, 0.03, 0.1, 3)
+    o = orc.OracleIndex(synth5m).map_reads(reads, orc.default_params(), n_threads=32)
+    g = vg.map_reads(synth5m, reads)
+    assert_same(g, o, FULL)
+    wide = (o.aln_status == 1) & (o.aln_cells > 10000 * 600)
+    assert wide.sum() >= 5 and (g.aln_status != vg.ALN_TOO_WIDE).all()
 
 
 def test_medium_reads_and_best_n(synth):
@@ -283,12 +316,6 @@ def test_c2_full_size_parity_and_repeatability():
 # BASELINE configs at their real sizes (the 5 Mbp index, whose table leaves L2, was never parity-checked)
 # ---------------------------------------------------------------------------------------------------------------
 FULL = ["n_anchors", "chain_off", "chain_anchor_off", "ca_qb", "ca_tb", "ca_te"] + ALN
-
-
-@pytest.fixture(scope="module")
-def synth5m():
-    """the 5 Mbp synthetic graph of configs C4 / C5, k=15 (same generator and seed as bench.py)"""
-    return vg.Index.build_from_text(vg.synth_gfa(5000000, 100, 1), 15)
 
 
 def test_c4_real_index_short_reads(synth5m):
