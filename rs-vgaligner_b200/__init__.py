@@ -65,6 +65,8 @@ GPU_SYMBOLS = ["vga_init", "vga_device_count", "vga_index_upload", "vga_index_fr
                "vga_map_batch_device", "vga_results_view", "vga_results_stats", "vga_results_free",
                "vga_last_error", "vga_measure_int32_peak"]
 
+HASH_FN = C.CFUNCTYPE(C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p)     # vgah_hash_fn: (kmer bytes, k, user) -> key hash
+
 _host = None
 _gpu = None
 
@@ -118,6 +120,7 @@ def host_lib():
         L.vgah_gaf_raw.argtypes = [C.c_void_p, C.POINTER(VgaResultsView), C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int,
                                    C.c_int, u64p, u64p]
         L.vgah_gaf_raw.restype = C.c_void_p
+        L.vgah_derive_keys.argtypes = [C.POINTER(VgaIndexView), u64p, HASH_FN, C.c_void_p, u64p, u64p, u64p]
         _host = L
     return _host
 
@@ -234,6 +237,24 @@ class Index:
     def table(self):
         return (_arr(self.view.tab_start, self.view.n_table, np.uint64), _arr(self.view.tab_end, self.view.n_table, np.uint64),
                 _arr(self.view.key_offset, self.view.n_keys, np.uint64))
+
+    def derive_keys(self, key_hash, hash_fn, n_keys=None):
+        """`Index::walk_kmer` for every key (INTEGRATION.md §3): the 2-bit packed k-mers rebuilt from the table positions, the
+        linearisation and the edge lists only, candidates told apart by `hash_fn(kmer_bytes) == key_hash[i]`.
+        Returns (key_kmer2bit, n_ambiguous, n_hopping)."""
+        v = VgaIndexView()
+        C.memmove(C.byref(v), C.byref(self.view), C.sizeof(VgaIndexView))
+        v.key_kmer2bit = None                  # not available to the walk
+        if n_keys is not None:
+            v.n_keys = min(int(n_keys), self.view.n_keys)
+        kh = np.ascontiguousarray(key_hash, dtype=np.uint64)
+        out = np.zeros(v.n_keys, dtype=np.uint64)
+        amb, hop = C.c_uint64(), C.c_uint64()
+        cb = HASH_FN(lambda p, k, _u: int(hash_fn(C.string_at(p, k))) & 0xFFFFFFFFFFFFFFFF)
+        rc = host_lib().vgah_derive_keys(C.byref(v), kh.ctypes.data_as(u64p), cb, None, out.ctypes.data_as(u64p), C.byref(amb), C.byref(hop))
+        if rc != 0:
+            raise VgaError("vgah_derive_keys failed (%d)" % rc)
+        return out, amb.value, hop.value
 
     # -- device side
     def upload(self, device=None):

@@ -25,6 +25,15 @@ int vgah_index_view(const vgah_index_t*, VgaIndexView* view);       /* borrowed 
 const char* vgah_index_keys(const vgah_index_t*, uint64_t* n_keys); /* n_keys*k bytes: the k-mer strings */
 const char* vgah_index_seq_rev(const vgah_index_t*);                /* Index.seq_rev */
 
+/* Key derivation (`Index::walk_kmer`): the 2-bit packed k-mer of every key, recovered from what a `.idx`
+ * holds — the key's first table position (key_offset, tab_start/tab_end), seq_fwd, node_ref, edges — plus the key's own hash
+ * to tell apart k-mers that share their first and last position (the alleles of a bubble).  view->key_kmer2bit is not read.
+ * hash: the function the keys were made with (Rust host: generate_hash, reference src/kmer.rs:931-934).
+ * n_ambiguous: keys whose (start, end) admitted more than one k-mer; n_hopping: forward keys with end - start != k. */
+typedef uint64_t (*vgah_hash_fn)(const char* kmer, uint32_t k, void* user);
+int vgah_derive_keys(const VgaIndexView* view, const uint64_t* key_hash, vgah_hash_fn hash, void* user,
+                     uint64_t* key_kmer2bit_out, uint64_t* n_ambiguous, uint64_t* n_hopping);
+
 /* read_seqs_from_file (reference src/io.rs:74-131): extension decides FASTA/FASTQ */
 vgah_reads_t* vgah_reads_from_file(const char* path);
 /* seeded read simulator: forward random walks over the graph, substitutions / insertions /

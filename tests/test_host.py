@@ -125,3 +125,42 @@ int main(void) {
     subprocess.run(["gcc", "-O2", "-ffp-contract=off", "-o", str(exe), str(src), "-lm"], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.strip()
     assert out == "0"
+
+
+# ---- key derivation (`Index::walk_kmer`): reference src/kmer.rs:347-505, src/index.rs:584-606, 1689-1693
+def _fnv(b):
+    """stands for the index's key hash (ahash on the Rust side): any 64-bit hash of the k-mer bytes"""
+    import hashlib
+    return int.from_bytes(hashlib.blake2b(b, digest_size=8).digest(), "little")
+
+
+@pytest.mark.parametrize("graph,k,n_keys", [("test.gfa", 3, None), ("test.gfa", 4, None), ("test.gfa", 6, None), ("test.gfa", 11, None),
+                                            ("graphs/19-MICB-4227-smooth.gfa", 11, None), ("graphs/5-B3106.gfa", 11, 600),
+                                            ("graphs/17-DRB1-3123-smooth.gfa", 11, 30000), ("graphs/2-DRB1-3123.gfa", 11, 30000)])
+def test_keys_rebuilt_from_table_positions_only(graph, k, n_keys):
+    """The device table's 2-bit keys are derivable from what a `.idx` holds (positions, linearisation, NodeRef, edges) plus the
+    key's opaque hash: the keys of every fixture graph (the first few thousand of the big ones), incl. k-mers that hop over
+    non-adjacent nodes (end - start != k), microsatellite loops whose k-mer ends where it starts (5-B3106) and bubbles whose
+    alleles share first and last position."""
+    ix = vg.Index.build(fixture_path(graph), k)
+    keys, n = ix.keys_bytes()
+    n = min(n, n_keys or n)
+    hashes = np.array([_fnv(keys[i * k:(i + 1) * k]) for i in range(n)], dtype=np.uint64)
+    got, n_amb, n_hop = ix.derive_keys(hashes, _fnv, n)
+    want = np.ctypeslib.as_array(ix.view.key_kmer2bit, shape=(ix.view.n_keys,))[:n]
+    assert np.array_equal(got, want)
+    if k >= 4 and graph != "test.gfa":
+        assert n_hop > 0 and n_amb > 0          # both situations occur on the HLA graphs
+
+
+def test_multinode_kmer_positions_are_walkable():
+    """reference src/index.rs:1689-1693: ACG / C / G / TTTTT, k = 5: ACGGT spans 0..6 (hops over node 2), and its key is still
+    recovered from (0, 6)."""
+    gfa = "H\tVN:Z:1.0\nS\t1\tACG\nS\t2\tC\nS\t3\tG\nS\t4\tTTTTT\nL\t1\t+\t2\t+\t0M\nL\t1\t+\t3\t+\t0M\nL\t2\t+\t4\t+\t0M\nL\t3\t+\t4\t+\t0M\n"
+    ix = vg.Index.build_from_text(gfa, 5)
+    keys, n = ix.keys_bytes()
+    ks = [keys[i * 5:(i + 1) * 5] for i in range(n)]
+    assert b"ACGGT" in ks and b"ACGCT" in ks
+    got, n_amb, n_hop = ix.derive_keys(np.array([_fnv(x) for x in ks], dtype=np.uint64), _fnv)
+    assert np.array_equal(got, np.ctypeslib.as_array(ix.view.key_kmer2bit, shape=(n,)))
+    assert n_hop >= 1
