@@ -147,6 +147,15 @@ int vga_index_image_size(const vga_index_t* ix, uint64_t* bytes);
 int vga_index_image_copy_to_device(const vga_index_t* ix, void* dev_dst);
 int vga_index_import_device(const void* dev_blob, uint64_t bytes, vga_index_t** out);
 
+/* Multi-GPU behind the ABI (no torch on a Rust host): one process or host thread per GPU.  Rank 0 creates an id
+ * (ncclGetUniqueId) and hands its VGA_COMM_ID_BYTES bytes to the other ranks by any means; then EVERY rank calls
+ * vga_index_broadcast after vga_init(its device): rank 0 with its uploaded index, the others with *ix = NULL, which receive a
+ * replica — ONE ncclBroadcast of the index image, the only collective of the path.  Each rank then maps its contiguous range
+ * of reads with vga_map_batch; outputs are concatenated in rank order.  NCCL is loaded at run time (libnccl.so.2). */
+#define VGA_COMM_ID_BYTES 128
+int vga_comm_unique_id(void* id_bytes);
+int vga_index_broadcast(vga_index_t** ix, const void* id_bytes, int rank, int world);
+
 void vga_default_params(VgaParams* p);
 /* Map one batch: reads as concatenated bytes + n_reads+1 offsets (host memory).  Blocking. */
 int vga_map_batch(vga_index_t* ix, const char* seqs, const uint64_t* seq_off, uint32_t n_reads,

@@ -63,7 +63,7 @@ ALN_PLACEHOLDER, ALN_OK, ALN_EMPTY, ALN_TRACE_ERR, ALN_BAND_ERR, ALN_UNSUPPORTED
 GPU_SYMBOLS = ["vga_init", "vga_device_count", "vga_index_upload", "vga_index_free", "vga_index_image_size",
                "vga_index_image_copy_to_device", "vga_index_import_device", "vga_default_params", "vga_map_batch",
                "vga_map_batch_device", "vga_results_view", "vga_results_stats", "vga_results_free",
-               "vga_last_error", "vga_measure_int32_peak"]
+               "vga_last_error", "vga_measure_int32_peak", "vga_comm_unique_id", "vga_index_broadcast"]
 
 HASH_FN = C.CFUNCTYPE(C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p)     # vgah_hash_fn: (kmer bytes, k, user) -> key hash
 

@@ -55,9 +55,37 @@ struct IndexHeader {
     u64 off_slots;      // Slot[n_slots]
     u64 off_pos_tb;     // u32[n_pos]      KmerPos.start.position of fwd/fwd entries, table order
     u64 off_pos_te;     // u32[n_pos]      KmerPos.end.position
-    u64 pad[8];
+    // compact table (k <= 16; see below): 64-byte buckets of 8 entries and the interleaved position array; n_buckets = 0: absent
+    u64 off_buckets;    // uint4[4 * n_buckets]
+    u64 n_buckets;
+    u64 off_pos2;       // uint2[n_pos2]   {start, end} of fwd/fwd entries, table order; a run with more than 30 entries is
+    u64 n_pos2;         //                 preceded by a header element {count, 0}
+    u64 pad[4];
 };
-static const u64 INDEX_MAGIC = 0x3258444947414756ull;  // "VGAGIDX2" (slot keys in bit-plane form)
+static const u64 INDEX_MAGIC = 0x3358444947414756ull;  // "VGAGIDX3" (slot keys in bit-plane form; compact bucket table)
+
+// Compact k-mer table for k <= 16 (both bit planes of a key fit 16 bits each): 8-byte entries in 64-byte buckets — one
+// DRAM access (64 B on HBM3e) answers a probe, where a 16-byte slot of the open-addressed table cost 1.4 accesses of
+// 64 B for 16 useful bytes — and a table a quarter of the size (C4: 134 MB instead of 537, most of it L2-resident).
+//   entry = key32 | payload << 32;  key32 = plane0 | plane1 << 16;  an all-zero entry is empty
+//   payload, one fwd/fwd position (the usual case): bit 31 set, start in bits 0..25, end - start - k in bits 26..30:
+//            the anchor comes out of the probe itself, the position array is not touched
+//   payload otherwise: first element in pos2 in bits 0..25, count in bits 26..30 (31 = the run has a header element)
+// A key lives in the first bucket from its home bucket on that has room; a probe walks buckets until it finds the key or a
+// bucket with an empty last entry.  Entries of a bucket are filled front to back and never removed.
+static const u32 CT_INLINE = 0x80000000u, CT_LOW26 = 0x03ffffffu;
+static const u32 CT_MAX_INLINE_DLT = 31, CT_MAX_CNT = 30;
+__host__ __device__ static inline u32 ct_bucket(u32 key32, u32 n_buckets) {
+    u32 h = key32 * 0x9E3779B1u;
+    h ^= h >> 15;
+    h *= 0x85EBCA77u;
+    h ^= h >> 13;
+#ifdef __CUDA_ARCH__
+    return __umulhi(h, n_buckets);
+#else
+    return (u32)(((u64)h * n_buckets) >> 32);
+#endif
+}
 
 struct DevIndex {       // resolved device pointers, passed to kernels by value
     u32 k, n_nodes, n_edges, L;
@@ -71,6 +99,9 @@ struct DevIndex {       // resolved device pointers, passed to kernels by value
     const Slot* slots;
     const u32* pos_tb;
     const u32* pos_te;
+    const uint4* buckets;   // compact table (n_buckets > 0): the seeding kernels use it instead of slots / pos_tb / pos_te
+    const uint2* pos2;
+    u32 n_buckets;
 };
 
 // Slot keys are stored in BIT-PLANE form: bit t of the low word = bit 0 of the 2-bit code (A0 C1 G2 T3) of base t of
@@ -108,6 +139,14 @@ static const i32 POA_DEEP = -(1 << 30);      // generator value of masked cells 
 // stored from the 8-column block that contains beg (the pair kernel stores whole blocks with 16-byte vectors)
 __host__ __device__ static inline i32 trace_col0(i32 beg) { return beg & ~7; }
 struct RowInfo { i32 beg, end; u32 toff; i32 ref; u32 prow, meta, node, off; };
+// PLANE trace format (k_poa_pair.cu -> k_poa_trace_planes.cu): a row is stored from the 8-column block that contains beg
+// (block b = columns 8b-8 .. 8b-1), 24 int16 per block: the H plane, the E1' plane, the E2' plane, each in the 16x2 register
+// order of the fill kernel (half-word 2t = column t, 2t+1 = column t+4 of the block).  Index of H(i,j) among the int16 of the
+// row; E1' is 8 further, E2' 16 further.
+__host__ __device__ static inline u32 planes_cell(i32 beg, i32 j) {
+    const i32 c = j + 8;
+    return (u32)(((c >> 3) - ((beg + 8) >> 3)) * 24 + (((c & 3) << 1) | ((c >> 2) & 1)));
+}
 // per subgraph node: band, row-maximum span and maximum of the node's LAST row
 struct NodeState { i32 beg, end, lpos, rpos, mx, pad0, pad1, pad2; };
 
@@ -138,6 +177,8 @@ struct AlignItem {      // one (read, chain) alignment job
     u32 n_runs, n_path, path_len, start_off, end_off, n_aligned;
     u32 run_pos, path_pos;  // where the (back-to-front) traceback output starts inside its region
     u64 cells;
+    u32 fmt;                // trace format of the item's rows: 0 = one 32-bit word per cell, 1 = int16 planes per 8-column block
+    u32 pad_;
 };
 
 }  // namespace vga

@@ -40,6 +40,7 @@ int launch_read_prep(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
 int launch_seed_count(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
 int launch_seed_emit(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st);
 
+static const int CHAIN_KMAX = 2048;   // gap lengths the integer DP keeps in shared memory (max_gap must be below)
 static const int CHAIN_SMAX = 512;   // anchors per read the fused sort+chain kernel keeps in shared memory
 struct ChainBuffers {
     u32 n_reads;
@@ -48,6 +49,7 @@ struct ChainBuffers {
     u32* sidx;                // sorted position -> local anchor id (per read segment); written by the fused kernel
     const u32* big_list; u32 n_big;   // reads with more than CHAIN_SMAX anchors (sorted by CUB)
     const double* gapcost;    // [max_gap+1]: 0.01*k*g + 0.5*log2(g), host-computed (src/chain.rs:348-354)
+    const i32* gapcost_i;     // [max_gap+1]: round(1000 * gapcost) when the all-integer DP is exact (vga_api.cu upload_gapcost), else NULL
     double* f;                // by sorted position
     i32* pred;                // sorted position of the best predecessor, -1 = None (consumed by backtracking)
     i32* pred_dbg;            // copy taken before backtracking, as anchor ids (NULL unless debug)
@@ -113,6 +115,7 @@ struct PoaBuffers {
 // (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu); 8 = bands wider than 1024 columns (k_poa_wide.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
 int poa_long_mode(u64 n_long_items, int n_sms);   // long-read kernel family for the batch: 1 = shared-memory kernel, 0 = SLIDE (k_poa.cu)
 int poa_class_count();
+bool poa_pair_active();    // classes 0..1 run on the 16x2 kernel (plane trace rows); false with VGA_POA_PAIR=0
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode);
 int poa_class_wider(int cls, int long_mode);    // -1: none
 int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
@@ -132,7 +135,9 @@ struct TraceBuffers {
     u32* out_runs;           // per item region at out_base, capacity nrows+qlen+2, written back to front
     u32* out_path;           // per item region at node_base, capacity S, written back to front
     i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
+    bool has_words, has_planes;   // trace formats among the items (word rows / plane rows of the 16x2 fill kernel)
 };
+int launch_poa_trace_planes(const DevIndex& ix, const TraceBuffers& b, u32 spread, cudaStream_t st);   // k_poa_trace_planes.cu
 int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st);
 
 double measure_int32_peak();

@@ -64,6 +64,24 @@ __device__ __forceinline__ i32 score_pair_nb(bool live, u32 qb_a, u32 tb_a, u32 
     return live ? r : INT_MIN;
 }
 
+// The all-integer form: with A = 1000 * f_a (the integer the reference's stored score is the quotient of) the f64 evaluation
+// above equals A + 1000 * m - K[g], K[g] = round(1000 * gap_cost(g)), for every A — provided no 1000 * gap_cost(g) lies within
+// the f64 rounding error of a rounding boundary, which the host checks when it builds K (vga_api.cu upload_gapcost).
+__device__ __forceinline__ i32 score_pair_int(bool live, u32 qb_a, u32 tb_a, u32 te_a, i32 r_a, u32 qb_b, u32 tb_b, u32 te_b,
+                                              u32 k, u32 max_gap, const i32* __restrict__ sK) {
+    live = live && qb_a < qb_b && te_a < te_b;
+    const u32 ql = qb_b - qb_a;
+    const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
+    const u32 ted = te_b - te_a;
+    const u32 tl = min(tbd, ted);
+    const u32 g = ql > tl ? ql - tl : tl - ql;
+    live = live && g <= max_gap;
+    const i32 kg = sK[min(g, max_gap)];
+    const u32 ml = min(min(ql, tl), k);
+    const i32 r = r_a + (i32)(ml * 1000u) - kg;
+    return live ? r : INT_MIN;
+}
+
 // r / 1000.0 correctly rounded, for an integer score r, without the division subroutine on the DP's critical path:
 // q0 = RN(r * RN(1/1000)), one FMA for the exact remainder, one FMA for the correction.  Equal to the IEEE quotient for
 // EVERY r in [-1e6, 2^31) — checked exhaustively on the host (tests/test_host.py::test_div1000_identity runs a stride of it).
@@ -78,16 +96,21 @@ __device__ __forceinline__ double div1000(i32 r) {
 // target_end.position (src/chain.rs:386-389) is a bitonic sort of (te, id) keys in shared memory,
 // and the integer scores / predecessor distances of the whole read stay in shared memory for the
 // backtracking.  !FUSED: the reads of big_list (more anchors than that), already sorted by CUB.
-template <bool FUSED>
+// INTDP: the all-integer DP (scores as round(x * 1000), gap costs from the integer table in shared memory; one packed
+// reduction per anchor when the scores fit 25 bits, which they always do in the fused kernel).
+template <bool FUSED, bool INTDP>
 __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b, bool two_pass_on) {
     __shared__ u32 s_q[CHAIN_WARPS][RING], s_tb[CHAIN_WARPS][RING], s_te[CHAIN_WARPS][RING];
-    __shared__ double s_f[CHAIN_WARPS][RING];
+    __shared__ double s_f[INTDP ? 1 : CHAIN_WARPS][INTDP ? 1 : RING];
+    __shared__ i32 s_r[INTDP ? CHAIN_WARPS : 1][INTDP ? RING : 1];
+
     __shared__ unsigned long long s_key[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
     __shared__ u8 s_pd[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
     const u32 lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
     const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
-    u32* rq = s_q[wl]; u32* rtb = s_tb[wl]; u32* rte = s_te[wl]; double* rf = s_f[wl];
+    u32* rq = s_q[wl]; u32* rtb = s_tb[wl]; u32* rte = s_te[wl]; double* rf = s_f[INTDP ? 0 : wl];
+    i32* rri = s_r[INTDP ? wl : 0];
     unsigned long long* keys = s_key[FUSED ? wl : 0];
     // integer score of sorted anchor i: kept in the HIGH word of keys[i] (its te) once the anchor has been staged into the
     // ring (a block of 32 is staged before any score of that block is written), the low word (anchor id) stays
@@ -127,6 +150,81 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
             for (u32 i = lane; i < n; i += 32) b.sidx[base + i] = (u32)keys[i];
         }
         i32 r_max = 0;                                                   // curr_max = 0.0 (:398)
+        if (INTDP) {
+            // All-integer DP, software-pipelined (bandwidth <= 64; the host gates this instance).  Of the up to 64 predecessors of
+            // anchor i only i-1 was scored in the previous iteration; its score is warp-uniform and stays in a register.  Everything
+            // else anchor i needs (coordinates of its window, gap costs, the older scores from the ring) was loaded and reduced to
+            // "valid, T = 1000 m - K[g], predecessor score" during iteration i-1, before that iteration's reduction — so the serial
+            // dependency between anchors is one add, one packed REDUX and the select, not a round trip through shared memory.
+            auto stage = [&](u32 first) {                                // anchors first .. first+31 of the sorted order into the ring
+                const u32 ii = first + lane;
+                if (ii < n) {
+                    const u32 id = FUSED ? (u32)keys[ii] : b.sidx[base + ii];
+                    rq[ii % RING] = b.a_qb[base + id];
+                    rtb[ii % RING] = b.a_tb[base + id];
+                    rte[ii % RING] = FUSED ? (u32)(keys[ii] >> 32) : b.a_te[base + id];
+                }
+            };
+            stage(0); stage(32);
+            __syncwarp();
+            const u32 d1 = lane + 1, d2 = lane + 33;
+            bool v1 = false, v2 = false;                                 // operands of the anchor about to be scored
+            i32 t1 = 0, t2 = 0, ra1 = 0, ra2 = 0;
+            auto prefetch = [&](u32 ia) {                                // operands of anchor ia (its predecessors ia-2 .. are in the ring)
+                const u32 sa = ia % RING;
+                const u32 qb_b = rq[sa], tb_b = rtb[sa], te_b = rte[sa];
+                const u32 s1 = (ia - d1) % RING, s2 = (ia - d2) % RING;
+                auto one = [&](bool live, u32 sj, bool& v, i32& t, i32& ra) {
+                    const u32 qb_a = rq[sj], tb_a = rtb[sj], te_a = rte[sj];
+                    live = live && qb_a < qb_b && te_a < te_b;
+                    const u32 ql = qb_b - qb_a;
+                    const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
+                    const u32 tl = min(tbd, te_b - te_a);
+                    const u32 g = ql > tl ? ql - tl : tl - ql;
+                    v = live && g <= b.max_gap;
+                    t = (i32)(min(min(ql, tl), b.k) * 1000u) - __ldg(b.gapcost_i + min(g, b.max_gap));
+                    ra = rri[sj];
+                };
+                one(d1 <= b.bandwidth && d1 <= ia, s1, v1, t1, ra1);
+                one(d2 <= b.bandwidth && d2 <= ia, s2, v2, t2, ra2);
+            };
+            i32 r_prev = rk;
+            for (u32 i = 0; i < n; i++) {
+                if (lane == 0) ra1 = r_prev;                             // predecessor i-1: just computed
+                const i32 a1 = v1 ? ra1 + t1 : INT_MIN, a2 = v2 ? ra2 + t2 : INT_MIN;
+                i32 m;
+                u32 dmin;
+                if (FUSED) {
+                    // |score| < 2^25 here (at most CHAIN_SMAX anchors of at most 32 bases, gap costs below 2^21): the score and the
+                    // nearest-predecessor rule (ties keep the smallest distance) travel as ONE key through one reduction
+                    const i32 k1 = v1 ? a1 * 64 + (64 - (i32)d1) : INT_MIN, k2 = v2 ? a2 * 64 + (64 - (i32)d2) : INT_MIN;
+                    const i32 km = __reduce_max_sync(FULLM, max(k1, k2));
+                    m = km == INT_MIN ? INT_MIN : (km >> 6);
+                    dmin = 64u - (u32)(km & 63);
+                } else {
+                    const i32 best = max(a1, a2);
+                    m = __reduce_max_sync(FULLM, best);
+                    dmin = __reduce_min_sync(FULLM, best == m && best != INT_MIN ? (a1 == m && v1 ? d1 : d2) : 0x7fffffffu);
+                }
+                // operands of anchor i+1 while the reduction is in flight (its own coordinates were staged a block ahead)
+                if (((i + 1) & 31) == 0) { stage(i + 33); __syncwarp(); }
+                if (i + 1 < n) prefetch(i + 1);
+                i32 r_i = rk;
+                i32 p = -1;
+                if (m > rk) { r_i = m; p = (i32)(i - dmin); }            // :430-443 strict >
+                if (m > r_max) r_max = m;                                // :445-447 (all proposals)
+                r_prev = r_i;
+                if (lane == 0) {
+                    rri[i % RING] = r_i;
+                    b.f[base + i] = div1000(r_i);                        // :360-363
+                    if (FUSED) { rr2[2 * i + 1] = r_i; pd[i] = p < 0 ? 0 : (u8)dmin; }
+                    else b.pred[base + i] = p;
+                    if (b.pred_dbg) b.pred_dbg[base + i] = p < 0 ? -1 : (i32)(FUSED ? (u32)keys[p] : b.sidx[base + p]);
+                }
+                __syncwarp();
+            }
+        }
+        if (!INTDP)
         for (u32 i = 0; i < n; i++) {
             if ((i & 31) == 0) {           // stage the next 32 anchors of the sorted order
                 const u32 ii = i + lane;
@@ -142,6 +240,9 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
             const u32 qb_i = rq[si], tb_i = rtb[si], te_i = rte[si];
             i32 best = INT_MIN;
             u32 bestd = 0x7fffffffu;
+            i32 m;
+            u32 dmin;
+            {
             if (two_pass) {
                 // bandwidth in (32, 64] (map_main.rs:103 passes 50): both halves of the window as straight-line code
                 const u32 d1 = lane + 1, d2 = lane + 33;
@@ -160,8 +261,9 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                     if (s > best) { best = s; bestd = d; }
                 }
             }
-            const i32 m = __reduce_max_sync(FULLM, best);
-            const u32 dmin = __reduce_min_sync(FULLM, best == m ? bestd : 0x7fffffffu);   // ties keep the nearest j
+            m = __reduce_max_sync(FULLM, best);
+            dmin = __reduce_min_sync(FULLM, best == m ? bestd : 0x7fffffffu);   // ties keep the nearest j
+            }
             i32 r_i = rk;
             i32 p = -1;
             if (m > rk) { r_i = m; p = (i32)(i - dmin); }                // :430-443 strict >
@@ -292,8 +394,16 @@ int launch_chain(const ChainBuffers& b, bool fused, cudaStream_t st) {
     // green (gpurun_out/ab16); VGA_CHAIN_TWO_PASS=0 restores the generic loop (A/B)
     const char* e = getenv("VGA_CHAIN_TWO_PASS");
     const bool tp = e ? atoi(e) != 0 : true;
-    if (fused) chain_kernel<true><<<grid_for_warps(b.n_reads, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
-    else if (b.n_big) chain_kernel<false><<<grid_for_warps(b.n_big, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
+    // all-integer DP when the host proved it exact for this (k, max_gap) (VGA_CHAIN_INT=0: the f64 body, A/B and tests)
+    const char* ei = getenv("VGA_CHAIN_INT");
+    const bool idp = b.gapcost_i != nullptr && b.bandwidth <= 64 && (ei ? atoi(ei) != 0 : true);
+    if (fused) {
+        if (idp) chain_kernel<true, true><<<grid_for_warps(b.n_reads, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
+        else chain_kernel<true, false><<<grid_for_warps(b.n_reads, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
+    } else if (b.n_big) {
+        if (idp) chain_kernel<false, true><<<grid_for_warps(b.n_big, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
+        else chain_kernel<false, false><<<grid_for_warps(b.n_big, CHAIN_WARPS), CHAIN_WARPS * 32, 0, st>>>(b, tp);
+    }
     else return 0;
     return 1;
 }

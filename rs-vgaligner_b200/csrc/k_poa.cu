@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     if (idx >= b.n_items) return;
     const u32 w = b.work[idx];
     AlignItem* itp = b.items + w;
-    if (itp->status != VGA_ALN_OK) return;
+    if (itp->status != VGA_ALN_OK || itp->fmt != 0u) return;       // fmt 1: plane rows of the 16x2 fill kernel (k_poa_trace_planes.cu)
     const AlignItem it = *itp;
     const u32 nb = it.node_base;
     const u32* __restrict__ rs = b.nd_row_start + nb;
@@ -551,6 +551,7 @@ int poa_long_mode(u64 n_long_items, int n_sms) {
 }
 static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
 int poa_class_count() { return 9; }
+bool poa_pair_active() { return g_pair != 0; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode) {
     if (const char* e = getenv("VGA_POA_WIDE")) { if (atoi(e) == 1) return 8; }      // tests: every alignment on the CTA-per-alignment kernel
     if (g_pair) {
@@ -608,9 +609,16 @@ int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st)
     const u64 threads = (u64)b.n_items * spread;
     // Tried and dropped: L2 prefetch of the diagonal trace word 2-8 rows ahead (consecutive rows lie back to back in a pool
     // chunk, so the stride is predictable): C2 3.44 -> 3.55-3.70 ms, C4 14.0 -> 18.6-19.8 ms, C5 unchanged (gpurun_out/ab13).
-    if (spread >= 4) poa_trace_kernel<true><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
-    else poa_trace_kernel<false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
-    return 1;
+    // one launch per trace format over the same work list (an item is traced by the kernel of its format, AlignItem.fmt);
+    // has_words / has_planes: which fill families contributed to the list
+    int n = 0;
+    if (b.has_words) {
+        if (spread >= 4) poa_trace_kernel<true><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
+        else poa_trace_kernel<false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
+        n++;
+    }
+    if (b.has_planes) n += launch_poa_trace_planes(ix, b, spread, st);
+    return n;
 }
 
 // ---------------------------------------------------------------------------------------------

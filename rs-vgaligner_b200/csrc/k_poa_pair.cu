@@ -79,7 +79,7 @@ struct SpanOut { i32 mx, lpos, rpos, mn; };   // mn: smallest Hhat of a band cel
 // carried from one span of a row to the next (group-uniform)
 struct SpanCarry {
     i32 fc1, fc2;      // F1', F2' arriving at the first column of the span (F' = F + o + e)
-    u32 hq;            // low half: old H (previous row) of the column left of the span; high half: 1 - new H of that column
+    u32 hq;            // low half: old H (previous row) of the column left of the span
 };
 
 template <int G> __device__ __forceinline__ u32 pair_group_mask(u32 lane) {
@@ -185,44 +185,26 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
             mxacc = __vmaxs2(mxacc, H[k][t]);
         }
     }
-    // 1 - H of the column left of the lane's first one (F fields of pair 0 of block 0); the first column of a row has none (don't care)
-    const u32 qlast = __vadd2(~H[NB - 1][3], 0x00020002u);
-    u32 qleft = __shfl_up_sync(FULLM, qlast, 1, G);
-    if (gl == 0) qleft = cy.hq;
     // carries for the next span: everything comes from the last lane of the group
     cy.fc1 = __shfl_sync(FULLM, tot1, G - 1, G);
     cy.fc2 = __shfl_sync(FULLM, tot2, G - 1, G);
-    cy.hq = __shfl_sync(FULLM, __byte_perm(hold_last, qlast, 0x7632), G - 1, G);
-    // ---- sweep 2b: E', trace words, stores
+    cy.hq = __shfl_sync(FULLM, hold_last >> 16, G - 1, G);
+    // ---- sweep 2b: E' and the stores.  The trace of the row IS the three planes (H, E1', E2') as they go to shared memory:
+    // 48 bytes per block to the pool; F1 / F2 are re-derived by the traceback where it needs them (k_poa_trace_planes.cu)
 #pragma unroll
     for (int k = 0; k < NB; k++) {
-        u32 q[4], wlo[4], whi[4], e1n[4], e2n[4];
-#pragma unroll
-        for (int t = 0; t < 4; t++) q[t] = __vadd2(~H[k][t], 0x00020002u);         // 1 - H
-        const u32 ql0 = __byte_perm(qleft, q[3], 0x5432);                          // (column 8k-1, column 8k+3)
-        qleft = q[3];
+        u32 e1n[4], e2n[4];
 #pragma unroll
         for (int t = 0; t < 4; t++) {
-            const u32 nq = ~H[k][t];
-            const u32 u1 = __vadd2(nq, P16(PO1 + 1)), u2 = __vadd2(nq, P16(PO2 + 1));   // o - H
-            const u32 d1 = __viaddmin_s16x2_relu(x1[k][t], u1, P16(PO1));           // E1' - (H - oe1) in [0, o1]
-            const u32 d2 = __viaddmin_s16x2_relu(x2[k][t], u2, P16(PO2));
-            const u32 ql = t == 0 ? ql0 : q[t - 1];
-            const u32 g1 = __viaddmin_s16x2_relu(f1[k][t], ql, P16(PO1 + 1));       // max(F1 - (Hleft - oe1), -1) + 1
-            const u32 g2 = __viaddmin_s16x2_relu(f2[k][t], ql, P16(PO2 + 1));
-            const u32 hi = d1 + d2 * 8u + g1 * 256u + g2 * 2048u;                   // fields are bounded: no carry between halves
-            wlo[t] = __byte_perm(H[k][t], hi, 0x5410);
-            whi[t] = __byte_perm(H[k][t], hi, 0x7632);
             e1n[t] = __viaddmax_s16x2(x1[k][t], P16(-PE1), __vadd2(H[k][t], P16(-POE1)));
             e2n[t] = __viaddmax_s16x2(x2[k][t], P16(-PE2), __vadd2(H[k][t], P16(-POE2)));
         }
         if (live && bme + k <= bend) {
-            uint4* const t4 = (uint4*)(tr + 8 * (bme + k - b0));
-            t4[0] = make_uint4(wlo[0], wlo[1], wlo[2], wlo[3]);
-            t4[1] = make_uint4(whi[0], whi[1], whi[2], whi[3]);
-            Hpl[bme + k] = make_uint4(H[k][0], H[k][1], H[k][2], H[k][3]);
-            E1pl[bme + k] = make_uint4(e1n[0], e1n[1], e1n[2], e1n[3]);
-            E2pl[bme + k] = make_uint4(e2n[0], e2n[1], e2n[2], e2n[3]);
+            const uint4 hq = make_uint4(H[k][0], H[k][1], H[k][2], H[k][3]);
+            const uint4 e1q = make_uint4(e1n[0], e1n[1], e1n[2], e1n[3]), e2q = make_uint4(e2n[0], e2n[1], e2n[2], e2n[3]);
+            uint4* const t4 = (uint4*)(tr + 12 * (bme + k - b0));
+            t4[0] = hq; t4[1] = e1q; t4[2] = e2q;
+            Hpl[bme + k] = hq; E1pl[bme + k] = e1q; E2pl[bme + k] = e2q;
         }
     }
     // guards: H(beg-1) = -inf (diagonal of column beg in the next row) and E'(end+1) = -inf (vertical of column end+1).
@@ -238,25 +220,31 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
     }
     // ---- maximum of the span and its leftmost / rightmost column (abPOA simd_abpoa_ada_max_i).  Masked cells are below
     // every in-band value of their block: left of beg they are -inf, right of end they hold an F that decays from H(end).
-    i32 mx = imax(sext16(mxacc), (i32)mxacc >> 16);
-#pragma unroll
-    for (int d = G / 2; d > 0; d >>= 1) mx = imax(mx, __shfl_xor_sync(FULLM, mx, d, G));
-    const u32 mxp = both16(mx);
+    // Every lane marks the columns that attain ITS maximum; (max, leftmost) and (max, rightmost) are then reduced as two
+    // independent keys in the same three shuffle rounds (a lane whose maximum is below the span's loses both).  Columns are
+    // biased by 8 (a lane left of the band starts at column -8); they stay below 512 in this class.
+    const i32 mxl = imax(sext16(mxacc), (i32)mxacc >> 16);
+    const u32 mxp = both16(mxl);
     u32 eq = 0;
 #pragma unroll
     for (int k = 0; k < NB; k++) {
 #pragma unroll
         for (int t = 0; t < 4; t++) {
             bool ph, pl;
-            (void)__vibmax_s16x2(H[k][t], mxp, &ph, &pl);          // H >= mx  <=>  H == mx
+            (void)__vibmax_s16x2(H[k][t], mxp, &ph, &pl);          // H >= lane max  <=>  H == lane max
             if (pl) eq |= 1u << (8 * k + t);
             if (ph) eq |= 1u << (8 * k + t + 4);
         }
     }
-    u32 key = 0;                                  // (511 - leftmost) << 16 | rightmost; lanes without a maximum lose both
-    if (eq) key = ((u32)(511 - (cfirst + __ffs((int)eq) - 1)) << 16) | (u32)(cfirst + 31 - __clz((int)eq));
+    const u32 mxb = (u32)(mxl + 32768) << 9;
+    u32 kL = mxb | (u32)(511 - (cfirst + 8 + __ffs((int)eq) - 1));
+    u32 kR = mxb | (u32)(cfirst + 8 + 31 - __clz((int)eq));
 #pragma unroll
-    for (int d = G / 2; d > 0; d >>= 1) key = __vmaxs2(key, __shfl_xor_sync(FULLM, key, d, G));
+    for (int d = G / 2; d > 0; d >>= 1) {
+        const u32 oL = __shfl_xor_sync(FULLM, kL, d, G), oR = __shfl_xor_sync(FULLM, kR, d, G);
+        kL = max(kL, oL); kR = max(kR, oR);
+    }
+    const i32 mx = (i32)(kL >> 9) - 32768;
     SpanOut o;
     o.mn = 0;
     if (CHK) {
@@ -266,8 +254,8 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
         o.mn = mn;
     }
     o.mx = mx;
-    o.lpos = 511 - (i32)(key >> 16);
-    o.rpos = (i32)(key & 0xffffu);
+    o.lpos = 511 - 8 - (i32)(kL & 511u);
+    o.rpos = (i32)(kR & 511u) - 8;
     return o;
 }
 
@@ -333,7 +321,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 i32 h = INT_MIN;
                 if (sx < S && b.nd_first_succ[nb + sx] < 0) {
                     const RowInfo ri = rows[rs[sx + 1] - 1];
-                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - trace_col0(ri.beg))]);
+                    if (ri.end >= qlen) h = (i32)((const short*)(b.pool + (u64)ri.toff * 4))[planes_cell(ri.beg, qlen)];
                 }
                 i32 mx = h;
 #pragma unroll
@@ -354,6 +342,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
             out->score = status == VGA_ALN_OK ? best : 0;
             out->end_node = bs;
             out->cells = cells;
+            out->fmt = status == VGA_ALN_OK ? 1u : 0u;          // plane trace rows (k_poa_trace_planes.cu)
             out->n_runs = 0; out->n_path = 0; out->path_len = 0; out->start_off = 0; out->end_off = 0; out->n_aligned = 0;
         }
         phase = PH_FETCH;
@@ -435,8 +424,8 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
             const i32 W = end - beg + 1;
             const i32 nblocks = ((end + 8) >> 3) - ((beg + 8) >> 3) + 1;
             if (beg > end) status = VGA_ALN_BAND_ERR;
-            // pool space: whole blocks, one trace word per cell
-            const u64 need = (u64)nblocks * 8;
+            // pool space: whole blocks, three int16 planes (12 words) per block
+            const u64 need = (u64)nblocks * 12;
             if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
                 unsigned long long got = 0;
                 const u64 take = need > PAIR_POOL_CHUNK ? need : PAIR_POOL_CHUNK;
@@ -474,16 +463,13 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                             const u32 p = pl[x];
                             const int2 pbe = *(const int2*)(b.nd_state + nb + p);
                             // this kernel keeps the trace offset of a node's last row in NodeState.pad0 (one dependent load less)
-                            const u32* __restrict__ tw = b.pool + (u64)(u32)b.nd_state[nb + p].pad0 * 4;
-                            const i32 pc0 = trace_col0(pbe.x);
+                            const short* __restrict__ tw = (const short*)(b.pool + (u64)(u32)b.nd_state[nb + p].pad0 * 4);
 #pragma unroll 2
                             for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
                                 i32 hv = NEG16, e1v = NEG16, e2v = NEG16;
                                 if (j >= pbe.x && j <= pbe.y) {
-                                    const u32 v = tw[j - pc0];
-                                    hv = sext16(v);
-                                    e1v = hv - POE1 + (i32)((v >> 16) & 7u);
-                                    e2v = hv - POE2 + (i32)((v >> 19) & 31u);
+                                    const short* c = tw + planes_cell(pbe.x, j);
+                                    hv = c[0]; e1v = c[8]; e2v = c[16];
                                 }
                                 const int xx = hw_index(j);
                                 if (x > 0) {
@@ -590,9 +576,18 @@ int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n
     static const int nbenv = getenv("VGA_POA_NBMAX") ? atoi(getenv("VGA_POA_NBMAX")) : 0;     // A/B measurements
     static const int genv = getenv("VGA_POA_G") ? atoi(getenv("VGA_POA_G")) : 0;
     const int nbmax = nbenv ? nbenv : b.nb_hint;
-    const int g = genv ? genv : 8;
+    // subgraphs much longer than their reads (nb_hint 3: most rows at full band width) keep 8 lanes x 3 blocks; otherwise a
+    // row has ~9 blocks and 4 lanes x 2 blocks waste fewer block slots (C4: fill 170 -> 141 ms per 2 M reads, gpurun_out/r02d)
+    const int g = genv ? genv : (nbmax >= 3 ? 8 : 4);
     if (cls == 1) { if (nbmax <= 2) launch_pair<8, 2, 4, true>(ix, b, n_sms, st); else launch_pair<8, 3, 4, true>(ix, b, n_sms, st); }
-    else if (g == 4) { if (nbmax <= 2) launch_pair<4, 2, 4, false>(ix, b, n_sms, st); else launch_pair<4, 3, 4, false>(ix, b, n_sms, st); }
+    else if (g == 4) {
+        static const int minb = getenv("VGA_POA_MINB") ? atoi(getenv("VGA_POA_MINB")) : 4;     // A/B: CTAs per SM the register budget is cut for
+        if (nbmax <= 2) {
+            if (minb == 5) launch_pair<4, 2, 5, false>(ix, b, n_sms, st);
+            else if (minb == 6) launch_pair<4, 2, 6, false>(ix, b, n_sms, st);
+            else launch_pair<4, 2, 4, false>(ix, b, n_sms, st);
+        } else launch_pair<4, 3, 4, false>(ix, b, n_sms, st);
+    }
     else if (g == 2) { if (nbmax <= 2) launch_pair<2, 2, 4, false>(ix, b, n_sms, st); else launch_pair<2, 3, 4, false>(ix, b, n_sms, st); }
     else if (nbmax == 1) launch_pair<8, 1, 4, false>(ix, b, n_sms, st);
     else if (nbmax == 2) launch_pair<8, 2, 4, false>(ix, b, n_sms, st);

@@ -35,6 +35,9 @@ __device__ __forceinline__ u32 base_code(u32 c) {
 // the 2-bit codes (and of the non-ACGT / past-the-end flag) for 32 positions, and the k-mer starting at position
 // i0+lane is a funnel shift over the planes of this chunk and the next one — the slot keys are stored in the same
 // bit-plane form (kmer_planes_from_2bit), so no per-base packing happens here.
+// COMPACT: the bucket table of common.cuh (k <= 16) — one 64-byte bucket per probe; koff receives the entry's payload
+// (an inline anchor, or the first element of the key's run in pos2), kcnt the number of positions.
+template <bool COMPACT>
 __global__ void __launch_bounds__(SEED_WARPS * 32)
 seed_count_kernel(DevIndex ix, const char* __restrict__ seqs, const u64* __restrict__ seq_off, u32 n,
                   const u64* __restrict__ read_koff, u32* __restrict__ kcnt, u32* __restrict__ koff,
@@ -65,6 +68,34 @@ seed_count_kernel(DevIndex ix, const char* __restrict__ seqs, const u64* __restr
                 const u32 bad = __funnelshift_r(pb, nbad, lane) & kmask;
                 if (!bad) {
                     const u32 lo = __funnelshift_r(p0, n0, lane) & kmask, hi = __funnelshift_r(p1, n1, lane) & kmask;
+                    if (COMPACT) {
+                        const u32 key32 = lo | (hi << 16);
+                        u32 bi = ct_bucket(key32, ix.n_buckets);
+                        while (true) {
+                            const uint4* bp = ix.buckets + 4ull * bi;
+                            const uint4 e0 = __ldg(bp), e1 = __ldg(bp + 1), e2 = __ldg(bp + 2), e3 = __ldg(bp + 3);
+                            u32 pay = 0;
+                            bool hit = false;
+                            if (e0.x == key32 && (e0.x | e0.y)) { pay = e0.y; hit = true; }
+                            if (e0.z == key32 && (e0.z | e0.w)) { pay = e0.w; hit = true; }
+                            if (e1.x == key32 && (e1.x | e1.y)) { pay = e1.y; hit = true; }
+                            if (e1.z == key32 && (e1.z | e1.w)) { pay = e1.w; hit = true; }
+                            if (e2.x == key32 && (e2.x | e2.y)) { pay = e2.y; hit = true; }
+                            if (e2.z == key32 && (e2.z | e2.w)) { pay = e2.w; hit = true; }
+                            if (e3.x == key32 && (e3.x | e3.y)) { pay = e3.y; hit = true; }
+                            if (e3.z == key32 && (e3.z | e3.w)) { pay = e3.w; hit = true; }
+                            if (hit) {
+                                if (pay & CT_INLINE) { cnt = 1; off = pay; }
+                                else {
+                                    cnt = (pay >> 26) & 31u; off = pay & CT_LOW26;
+                                    if (cnt > CT_MAX_CNT) { cnt = __ldg(ix.pos2 + off).x; off++; }      // header element: the real count
+                                }
+                                break;
+                            }
+                            if ((e3.z | e3.w) == 0) break;           // room in this bucket: the key is not in the index
+                            bi = bi + 1 == ix.n_buckets ? 0 : bi + 1;
+                        }
+                    } else {
                     const u64 key = ((u64)hi << 32) | lo;
                     u32 h = (u32)kmer_slot_hash(key) & ix.slot_mask;
                     while (true) {
@@ -72,6 +103,7 @@ seed_count_kernel(DevIndex ix, const char* __restrict__ seqs, const u64* __restr
                         if (raw.w == 0) break;                      // empty slot: not in index
                         if (raw.x == lo && raw.y == hi) { off = raw.z; cnt = raw.w; break; }
                         h = (h + 1) & ix.slot_mask;
+                    }
                     }
                 }
                 kcnt[kb + i] = cnt;
@@ -84,6 +116,7 @@ seed_count_kernel(DevIndex ix, const char* __restrict__ seqs, const u64* __restr
     }
 }
 
+template <bool COMPACT>
 __global__ void __launch_bounds__(SEED_WARPS * 32)
 seed_emit_kernel(DevIndex ix, u32 n, const u64* __restrict__ read_koff, const u32* __restrict__ kcnt,
                  const u32* __restrict__ koff, const u32* __restrict__ read_aoff, u32* __restrict__ a_qb,
@@ -113,7 +146,11 @@ seed_emit_kernel(DevIndex ix, u32 n, const u64* __restrict__ read_koff, const u3
             const u32 first = carry + incl - cnt;          // Anchor.id of this k-mer's first anchor
             for (u32 t = 0; t < cnt; t++) {                // table order (src/index.rs:372-378)
                 const u32 id = first + t;
-                const u32 tb = __ldg(ix.pos_tb + off + t), te = __ldg(ix.pos_te + off + t);
+                u32 tb, te;
+                if (COMPACT) {
+                    if (off & CT_INLINE) { tb = off & CT_LOW26; te = tb + ix.k + ((off >> 26) & 31u); }
+                    else { const uint2 pp = __ldg(ix.pos2 + off + t); tb = pp.x; te = pp.y; }
+                } else { tb = __ldg(ix.pos_tb + off + t); te = __ldg(ix.pos_te + off + t); }
                 a_qb[abase + id] = i;                      // query_begin = i, query_end = i + k
                 a_tb[abase + id] = tb;
                 a_te[abase + id] = te;
@@ -140,13 +177,22 @@ int launch_read_prep(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st) 
 }
 
 int launch_seed_count(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st) {
-    seed_count_kernel<<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
+    if (ix.n_buckets)
+        seed_count_kernel<true><<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
+            ix, b.seqs, b.seq_off, b.n_reads, b.read_koff, b.kcnt, b.koff, b.read_acnt);
+    else
+    seed_count_kernel<false><<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
         ix, b.seqs, b.seq_off, b.n_reads, b.read_koff, b.kcnt, b.koff, b.read_acnt);
     return 1;
 }
 
 int launch_seed_emit(const DevIndex& ix, const SeedBuffers& b, cudaStream_t st) {
-    seed_emit_kernel<<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
+    if (ix.n_buckets)
+        seed_emit_kernel<true><<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
+            ix, b.n_reads, b.read_koff, b.kcnt, b.koff, b.read_aoff, b.a_qb, b.a_tb, b.a_te, b.sort_key_in,
+            b.sort_val_in);
+    else
+    seed_emit_kernel<false><<<grid_for_warps(b.n_reads, SEED_WARPS), SEED_WARPS * 32, 0, st>>>(
         ix, b.n_reads, b.read_koff, b.kcnt, b.koff, b.read_aoff, b.a_qb, b.a_tb, b.a_te, b.sort_key_in,
         b.sort_val_in);
     return 1;

@@ -44,7 +44,7 @@ struct DBuf {
 enum {
     B_SEQS, B_SEQOFF, B_KOFF, B_KCNT, B_KSLOT, B_ACNT, B_AOFF, B_AQB, B_ATB, B_ATE, B_KEYIN, B_VALIN, B_KEYOUT, B_VALOUT,
     B_CUB, B_BIG, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
-    B_CATE, B_CASC, B_GAP, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
+    B_CATE, B_CASC, B_GAP, B_GAPI, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
     B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDSTATE, B_ROWS, B_ROWMETA,
     B_POOL, B_WORK, B_TWORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
     B_DBGSUBCNT, B_DBGSUBOFF, B_DBGSUB, B_DBGEDGECNT, B_DBGEDGEOFF, B_DBGEDGE, B_CELLS, B_COUNT
@@ -61,6 +61,7 @@ struct vga_workspace {
     bool scratch_zeroed = false;
     u64 pool_capped_words = 0;  // size the trace pool was cut to by free memory (0: never cut)
     double gap_k = -1, gap_max = -1;
+    bool gap_int_ok = false;
 };
 
 namespace vga {
@@ -375,10 +376,28 @@ static void upload_gapcost(Ctx& c, u32 k, u32 max_gap) {
         volatile double l = 0.5 * std::log2((double)x);
         g[x] = b + l;
     }
+    // Integer form of the same table for the all-integer DP of k_chain.cu: the reference's score is
+    // round((f_a + m - gap_cost) * 1000) / 1000 with f_a = A / 1000 for an integer A, i.e. round(A + 1000 m - 1000 gap_cost)
+    // up to the rounding errors of the three f64 operations (< 2e-7 for |score| < 2^18).  1000 * gap_cost(g) is a fixed
+    // real number per g; when its fractional part is further than 1e-4 from 1/2 for EVERY g, no rounding error can move the
+    // result across a rounding boundary and the f64 evaluation equals A + 1000 m - K[g] with K[g] = nearest integer —
+    // exactly, for every A.  (k = 11, 15, max_gap = 1000: the closest is g = 881 at 9e-4.)  Otherwise the f64 body runs.
+    std::vector<i32> gi(max_gap + 1);
+    bool int_ok = max_gap < CHAIN_KMAX;
+    gi[0] = 0;
+    for (u32 x = 1; x <= max_gap && int_ok; x++) {
+        const long double t = (long double)g[x] * 1000.0L;       // exact: a double times 1000 fits the 64-bit mantissa
+        const long double fl = floorl(t);
+        const long double fr = t - fl;
+        if (fabsl(fr - 0.5L) < 1e-4L || t > 2.0e9L) int_ok = false;
+        gi[x] = (i32)(fl + (fr > 0.5L ? 1 : 0));
+    }
     double* d = w->b[B_GAP].get<double>(max_gap + 1);
+    i32* di = w->b[B_GAPI].get<i32>(max_gap + 1);
     VGA_CUDA(cudaMemcpyAsync(d, g.data(), g.size() * sizeof(double), cudaMemcpyHostToDevice, c.st));
+    VGA_CUDA(cudaMemcpyAsync(di, gi.data(), gi.size() * sizeof(i32), cudaMemcpyHostToDevice, c.st));
     VGA_CUDA(cudaStreamSynchronize(c.st));
-    w->gap_k = k; w->gap_max = max_gap;
+    w->gap_k = k; w->gap_max = max_gap; w->gap_int_ok = int_ok;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -449,6 +468,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     ChainBuffers cb;
     cb.n_reads = n; cb.read_aoff = sb.read_aoff; cb.a_qb = sb.a_qb; cb.a_tb = sb.a_tb; cb.a_te = sb.a_te;
     cb.sidx = val_out; cb.gapcost = (const double*)w->b[B_GAP].p;
+    cb.gapcost_i = w->gap_int_ok ? (const i32*)w->b[B_GAPI].p : nullptr;
     cb.big_list = big_list; cb.n_big = n_big;
     cb.f = w->b[B_F].get<double>(A); cb.pred = w->b[B_PRED].get<i32>(A);
     cb.pred_dbg = dbg ? w->b[B_PREDDBG].get<i32>(A) : nullptr;
@@ -691,8 +711,9 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                 // rows are stored from an 8-column boundary (trace_col0); no kernel computes a band wider than 1024 columns
                 est[i] = (u64)(nrows * (std::min<i64>(west, 1024) + 12));
                 if (qlen < 256) { if ((u64)qlen > qm) qm = (u64)qlen; sr += (u64)nrows; sq += (u64)qlen; }
-                et += est[i];
                 const int ci = poa_class_for(qlen, nrows, west, P, pb.long_mode);
+                if (ci <= 1 && poa_pair_active()) est[i] += est[i] / 2;     // plane rows of the 16x2 kernel: 12 words per 8-column block
+                et += est[i];
                 const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
                 key[i] = (u32)(ci * NB + (NB - 1 - std::min(lb, NB - 1)));
                 h[key[i]]++;
@@ -758,6 +779,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     // launch when the pool is about to run out (or at the end), after which the pool starts over.
     std::vector<u32> trace_list;
     trace_list.reserve(NI);
+    bool trace_words = false, trace_planes = false;      // fill families of the items waiting in trace_list
     u64 pool_acc = warp_slack;                  // estimated words in use since the last traceback
     u64 used_prev = 0;                          // pool counter after the previous wave (timeline print only)
     VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
@@ -765,6 +787,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         if (!trace_list.empty()) {
             VGA_CUDA(cudaMemcpyAsync(d_twork, trace_list.data(), 4ull * trace_list.size(), cudaMemcpyHostToDevice, st));
             tbuf.n_items = (u32)trace_list.size(); tbuf.work = d_twork;
+            tbuf.has_words = trace_words; tbuf.has_planes = trace_planes;
+            trace_words = trace_planes = false;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
             c.launches += launch_poa_trace(dv, tbuf, st);
             stage_check(st, "poa_trace");
@@ -823,6 +847,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             for (int cj = ci + 1; cj < NCLS && traced_here; cj++) traced_here = cls[cj].empty();
             if (traced_here) {
                 tbuf.n_items = nw; tbuf.work = d_work;
+                tbuf.has_words = ci > 1 || !poa_pair_active(); tbuf.has_planes = !tbuf.has_words;
                 c.launches += launch_poa_trace(dv, tbuf, st);
                 stage_check(st, "poa_trace");
                 VGA_CUDA(cudaEventRecord(w->ev[10], st));
@@ -862,7 +887,13 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                     if (nc >= 0) cls[nc].push_back(it); else done++;
                 }
                 else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
-                else { done++; if (h_status[x] == VGA_ALN_OK && !traced_here) trace_list.push_back(it); }
+                else {
+                    done++;
+                    if (h_status[x] == VGA_ALN_OK && !traced_here) {
+                        trace_list.push_back(it);
+                        if (ci <= 1 && poa_pair_active()) trace_planes = true; else trace_words = true;
+                    }
+                }
             }
             pos = end;
             if (!again.empty()) {

@@ -48,6 +48,9 @@ void resolve_pointers(vga_index* ix) {
     d.slots = (const Slot*)(b + h.off_slots);
     d.pos_tb = (const u32*)(b + h.off_pos_tb);
     d.pos_te = (const u32*)(b + h.off_pos_te);
+    d.n_buckets = (u32)h.n_buckets;
+    d.buckets = (const uint4*)(b + h.off_buckets);
+    d.pos2 = (const uint2*)(b + h.off_pos2);
 }
 
 static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader& hdr) {
@@ -87,8 +90,48 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
     }
     if (ptb.size() >= (1ull << 32)) { set_error("too many k-mer positions"); return VGA_ERR_UNSUPPORTED; }
     u64 n_slots = 16;
-    while (n_slots < 2 * ents.size()) n_slots <<= 1;
+    const char* ct_env = getenv("VGA_TABLE_COMPACT");
+    // by default only for tables that would not stay in L2 as 16-byte slots (measured: C4 seed stage 7.8 -> 6.0 ms per 2 M reads,
+    // C5 6.8 -> 5.6 ms; on the L2-resident 2.8 MB table of C2 the longer probe body costs 0.39 -> 0.44 ms; gpurun_out/r02g)
+    const bool compact = v->k <= 16 && L < (1ull << 26) && ptb.size() + ents.size() < (1ull << 26) && !ents.empty() &&
+                         (ct_env ? atoi(ct_env) != 0 : ents.size() >= (1u << 20));
+    if (!compact) while (n_slots < 2 * ents.size()) n_slots <<= 1;            // the compact table replaces the slots
     if (n_slots > (1ull << 32)) { set_error("k-mer table too large"); return VGA_ERR_UNSUPPORTED; }
+    // ---- compact bucket table (common.cuh) when the key fits 32 bits and every field its bits; VGA_TABLE_COMPACT=0: the
+    // open-addressed 16-byte slots (A/B measurements and tests; also what k > 16 uses)
+    std::vector<u64> bkt;
+    std::vector<u32> pos2;                  // interleaved {start, end}
+    u64 n_buckets = 0;
+    {
+        if (compact) {
+            n_buckets = (ents.size() * 5 + 23) / 24 + 1;            // load 0.6: one bucket per 4.8 keys
+            bkt.assign(n_buckets * 8, 0);
+            pos2.reserve(2 * ptb.size() + 64);
+            for (const Ent& en : ents) {
+                const u32 key32 = (u32)(en.key & 0xffffu) | ((u32)(en.key >> 32) << 16);
+                u32 payload;
+                const u64 dlt = (u64)pte[en.off] - ptb[en.off] - v->k;      // unsigned: start > end wraps to a huge value
+                if (en.cnt == 1 && dlt <= CT_MAX_INLINE_DLT) payload = CT_INLINE | ptb[en.off] | ((u32)dlt << 26);
+                else {
+                    const u32 first = (u32)(pos2.size() / 2);
+                    if (en.cnt > CT_MAX_CNT) { pos2.push_back(en.cnt); pos2.push_back(0); }
+                    for (u32 t = 0; t < en.cnt; t++) { pos2.push_back(ptb[en.off + t]); pos2.push_back(pte[en.off + t]); }
+                    payload = first | ((en.cnt > CT_MAX_CNT ? CT_MAX_CNT + 1 : en.cnt) << 26);
+                }
+                u64 bi = ct_bucket(key32, (u32)n_buckets);
+                for (;;) {
+                    u64* slot = bkt.data() + bi * 8;
+                    int x = 0;
+                    while (x < 8 && slot[x] != 0) {
+                        if ((u32)slot[x] == key32) { set_error("duplicate k-mer key in index"); return VGA_ERR_INVALID; }
+                        x++;
+                    }
+                    if (x < 8) { slot[x] = (u64)key32 | ((u64)payload << 32); break; }
+                    bi = bi + 1 == n_buckets ? 0 : bi + 1;
+                }
+            }
+        }
+    }
     // ---- layout
     memset(&hdr, 0, sizeof(hdr));
     hdr.magic = INDEX_MAGIC;
@@ -103,8 +146,11 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
     place(hdr.off_edges, 4 * v->n_edges);
     place(hdr.off_pos2node, 4 * L);
     place(hdr.off_slots, sizeof(Slot) * n_slots);
-    place(hdr.off_pos_tb, 4 * ptb.size());
-    place(hdr.off_pos_te, 4 * pte.size());
+    place(hdr.off_pos_tb, compact ? 0 : 4 * ptb.size());
+    place(hdr.off_pos_te, compact ? 0 : 4 * pte.size());
+    hdr.n_buckets = n_buckets; hdr.n_pos2 = pos2.size() / 2;
+    place(hdr.off_buckets, 64 * n_buckets);
+    place(hdr.off_pos2, 4 * pos2.size());
     hdr.bytes = o;
     img.assign(o, 0);
     u8* b = img.data();
@@ -136,6 +182,7 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
     for (u64 id = 1; id <= N; id++)
         for (u32 p = sidx[id - 1]; p < sidx[id]; p++) p2n[p] = (u32)id;   // get_bv_rank (src/index.rs:427-439)
     Slot* slots = (Slot*)(b + hdr.off_slots);
+    if (!compact)
     for (const Ent& e : ents) {
         u64 h = kmer_slot_hash(e.key) & (n_slots - 1);
         while (slots[h].cnt != 0) {
@@ -144,9 +191,13 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
         }
         slots[h].key = e.key; slots[h].off = e.off; slots[h].cnt = e.cnt;
     }
-    if (!ptb.empty()) {
+    if (!ptb.empty() && !compact) {
         memcpy(b + hdr.off_pos_tb, ptb.data(), 4 * ptb.size());
         memcpy(b + hdr.off_pos_te, pte.data(), 4 * pte.size());
+    }
+    if (n_buckets) {
+        memcpy(b + hdr.off_buckets, bkt.data(), 64 * n_buckets);
+        if (!pos2.empty()) memcpy(b + hdr.off_pos2, pos2.data(), 4 * pos2.size());
     }
     memcpy(b, &hdr, sizeof(hdr));
     return VGA_OK;

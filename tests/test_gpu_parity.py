@@ -216,6 +216,22 @@ def test_bands_wider_than_1024_columns(synth5m):
     assert wide.sum() >= 5 and (g.aln_status != vg.ALN_TOO_WIDE).all()
 
 
+def test_compact_bucket_table_on_small_graphs(monkeypatch):
+    """The 8-byte-entry bucket table (k <= 16; chosen by default only for tables beyond L2 size, i.e. the 5 Mbp index) forced on
+    the small fixtures: inline single-position entries, runs in the position array, k-mers with up to 41 occurrences, and the
+    16-byte slots forced on the same inputs — identical anchors either way."""
+    for compact in ("1", "0"):
+        monkeypatch.setenv("VGA_TABLE_COMPACT", compact)
+        for graph, k in (("test.gfa", 4), ("graphs/2-DRB1-3123.gfa", 11), ("graphs/17-DRB1-3123-smooth.gfa", 11)):
+            ix = vg.Index.build(fixture_path(graph), k)
+            reads = vg.simulate_reads(ix, 800, 150 if k == 11 else 30, 0.01, 0.0005, 0.0005, 0.1, 21)
+            g, o = both(ix, reads)
+            assert_same(g, o, SEED + SORT + CHAIN)
+        rep = vg.Index.build_from_text(gfa_text(["ACGT" * 40], []), 5)       # every 5-mer occurs ~40 times: runs longer than 30
+        g, o = both(rep, FakeReads(["ACGTACGTACGTAC", "GTACGTACG"]))
+        assert_same(g, o, SEED + SORT + CHAIN)
+
+
 def test_medium_reads_and_best_n(synth):
     reads = vg.simulate_reads(synth, 300, 1000, 0.03, 0.01, 0.01, 0.0, 9)
     g, o = both(synth, reads, best_n=3, min_anchors=2)
