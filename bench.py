@@ -237,24 +237,22 @@ def gpu_record(G, name, wl, args):
     # ---- index: rank 0 builds + uploads; ONE NCCL broadcast of the device image replicates it
     ix, t_index = build_index(vg, wl, rank, world, barrier if world > 1 else None)
     t_bcast, nbytes = 0.0, 0
-    if rank == 0:
-        gix = ix.upload()
-        nbytes = ix.image_size()
+    gix = ix.upload() if rank == 0 else None
     if world > 1:
-        sz = torch.tensor([nbytes], dtype=torch.int64, device=dev)
-        dist.broadcast(sz, 0)
-        nbytes = int(sz.item())
-        img = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        # the library replicates the image itself (vga_index_broadcast: ONE ncclBroadcast over NVLink, NCCL bound at run time);
+        # torch.distributed only carries the 128-byte communicator id to the other ranks
+        cid = torch.zeros(128, dtype=torch.uint8, device=dev)
         if rank == 0:
-            ix.copy_image_to(img.data_ptr())
+            cid.copy_(torch.frombuffer(bytearray(vg.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(cid, 0)
+        id_bytes = bytes(cid.cpu().numpy().tobytes())
         barrier()
         t0 = time.perf_counter()
-        dist.broadcast(img, 0)
+        gix = vg.index_broadcast(gix, id_bytes, rank, world)
         torch.cuda.synchronize()
         t_bcast = time.perf_counter() - t0
-        if rank != 0:
-            gix = ix.adopt_device_image(img.data_ptr(), nbytes)
-        del img
+        ix._gpu = gix
+    nbytes = ix.image_size()
 
     # ---- reads: contiguous shard [rank*n/world, (rank+1)*n/world) of ONE seeded read set (one RNG stream per read)
     total = wl["reads"]

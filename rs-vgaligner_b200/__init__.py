@@ -491,6 +491,74 @@ def map_reads(index, inputs, bandwidth=50, max_gap=1000, chain_min_n_anchors=3, 
     return res
 
 
+def comm_unique_id():
+    """vga_comm_unique_id: the 128 bytes rank 0 hands to the other ranks before vga_index_broadcast."""
+    buf = (C.c_ubyte * 128)()
+    _check(gpu_lib().vga_comm_unique_id(buf), "vga_comm_unique_id")
+    return bytes(buf)
+
+
+def index_broadcast(gix, id_bytes, rank, world):
+    """vga_index_broadcast on the calling thread's device: rank 0 passes its uploaded handle, the others None; returns the
+    handle of this rank's replica (ONE ncclBroadcast of the index image inside the library)."""
+    h = C.c_void_p(gix.value if (rank == 0 and gix is not None) else None)
+    _check(gpu_lib().vga_index_broadcast(C.byref(h), id_bytes, rank, world), "vga_index_broadcast")
+    return h
+
+
+class _Slice:
+    """reads [lo, hi) of a read set, sharing the sequence bytes (offsets stay absolute, as vga_map_batch accepts them)"""
+
+    def __init__(self, reads, lo, hi):
+        self.n, self.seqs, self.offsets = hi - lo, reads.seqs, reads.offsets[lo:hi + 1]
+        self._reads, self._lo, self._hi = reads, lo, hi
+
+    @property
+    def names(self):
+        return self._reads.names[self._lo:self._hi]
+
+
+def map_reads_multi(index, inputs, n_gpus, params=None):
+    """map_reads sharded over `n_gpus` devices of this box through the C ABI alone (no torch): one host thread per GPU,
+    index replicated by vga_index_broadcast, rank r maps the contiguous range [r*n/N, (r+1)*n/N).  Returns the per-rank
+    MapResults in rank order (their concatenation is the single-GPU result: output order = input order, src/map.rs:123-133)."""
+    import threading
+    L = gpu_lib()
+    p = params or default_params()
+    _check(L.vga_init(0), "vga_init")
+    g0 = index.upload()
+    cid = comm_unique_id() if n_gpus > 1 else bytes(128)
+    out, errs = [None] * n_gpus, [None] * n_gpus
+    seqs = np.ascontiguousarray(inputs.seqs)
+    offs = np.ascontiguousarray(inputs.offsets)
+
+    def worker(r):
+        try:
+            _check(L.vga_init(r), "vga_init")
+            gix = index_broadcast(g0, cid, r, n_gpus)
+            lo, hi = inputs.n * r // n_gpus, inputs.n * (r + 1) // n_gpus
+            res = C.c_void_p()
+            _check(L.vga_map_batch(gix, seqs.ctypes.data_as(C.c_void_p), C.c_void_p(offs.ctypes.data + 8 * lo), hi - lo, C.byref(p),
+                                   C.byref(res)), "vga_map_batch")
+            out[r] = MapResults(res, index, _Slice(inputs, lo, hi))
+            if r != 0:
+                L.vga_index_free(gix)
+        except Exception as e:      # noqa: BLE001 - reported to the caller below
+            errs[r] = e
+
+    th = [threading.Thread(target=worker, args=(r,)) for r in range(1, n_gpus)]
+    for t in th:
+        t.start()
+    worker(0)
+    for t in th:
+        t.join()
+    L.vga_init(0)
+    for e in errs:
+        if e is not None:
+            raise e
+    return out
+
+
 def measure_int32_peak():
     v = C.c_double()
     _check(gpu_lib().vga_measure_int32_peak(C.byref(v)), "vga_measure_int32_peak")

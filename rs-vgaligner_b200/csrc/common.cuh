@@ -139,14 +139,6 @@ static const i32 POA_DEEP = -(1 << 30);      // generator value of masked cells 
 // stored from the 8-column block that contains beg (the pair kernel stores whole blocks with 16-byte vectors)
 __host__ __device__ static inline i32 trace_col0(i32 beg) { return beg & ~7; }
 struct RowInfo { i32 beg, end; u32 toff; i32 ref; u32 prow, meta, node, off; };
-// PLANE trace format (k_poa_pair.cu -> k_poa_trace_planes.cu): a row is stored from the 8-column block that contains beg
-// (block b = columns 8b-8 .. 8b-1), 24 int16 per block: the H plane, the E1' plane, the E2' plane, each in the 16x2 register
-// order of the fill kernel (half-word 2t = column t, 2t+1 = column t+4 of the block).  Index of H(i,j) among the int16 of the
-// row; E1' is 8 further, E2' 16 further.
-__host__ __device__ static inline u32 planes_cell(i32 beg, i32 j) {
-    const i32 c = j + 8;
-    return (u32)(((c >> 3) - ((beg + 8) >> 3)) * 24 + (((c & 3) << 1) | ((c >> 2) & 1)));
-}
 // per subgraph node: band, row-maximum span and maximum of the node's LAST row
 struct NodeState { i32 beg, end, lpos, rpos, mx, pad0, pad1, pad2; };
 
@@ -177,8 +169,6 @@ struct AlignItem {      // one (read, chain) alignment job
     u32 n_runs, n_path, path_len, start_off, end_off, n_aligned;
     u32 run_pos, path_pos;  // where the (back-to-front) traceback output starts inside its region
     u64 cells;
-    u32 fmt;                // trace format of the item's rows: 0 = one 32-bit word per cell, 1 = int16 planes per 8-column block
-    u32 pad_;
 };
 
 }  // namespace vga

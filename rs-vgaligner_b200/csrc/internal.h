@@ -114,6 +114,7 @@ struct PoaBuffers {
 // kernel classes: 0..1 = short reads on the 16x2 kernel (k_poa_pair.cu; 1 = with the per-row range check); 2 = short reads, 32 lanes
 // (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu); 8 = bands wider than 1024 columns (k_poa_wide.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
 int poa_long_mode(u64 n_long_items, int n_sms);   // long-read kernel family for the batch: 1 = shared-memory kernel, 0 = SLIDE (k_poa.cu)
+void poa_begin_batch();     // re-reads the per-batch test / A-B switches of the class selection
 int poa_class_count();
 bool poa_pair_active();    // classes 0..1 run on the 16x2 kernel (plane trace rows); false with VGA_POA_PAIR=0
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode);
@@ -135,9 +136,7 @@ struct TraceBuffers {
     u32* out_runs;           // per item region at out_base, capacity nrows+qlen+2, written back to front
     u32* out_path;           // per item region at node_base, capacity S, written back to front
     i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
-    bool has_words, has_planes;   // trace formats among the items (word rows / plane rows of the 16x2 fill kernel)
 };
-int launch_poa_trace_planes(const DevIndex& ix, const TraceBuffers& b, u32 spread, cudaStream_t st);   // k_poa_trace_planes.cu
 int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st);
 
 double measure_int32_peak();

@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     if (idx >= b.n_items) return;
     const u32 w = b.work[idx];
     AlignItem* itp = b.items + w;
-    if (itp->status != VGA_ALN_OK || itp->fmt != 0u) return;       // fmt 1: plane rows of the 16x2 fill kernel (k_poa_trace_planes.cu)
+    if (itp->status != VGA_ALN_OK) return;
     const AlignItem it = *itp;
     const u32 nb = it.node_base;
     const u32* __restrict__ rs = b.nd_row_start + nb;
@@ -537,8 +537,13 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
 // An item that does not fit its class moves to the next.
 // VGA_POA_PAIR=0 restores the 8 / 16 / 32-lane kernels of k_poa_short.cu on classes 0..2 (A/B measurements).
 static int g_pair = getenv("VGA_POA_PAIR") ? atoi(getenv("VGA_POA_PAIR")) : 1;
-// off by default: measured slower than the SLIDE kernel on the few very long subgraphs of 17-DRB1-3123-smooth (one 8-lane group per item is a longer critical path than one warp per item)
-static int g_pair_chk = getenv("VGA_POA_CHK") ? atoi(getenv("VGA_POA_CHK")) : 0;
+// Class 1, the range-checked 16x2 instance, re-centres its int16 planes on the row maximum (RowInfo.ref), so subgraphs thousands
+// of rows longer than their read (17-DRB1-3123-smooth: 1.5 k items per 125 k reads) stay inside int16 — but it is off by default:
+// measured 125 ms against 74 ms on the SLIDE kernel for those items (gpurun_out/r02l).  Few items mean two or three warps per SM,
+// so what counts is the latency of ONE row, and an 8-lane step of ~550 dependent instructions is longer than a 32-lane SLIDE row.
+// VGA_POA_CHK=1 enables it (read per batch: the tests run both).
+static int g_pair_chk = 0;
+void poa_begin_batch() { const char* e = getenv("VGA_POA_CHK"); g_pair_chk = e ? atoi(e) : 0; }
 // long reads (and everything else that is not a short-read class) run on the shared-memory kernel of k_poa_long.cu as
 // class 3; VGA_POA_LONG=0 restores the register-resident SLIDE instances on classes 3..7 (A/B measurements)
 // The shared-memory kernel wins on throughput (work proportional to the band, 64 registers), the register-resident
@@ -609,16 +614,13 @@ int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st)
     const u64 threads = (u64)b.n_items * spread;
     // Tried and dropped: L2 prefetch of the diagonal trace word 2-8 rows ahead (consecutive rows lie back to back in a pool
     // chunk, so the stride is predictable): C2 3.44 -> 3.55-3.70 ms, C4 14.0 -> 18.6-19.8 ms, C5 unchanged (gpurun_out/ab13).
-    // one launch per trace format over the same work list (an item is traced by the kernel of its format, AlignItem.fmt);
-    // has_words / has_planes: which fill families contributed to the list
-    int n = 0;
-    if (b.has_words) {
-        if (spread >= 4) poa_trace_kernel<true><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
-        else poa_trace_kernel<false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
-        n++;
-    }
-    if (b.has_planes) n += launch_poa_trace_planes(ix, b, spread, st);
-    return n;
+    // Tried and dropped (round 2): storing the fill kernel's int16 planes (H, E1', E2'; 6 B per cell) as the trace of short reads
+    // and re-deriving F in the traceback.  28 % fewer instructions in the fill (2.5 -> 1.8 warp-instructions per cell) but no
+    // time gained — the fill is bound by dependency latency at 16 warps per SM, not by issue — and the traceback of the wider
+    // rows took 36 instead of 23 ms per 2 M reads (gpurun_out/r02h, r02i).
+    if (spread >= 4) poa_trace_kernel<true><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
+    else poa_trace_kernel<false><<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(ix, b, spread);
+    return 1;
 }
 
 // ---------------------------------------------------------------------------------------------

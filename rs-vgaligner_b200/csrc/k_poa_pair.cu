@@ -46,6 +46,8 @@ static const u64 PAIR_POOL_CHUNK = 4096;       // trace words a group takes from
 static const i32 NEG16 = -32000;               // -inf of the int16 planes; reachable scores are >= -30000 in this class
 static const u32 NEGP = 0x83008300u;           // NEG16 in both halves
 static const i32 PAIR_SCORE_LIMIT = 30000;
+static const i32 PAIR_REBASE_AT = 8000;        // CHK instances: a row maximum this far below ref re-centres the planes
+static const i32 PAIR_UNREACH = 31000;         // values below -this are -inf (NEG16 plus what an unreachable cell can gain)
 static const int VT_WORDS = 8 * 9;             // validity table entries (uint4 each): [a = 0..7][z = 0..8]
 // abPOA's default convex gap model (rs-abPOA defaults)
 static const i32 PO1 = 4, PE1 = 2, PO2 = 24, PE2 = 1, POE1 = PO1 + PE1, POE2 = PO2 + PE2;
@@ -79,7 +81,7 @@ struct SpanOut { i32 mx, lpos, rpos, mn; };   // mn: smallest Hhat of a band cel
 // carried from one span of a row to the next (group-uniform)
 struct SpanCarry {
     i32 fc1, fc2;      // F1', F2' arriving at the first column of the span (F' = F + o + e)
-    u32 hq;            // low half: old H (previous row) of the column left of the span
+    u32 hq;            // low half: old H (previous row) of the column left of the span; high half: 1 - new H of that column
 };
 
 template <int G> __device__ __forceinline__ u32 pair_group_mask(u32 lane) {
@@ -185,26 +187,44 @@ __device__ __forceinline__ SpanOut span_step(u32 gl, i32 beg, i32 end, i32 bdone
             mxacc = __vmaxs2(mxacc, H[k][t]);
         }
     }
+    // 1 - H of the column left of the lane's first one (F fields of pair 0 of block 0); the first column of a row has none (don't care)
+    const u32 qlast = __vadd2(~H[NB - 1][3], 0x00020002u);
+    u32 qleft = __shfl_up_sync(FULLM, qlast, 1, G);
+    if (gl == 0) qleft = cy.hq;
     // carries for the next span: everything comes from the last lane of the group
     cy.fc1 = __shfl_sync(FULLM, tot1, G - 1, G);
     cy.fc2 = __shfl_sync(FULLM, tot2, G - 1, G);
-    cy.hq = __shfl_sync(FULLM, hold_last >> 16, G - 1, G);
-    // ---- sweep 2b: E' and the stores.  The trace of the row IS the three planes (H, E1', E2') as they go to shared memory:
-    // 48 bytes per block to the pool; F1 / F2 are re-derived by the traceback where it needs them (k_poa_trace_planes.cu)
+    cy.hq = __shfl_sync(FULLM, __byte_perm(hold_last, qlast, 0x7632), G - 1, G);
+    // ---- sweep 2b: E', trace words, stores
 #pragma unroll
     for (int k = 0; k < NB; k++) {
-        u32 e1n[4], e2n[4];
+        u32 q[4], wlo[4], whi[4], e1n[4], e2n[4];
+#pragma unroll
+        for (int t = 0; t < 4; t++) q[t] = __vadd2(~H[k][t], 0x00020002u);         // 1 - H
+        const u32 ql0 = __byte_perm(qleft, q[3], 0x5432);                          // (column 8k-1, column 8k+3)
+        qleft = q[3];
 #pragma unroll
         for (int t = 0; t < 4; t++) {
+            const u32 nq = ~H[k][t];
+            const u32 u1 = __vadd2(nq, P16(PO1 + 1)), u2 = __vadd2(nq, P16(PO2 + 1));   // o - H
+            const u32 d1 = __viaddmin_s16x2_relu(x1[k][t], u1, P16(PO1));           // E1' - (H - oe1) in [0, o1]
+            const u32 d2 = __viaddmin_s16x2_relu(x2[k][t], u2, P16(PO2));
+            const u32 ql = t == 0 ? ql0 : q[t - 1];
+            const u32 g1 = __viaddmin_s16x2_relu(f1[k][t], ql, P16(PO1 + 1));       // max(F1 - (Hleft - oe1), -1) + 1
+            const u32 g2 = __viaddmin_s16x2_relu(f2[k][t], ql, P16(PO2 + 1));
+            const u32 hi = d1 + d2 * 8u + g1 * 256u + g2 * 2048u;                   // fields are bounded: no carry between halves
+            wlo[t] = __byte_perm(H[k][t], hi, 0x5410);
+            whi[t] = __byte_perm(H[k][t], hi, 0x7632);
             e1n[t] = __viaddmax_s16x2(x1[k][t], P16(-PE1), __vadd2(H[k][t], P16(-POE1)));
             e2n[t] = __viaddmax_s16x2(x2[k][t], P16(-PE2), __vadd2(H[k][t], P16(-POE2)));
         }
         if (live && bme + k <= bend) {
-            const uint4 hq = make_uint4(H[k][0], H[k][1], H[k][2], H[k][3]);
-            const uint4 e1q = make_uint4(e1n[0], e1n[1], e1n[2], e1n[3]), e2q = make_uint4(e2n[0], e2n[1], e2n[2], e2n[3]);
-            uint4* const t4 = (uint4*)(tr + 12 * (bme + k - b0));
-            t4[0] = hq; t4[1] = e1q; t4[2] = e2q;
-            Hpl[bme + k] = hq; E1pl[bme + k] = e1q; E2pl[bme + k] = e2q;
+            uint4* const t4 = (uint4*)(tr + 8 * (bme + k - b0));
+            t4[0] = make_uint4(wlo[0], wlo[1], wlo[2], wlo[3]);
+            t4[1] = make_uint4(whi[0], whi[1], whi[2], whi[3]);
+            Hpl[bme + k] = make_uint4(H[k][0], H[k][1], H[k][2], H[k][3]);
+            E1pl[bme + k] = make_uint4(e1n[0], e1n[1], e1n[2], e1n[3]);
+            E2pl[bme + k] = make_uint4(e2n[0], e2n[1], e2n[2], e2n[3]);
         }
     }
     // guards: H(beg-1) = -inf (diagonal of column beg in the next row) and E'(end+1) = -inf (vertical of column end+1).
@@ -295,8 +315,9 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
     u32 w = 0, nb = 0, S = 0, pred_base = 0, row_base = 0, nrows = 0;
     i32 qlen = 0, wband = 0, end0 = 0;
     const u8* __restrict__ q = nullptr;
-    u32 row = 0, s = 0, o = 0, metas = 0, metas_next = 0, meta = 0;
+    u32 row = 0, s = 0, o = 0, meta = 0;
     i32 beg = 0, end = -1, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
+    i32 ref = 0;                                    // CHK instances: the planes and trace words of a row hold score - ref (RowInfo.ref)
     i32 bdone = 0, nblocks_row = 1, rl = 0, rr = 0;
     u64 cells = 0;
     u32 status = VGA_ALN_OK, custom_base = 0xffffffffu;
@@ -321,7 +342,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 i32 h = INT_MIN;
                 if (sx < S && b.nd_first_succ[nb + sx] < 0) {
                     const RowInfo ri = rows[rs[sx + 1] - 1];
-                    if (ri.end >= qlen) h = (i32)((const short*)(b.pool + (u64)ri.toff * 4))[planes_cell(ri.beg, qlen)];
+                    if (ri.end >= qlen) h = ri.ref + sext16(b.pool[(u64)ri.toff * 4 + (u32)(qlen - trace_col0(ri.beg))]);
                 }
                 i32 mx = h;
 #pragma unroll
@@ -342,7 +363,6 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
             out->score = status == VGA_ALN_OK ? best : 0;
             out->end_node = bs;
             out->cells = cells;
-            out->fmt = status == VGA_ALN_OK ? 1u : 0u;          // plane trace rows (k_poa_trace_planes.cu)
             out->n_runs = 0; out->n_path = 0; out->path_len = 0; out->start_off = 0; out->end_off = 0; out->n_aligned = 0;
         }
         phase = PH_FETCH;
@@ -363,7 +383,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 wband = b.wb + (i32)(b.wf * (float)qlen);
                 nb = it.node_base; S = it.S; row_base = it.row_base; pred_base = it.pred_base; nrows = it.nrows;
                 status = VGA_ALN_OK;
-                cells = 0; row = 0; s = 0; o = 0; ppb = 0; ppe = -1; lpos = 0; rpos = 0; mxrow = 0;
+                cells = 0; row = 0; s = 0; o = 0; ppb = 0; ppe = -1; lpos = 0; rpos = 0; mxrow = 0; ref = 0;
                 custom_base = 0xffffffffu;
                 phase = PH_ROW;
                 if (S == 0 || nrows == 0) { status = VGA_ALN_EMPTY; finish(); }
@@ -388,15 +408,19 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 }
             }
         }
-        // ---- B: row prologue (groups that start a DP row); row records (sub_rowmeta_kernel) are fetched G rows at a time
-        // (the batch after the current one is already in flight, so its latency is not on the row's critical path)
-        if (phase == PH_ROW && (row & (G - 1)) == 0) {
-            metas = row == 0 ? ((gl < nrows) ? b.row_meta[row_base + gl] : 0u) : metas_next;
-            metas_next = (row + G + gl < nrows) ? b.row_meta[row_base + row + G + gl] : 0u;
-        }
-        {
-            const u32 mt = __shfl_sync(FULLM, metas, row & (G - 1), G);
-            if (phase == PH_ROW) meta = mt;
+        // ---- B: row prologue (groups that start a DP row).  The row record (sub_rowmeta_kernel) comes by a plain cached load
+        // that every lane of the group issues for the same address; the lines it will need are pulled into L1 a few dozen rows
+        // ahead by prefetches, which have no destination register.  (A register prefetch — load G rows ahead, consume later —
+        // stalls on the warp-wide scoreboard whenever ANOTHER group of the warp has just issued its own: 10 % of all stall
+        // samples of this kernel sat on that dependency, profiles/r02_pair_stalls.txt.)
+        if (phase == PH_ROW) {
+            if ((row & 31u) == 0 && gl == 0) {
+                const u32* nx = b.row_meta + row_base + row + 32;
+                if (row == 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(nx - 32 + 31));     // rest of the first 128 bytes
+                if (row + 32 < nrows) asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
+                if (row + 64 < nrows) asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + 32));
+            }
+            meta = __ldca(b.row_meta + row_base + row);
         }
         if (phase == PH_ROW) {
             const u32 base = meta & 0xffu, kind = (meta >> 8) & 3u;
@@ -410,12 +434,28 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 np = b.nd_pred_off[nb + s + 1] - po;
                 const u32* __restrict__ pl = b.nd_pred + pred_base + po;
                 mpl = INT_MAX; mpr = 0; min_pb = INT_MAX; max_pe = -1;
+                i32 mxp = INT_MIN;
                 for (u32 x = 0; x < np; x++) {
                     const NodeState ns = b.nd_state[nb + pl[x]];
                     mpl = imin(mpl, ns.lpos + 1); mpr = imax(mpr, ns.rpos + 1);
                     min_pb = imin(min_pb, ns.beg); max_pe = imax(max_pe, ns.end);
+                    mxp = imax(mxp, ns.mx);
                 }
                 prow = b.nd_row_start[nb + pl[0] + 1] - 1;
+                if (CHK) ref = imin(mxp, 0);            // the merged row is rebuilt below, relative to the best predecessor maximum
+            }
+            if (CHK && kind == 1) ref = 0;
+            if (CHK && kind == 0 && mxrow < -PAIR_REBASE_AT) {
+                // Scores have drifted down (a subgraph thousands of rows longer than its read is mostly deletions): re-centre the
+                // previous row on its maximum.  Cells already at -inf stay there; nothing else of this alignment is relative to ref.
+                const i32 delta = -mxrow;
+                __syncwarp(gm);
+                for (int x = (int)gl; x < 24 * nblk; x += G) {
+                    const i32 v = ((short*)planes)[x];
+                    ((short*)planes)[x] = (short)(v < -PAIR_UNREACH ? NEG16 : v + delta);
+                }
+                __syncwarp(gm);
+                ref -= delta; mxrow = 0;
             }
             // adaptive band (abPOA GET_AD_DP_BEGIN/END + clipping to the predecessors' bands)
             const i32 r = qlen - (i32)(meta >> 11);
@@ -424,8 +464,8 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
             const i32 W = end - beg + 1;
             const i32 nblocks = ((end + 8) >> 3) - ((beg + 8) >> 3) + 1;
             if (beg > end) status = VGA_ALN_BAND_ERR;
-            // pool space: whole blocks, three int16 planes (12 words) per block
-            const u64 need = (u64)nblocks * 12;
+            // pool space: whole blocks, one trace word per cell
+            const u64 need = (u64)nblocks * 8;
             if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
                 unsigned long long got = 0;
                 const u64 take = need > PAIR_POOL_CHUNK ? need : PAIR_POOL_CHUNK;
@@ -439,7 +479,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 tr = b.pool + pool_cur;
                 if (gl == 0) {
                     uint4* dst = (uint4*)(b.rows + row_base + row);
-                    dst[0] = make_uint4((u32)beg, (u32)end, (u32)(pool_cur >> 2), 0u);
+                    dst[0] = make_uint4((u32)beg, (u32)end, (u32)(pool_cur >> 2), (u32)ref);
                     dst[1] = make_uint4(prow, (np < 0xffffffu ? np : 0xffffffu) | (base << 24), s, o);
                 }
                 pool_cur += need;
@@ -457,19 +497,29 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                             E2s[x] = (short)(j == 0 ? -POE2 : NEG16);
                         }
                     } else {                  // merge of the predecessors' last rows, decoded from their trace words
+                        bool lost = false;
                         const u32* __restrict__ pl = b.nd_pred + pred_base + po;
                         for (u32 x = 0; x < np; x++) {
                             // one predecessor at a time: its band and trace row are read once, its words stream through the lanes
                             const u32 p = pl[x];
                             const int2 pbe = *(const int2*)(b.nd_state + nb + p);
                             // this kernel keeps the trace offset of a node's last row in NodeState.pad0 (one dependent load less)
-                            const short* __restrict__ tw = (const short*)(b.pool + (u64)(u32)b.nd_state[nb + p].pad0 * 4);
+                            const u32* __restrict__ tw = b.pool + (u64)(u32)b.nd_state[nb + p].pad0 * 4;
+                            const i32 pc0 = trace_col0(pbe.x);
+                            const i32 adj = CHK ? b.nd_state[nb + p].pad1 - ref : 0;      // the predecessor row's ref (pad1) against this row's
 #pragma unroll 2
                             for (i32 j = jlo + (i32)gl; j <= end + 1; j += G) {
                                 i32 hv = NEG16, e1v = NEG16, e2v = NEG16;
                                 if (j >= pbe.x && j <= pbe.y) {
-                                    const short* c = tw + planes_cell(pbe.x, j);
-                                    hv = c[0]; e1v = c[8]; e2v = c[16];
+                                    const u32 v = tw[j - pc0];
+                                    hv = sext16(v);
+                                    if (CHK) {
+                                        // a reachable cell that cannot be expressed against this row's ref: the alignment goes to the 32-bit kernel
+                                        if (hv >= -PAIR_UNREACH && hv + adj < -PAIR_SCORE_LIMIT) lost = true;
+                                        hv = hv < -PAIR_UNREACH ? NEG16 : hv + adj;
+                                    }
+                                    e1v = hv - POE1 + (i32)((v >> 16) & 7u);
+                                    e2v = hv - POE2 + (i32)((v >> 19) & 31u);
                                 }
                                 const int xx = hw_index(j);
                                 if (x > 0) {
@@ -478,6 +528,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                                 Hs[xx] = (short)hv; E1s[xx] = (short)e1v; E2s[xx] = (short)e2v;
                             }
                         }
+                        if (CHK && __any_sync(gm, lost)) status = IT_RETRY_WIDER;
                     }
                 }
                 // substitution scores of this graph base: look-up bytes for the read's selectors
@@ -503,6 +554,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 nblocks_row = nblocks;
                 cy.fc1 = NEG16; cy.fc2 = NEG16; cy.hq = 0;
                 phase = PH_SPAN;
+                if (CHK && status != VGA_ALN_OK) finish();
             }
         }
         // ---- C: one span of every group's row; all 32 lanes take part (groups without a row run it with stores disabled)
@@ -535,7 +587,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                     if (gl == 0) {
                         int4* dst = (int4*)(b.nd_state + nb + s);
                         dst[0] = make_int4(beg, end, lpos, rpos);
-                        dst[1] = make_int4(mxrow, (i32)(u32)((u64)(tr - b.pool) >> 2), 0, 0);
+                        dst[1] = make_int4(ref + mxrow, (i32)(u32)((u64)(tr - b.pool) >> 2), ref, 0);
                     }
                     s++; o = 0;
                 } else o++;
@@ -579,7 +631,7 @@ int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n
     // subgraphs much longer than their reads (nb_hint 3: most rows at full band width) keep 8 lanes x 3 blocks; otherwise a
     // row has ~9 blocks and 4 lanes x 2 blocks waste fewer block slots (C4: fill 170 -> 141 ms per 2 M reads, gpurun_out/r02d)
     const int g = genv ? genv : (nbmax >= 3 ? 8 : 4);
-    if (cls == 1) { if (nbmax <= 2) launch_pair<8, 2, 4, true>(ix, b, n_sms, st); else launch_pair<8, 3, 4, true>(ix, b, n_sms, st); }
+    if (cls == 1) launch_pair<8, 3, 4, true>(ix, b, n_sms, st);      // subgraphs far longer than the read: most rows at full band width
     else if (g == 4) {
         static const int minb = getenv("VGA_POA_MINB") ? atoi(getenv("VGA_POA_MINB")) : 4;     // A/B: CTAs per SM the register budget is cut for
         if (nbmax <= 2) {

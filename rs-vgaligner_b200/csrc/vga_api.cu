@@ -670,6 +670,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     tbuf.match = P.match; tbuf.mismatch = P.mismatch; tbuf.o1 = P.o1; tbuf.e1 = P.e1; tbuf.o2 = P.o2; tbuf.e2 = P.e2; tbuf.wb = P.wb; tbuf.wf = P.wf;
     // estimated trace words per item and its kernel class; inside a class the large items go first
     // (persistent warps pull work in list order, so the long alignments do not end up as a tail)
+    poa_begin_batch();
     const int NCLS = poa_class_count();
     std::vector<u64> est(NI);
     std::vector<std::vector<u32>> cls(NCLS);
@@ -712,7 +713,6 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                 est[i] = (u64)(nrows * (std::min<i64>(west, 1024) + 12));
                 if (qlen < 256) { if ((u64)qlen > qm) qm = (u64)qlen; sr += (u64)nrows; sq += (u64)qlen; }
                 const int ci = poa_class_for(qlen, nrows, west, P, pb.long_mode);
-                if (ci <= 1 && poa_pair_active()) est[i] += est[i] / 2;     // plane rows of the 16x2 kernel: 12 words per 8-column block
                 et += est[i];
                 const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
                 key[i] = (u32)(ci * NB + (NB - 1 - std::min(lb, NB - 1)));
@@ -779,7 +779,6 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     // launch when the pool is about to run out (or at the end), after which the pool starts over.
     std::vector<u32> trace_list;
     trace_list.reserve(NI);
-    bool trace_words = false, trace_planes = false;      // fill families of the items waiting in trace_list
     u64 pool_acc = warp_slack;                  // estimated words in use since the last traceback
     u64 used_prev = 0;                          // pool counter after the previous wave (timeline print only)
     VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
@@ -787,8 +786,6 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         if (!trace_list.empty()) {
             VGA_CUDA(cudaMemcpyAsync(d_twork, trace_list.data(), 4ull * trace_list.size(), cudaMemcpyHostToDevice, st));
             tbuf.n_items = (u32)trace_list.size(); tbuf.work = d_twork;
-            tbuf.has_words = trace_words; tbuf.has_planes = trace_planes;
-            trace_words = trace_planes = false;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
             c.launches += launch_poa_trace(dv, tbuf, st);
             stage_check(st, "poa_trace");
@@ -847,7 +844,6 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             for (int cj = ci + 1; cj < NCLS && traced_here; cj++) traced_here = cls[cj].empty();
             if (traced_here) {
                 tbuf.n_items = nw; tbuf.work = d_work;
-                tbuf.has_words = ci > 1 || !poa_pair_active(); tbuf.has_planes = !tbuf.has_words;
                 c.launches += launch_poa_trace(dv, tbuf, st);
                 stage_check(st, "poa_trace");
                 VGA_CUDA(cudaEventRecord(w->ev[10], st));
@@ -887,13 +883,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                     if (nc >= 0) cls[nc].push_back(it); else done++;
                 }
                 else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
-                else {
-                    done++;
-                    if (h_status[x] == VGA_ALN_OK && !traced_here) {
-                        trace_list.push_back(it);
-                        if (ci <= 1 && poa_pair_active()) trace_planes = true; else trace_words = true;
-                    }
-                }
+                else { done++; if (h_status[x] == VGA_ALN_OK && !traced_here) trace_list.push_back(it); }
             }
             pos = end;
             if (!again.empty()) {

@@ -232,6 +232,17 @@ def test_compact_bucket_table_on_small_graphs(monkeypatch):
         assert_same(g, o, SEED + SORT + CHAIN)
 
 
+def test_range_checked_pair_class_rebases_its_planes(monkeypatch):
+    """Class 1 (VGA_POA_CHK=1): short reads whose subgraph is thousands of rows long run on the 16x2 kernel with int16 planes
+    re-centred on the row maximum (RowInfo.ref) instead of the 32-bit SLIDE kernel; same results."""
+    monkeypatch.setenv("VGA_POA_CHK", "1")
+    ix = vg.Index.build(fixture_path("graphs/17-DRB1-3123-smooth.gfa"), 11)
+    reads = vg.simulate_reads(ix, 6000, 150, 0.01, 0.0005, 0.0005, 0.1, 23)
+    g, o = both(ix, reads)
+    check_all(g, o)
+    assert ((o.aln_status == 1) & (o.aln_cells > 150 * 6000)).sum() >= 10      # subgraphs far beyond the a-priori int16 bound
+
+
 def test_medium_reads_and_best_n(synth):
     reads = vg.simulate_reads(synth, 300, 1000, 0.03, 0.01, 0.01, 0.0, 9)
     g, o = both(synth, reads, best_n=3, min_anchors=2)
@@ -380,3 +391,21 @@ def test_failed_alignment_status_reaches_the_gaf_text(synth, monkeypatch):
     text, failed = vg.gaf_text(synth, view, 1, reads.seqs, reads.offsets, reads.names)
     line = text.decode().split("\n")[ok[0]]
     assert failed == 1 and line.split("\t")[2:] == ["*"] * 9 + ["0", "*"]
+
+
+def test_n_gpus_through_the_c_abi_equal_one_gpu(synth):
+    """Multi-GPU behind the C ABI (vga_comm_unique_id + vga_index_broadcast, NCCL loaded at run time, no torch): the
+    concatenated arrays and GAF texts of N ranks equal the single-GPU result.  Needs a box with at least 2 GPUs."""
+    n_dev = vg.gpu_lib().vga_device_count()
+    if n_dev < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    n_gpus = min(n_dev, 4)
+    reads = vg.simulate_reads(synth, 6001, 150, 0.01, 0.0005, 0.0005, 0.1, 31)
+    one = vg.map_reads(synth, reads)
+    parts = vg.map_reads_multi(synth, reads, n_gpus)
+    assert sum(p.view.n_reads for p in parts) == reads.n
+    for f in ("n_anchors", "aln_status", "aln_score", "aln_cells", "aln_path_len", "aln_start_off", "aln_end_off", "aln_n_aligned",
+              "ca_qb", "ca_tb", "ca_te", "aln_path", "aln_runs"):
+        assert np.array_equal(np.concatenate([getattr(p, f) for p in parts]), getattr(one, f)), f
+    for which in (0, 1):
+        assert "".join(p.gaf(which) for p in parts) == one.gaf(which)
