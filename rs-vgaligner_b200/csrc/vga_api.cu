@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -46,13 +47,16 @@ enum {
     B_CUB, B_BIG, B_F, B_PRED, B_PREDDBG, B_NCH, B_NMEM, B_CLEN, B_CMEM, B_CHOFF, B_MEMOFF, B_CAOFF, B_CAID, B_CAQB, B_CATB,
     B_CATE, B_CASC, B_GAP, B_GAPI, B_ITEMCNT, B_ITEMOFF, B_ITEMS, B_EXT, B_CTR, B_SCRATCH, B_SZ, B_SZOFF, B_NDH, B_NDRS,
     B_NDSRC, B_NDPO, B_NDPRED, B_NDFS, B_NDRL, B_NDSTATE, B_ROWS, B_ROWMETA,
-    B_POOL, B_WORK, B_TWORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
+    B_POOL, B_WORK, B_WORK2, B_STATUS2, B_TWORK, B_OUTRUNS, B_OUTPATH, B_SEL, B_RCNT, B_ROFF, B_PCNT, B_POFF2, B_RUNS, B_PATH, B_SCAL, B_STATUS,
     B_DBGSUBCNT, B_DBGSUBOFF, B_DBGSUB, B_DBGEDGECNT, B_DBGEDGEOFF, B_DBGEDGE, B_CELLS, B_COUNT
 };
 
 struct vga_workspace {
     cudaStream_t st = nullptr, st2 = nullptr;   // st2: result copies overlapped with the POA stage
+    cudaStream_t st3 = nullptr;                 // the few long alignments of a short-read batch, beside the 16x2 kernel
     cudaEvent_t ev[12];
+    cudaEvent_t ev_e0 = nullptr, ev_e1 = nullptr;   // span of the early wave on st3 (timed)
+    cudaEvent_t ev_stf = nullptr;                   // end of the latest fill wave on st
     cudaEvent_t ev_copy = nullptr, ev_fork = nullptr, ev_join = nullptr;
     DBuf b[B_COUNT];
     int n_sms = 148;
@@ -73,6 +77,10 @@ void free_workspace(vga_index* ix) {
     if (ix->ws->ev_fork) cudaEventDestroy(ix->ws->ev_fork);
     if (ix->ws->ev_join) cudaEventDestroy(ix->ws->ev_join);
     if (ix->ws->st2) cudaStreamDestroy(ix->ws->st2);
+    if (ix->ws->st3) cudaStreamDestroy(ix->ws->st3);
+    if (ix->ws->ev_e0) cudaEventDestroy(ix->ws->ev_e0);
+    if (ix->ws->ev_e1) cudaEventDestroy(ix->ws->ev_e1);
+    if (ix->ws->ev_stf) cudaEventDestroy(ix->ws->ev_stf);
     if (ix->ws->st) cudaStreamDestroy(ix->ws->st);
     delete ix->ws;
     ix->ws = nullptr;
@@ -84,6 +92,10 @@ static vga_workspace* workspace(vga_index* ix) {
     vga_workspace* w = new vga_workspace();
     VGA_CUDA(cudaStreamCreate(&w->st));
     VGA_CUDA(cudaStreamCreateWithFlags(&w->st2, cudaStreamNonBlocking));
+    VGA_CUDA(cudaStreamCreateWithFlags(&w->st3, cudaStreamNonBlocking));
+    VGA_CUDA(cudaEventCreate(&w->ev_e0));
+    VGA_CUDA(cudaEventCreate(&w->ev_e1));
+    VGA_CUDA(cudaEventCreate(&w->ev_stf));
     VGA_CUDA(cudaEventCreateWithFlags(&w->ev_copy, cudaEventDisableTiming));
     VGA_CUDA(cudaEventCreateWithFlags(&w->ev_fork, cudaEventDisableTiming));
     VGA_CUDA(cudaEventCreateWithFlags(&w->ev_join, cudaEventDisableTiming));
@@ -782,7 +794,9 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     u64 pool_acc = warp_slack;                  // estimated words in use since the last traceback
     u64 used_prev = 0;                          // pool counter after the previous wave (timeline print only)
     VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
+    std::function<void()> collect_early_fn;      // set below; a traceback that empties the pool takes the early wave's rows with it
     auto flush_trace = [&]() {
+        if (collect_early_fn) collect_early_fn();
         if (!trace_list.empty()) {
             VGA_CUDA(cudaMemcpyAsync(d_twork, trace_list.data(), 4ull * trace_list.size(), cudaMemcpyHostToDevice, st));
             tbuf.n_items = (u32)trace_list.size(); tbuf.work = d_twork;
@@ -801,7 +815,94 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         pool_acc = warp_slack;
         used_prev = 0;
     };
+    // what a wave's statuses mean for the lists: retries move on (a wider class, or the same class again after a traceback
+    // has emptied the pool), completed alignments wait for their traceback
+    auto absorb = [&](int ci, const u32* wave, u32 nw, const u32* hs, bool traced, std::vector<u32>& again, u32& done) {
+        for (u32 x = 0; x < nw; x++) {
+            const u32 it = wave[x];
+            if (hs[x] == IT_RETRY_WIDER) {
+                const int nc = poa_class_wider(ci, pb.long_mode);
+                if (nc == 8) {
+                    // the band left the 1024 columns of the warp kernels: nothing bounds it but the read.  Measured on C5's
+                    // reverse-strand reads (random k-mer hits chained): 0.07-0.1 of rows x read length
+                    const u64 nr = h_meta[it], ql = h_meta[NI + it];
+                    est[it] = std::max<u64>(est[it], nr * (ql / 4 + 1024));
+                }
+                if (nc >= 0) cls[nc].push_back(it); else done++;
+            }
+            else if (hs[x] == IT_RETRY_POOL) again.push_back(it);
+            else { done++; if (hs[x] == VGA_ALN_OK && !traced) trace_list.push_back(it); }
+        }
+    };
+    // Early wave.  A short-read batch usually holds a few alignments outside the short-read classes (17-DRB1-3123-smooth: 1.5 k
+    // subgraphs of thousands of rows per 125 k reads).  One warp each, they are two or three warps per SM and run for as long as
+    // their longest row sequence takes (74 ms) — after the 24 ms of the 16x2 kernel that is a tail of idle SMs.  When both fit the
+    // pool together, the long class is launched FIRST on its own stream, with its own work list and counter, and the 16x2 kernel's
+    // CTAs fill what the few long-class CTAs leave of every SM.  Its statuses are absorbed when the class loop reaches it, or
+    // before any traceback empties the pool.
+    int early_ci = -1;
+    u32 early_n = 0;
+    HArr<u32> h_status2;
+    PinGuard h_status2_guard{h_status2};
+    float ms_early_span = 0;
+    bool early_timed = false, st_fill_after_fork = false;
+    auto collect_early = [&]() {
+        if (early_ci < 0 || early_n == 0) return;
+        VGA_CUDA(cudaEventSynchronize(w->ev_e1));
+        cudaEventElapsedTime(&ms_early_span, w->ev_e0, w->ev_e1);
+        early_timed = true;
+        // the POA stage lasts until both streams are done: what the early wave ran beyond the fill waves of the main stream
+        float t_st = 0;
+        if (st_fill_after_fork) { VGA_CUDA(cudaEventSynchronize(w->ev_stf)); cudaEventElapsedTime(&t_st, w->ev_e0, w->ev_stf); }
+        if (ms_early_span > t_st) ms_fill += ms_early_span - t_st;
+        std::vector<u32> again;
+        u32 done = 0;
+        std::vector<u32>& el = cls[early_ci];
+        absorb(early_ci, el.data(), early_n, h_status2.data(), false, again, done);
+        if (host_timeline()) fprintf(stderr, "[vga] poa fill class %d (early wave, beside the short-read classes): %u items, done %.3f ms after the fork\n",
+                                     early_ci, early_n, ms_early_span);
+        // the wave's items leave the list; pool retries come back at its end with a doubled estimate
+        el.erase(el.begin(), el.begin() + early_n);
+        for (u32 it : again) est[it] *= 2;
+        el.insert(el.end(), again.begin(), again.end());
+        early_n = 0;
+    };
+    collect_early_fn = collect_early;
+    {
+        const char* ee = getenv("VGA_POA_EARLY");
+        const bool on = ee ? atoi(ee) != 0 : true;
+        int cj = -1;
+        for (int x = 2; x < NCLS && cj < 0; x++) if (!cls[x].empty()) cj = x;
+        const size_t n_short = cls[0].size() + cls[1].size();
+        if (on && cj >= 3 && cj < 8 && n_short > 0 && cls[cj].size() <= (size_t)w->n_sms * 32) {
+            u64 need = warp_slack;
+            for (int x = 0; x < NCLS; x++)
+                for (u32 it : cls[x]) need += est[it] + est[it] / 4 + 64;
+            if (need <= pb.pool_words) {
+                early_ci = cj;
+                early_n = (u32)cls[cj].size();
+                u32* d_work2 = w->b[B_WORK2].get<u32>(early_n);
+                u32* d_status2 = w->b[B_STATUS2].get<u32>(early_n);
+                h_status2.alloc(early_n);
+                PoaBuffers pb2 = pb;
+                pb2.n_items = early_n; pb2.work = d_work2; pb2.work_ctr = ctr + 3;
+                VGA_CUDA(cudaMemcpyAsync(d_work2, cls[cj].data(), 4ull * early_n, cudaMemcpyHostToDevice, st));
+                VGA_CUDA(cudaMemsetAsync(ctr + 3, 0, 4, st));
+                VGA_CUDA(cudaEventRecord(w->ev_e0, st));
+                VGA_CUDA(cudaStreamWaitEvent(w->st3, w->ev_e0, 0));
+                c.launches += launch_poa_fill(dv, pb2, cj, w->n_sms, w->st3);
+                stage_check(w->st3, "poa_fill (early wave)");
+                R.stats.poa_launches++;
+                item_status_kernel<<<(early_n + 255) / 256, 256, 0, w->st3>>>(items, d_work2, early_n, d_status2);
+                c.launches++;
+                VGA_CUDA(cudaMemcpyAsync(h_status2.data(), d_status2, 4ull * early_n, cudaMemcpyDeviceToHost, w->st3));
+                VGA_CUDA(cudaEventRecord(w->ev_e1, w->st3));
+                for (u32 it : cls[cj]) pool_acc += est[it] + est[it] / 4 + 64;
+            }
+        }
+    }
     for (int ci = 0; ci < NCLS; ci++) {
+        if (ci == early_ci) collect_early();
         std::vector<u32>& list = cls[ci];
         size_t pos = 0;
         int stall = 0;
@@ -837,10 +938,11 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             stage_check(st, "poa_fill");
             R.stats.poa_launches++;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
+            if (early_n) { VGA_CUDA(cudaEventRecord(w->ev_stf, st)); st_fill_after_fork = true; }
             // A wave that holds everything there is to align (the usual short-read batch) is traced right behind its fill,
             // from the same work list, without the host round trip in between: the traceback skips every item whose status is
             // not OK, and items a retry brings back are traced by the final flush as before.
-            bool traced_here = trace_list.empty() && pos == 0 && end == list.size();
+            bool traced_here = trace_list.empty() && pos == 0 && end == list.size() && early_n == 0;
             for (int cj = ci + 1; cj < NCLS && traced_here; cj++) traced_here = cls[cj].empty();
             if (traced_here) {
                 tbuf.n_items = nw; tbuf.work = d_work;
@@ -870,21 +972,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             pool_acc = acc;
             std::vector<u32> again;
             u32 done = 0;
-            for (u32 x = 0; x < nw; x++) {
-                const u32 it = list[pos + x];
-                if (h_status[x] == IT_RETRY_WIDER) {
-                    const int nc = poa_class_wider(ci, pb.long_mode);
-                    if (nc == 8) {
-                        // the band left the 1024 columns of the warp kernels: nothing bounds it but the read.  Measured on C5's
-                        // reverse-strand reads (random k-mer hits chained): 0.07-0.1 of rows x read length
-                        const u64 nr = h_meta[it], ql = h_meta[NI + it];
-                        est[it] = std::max<u64>(est[it], nr * (ql / 4 + 1024));
-                    }
-                    if (nc >= 0) cls[nc].push_back(it); else done++;
-                }
-                else if (h_status[x] == IT_RETRY_POOL) again.push_back(it);
-                else { done++; if (h_status[x] == VGA_ALN_OK && !traced_here) trace_list.push_back(it); }
-            }
+            absorb(ci, list.data() + pos, nw, h_status.data(), traced_here, again, done);
             pos = end;
             if (!again.empty()) {
                 // the pool ran out: trace what is complete, start the pool over and run the rest again
@@ -898,6 +986,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             }
         }
     }
+    collect_early();
     flush_trace();
     VGA_CUDA(cudaEventRecord(w->ev[5], st));
     tl_mark("poa waves done");
