@@ -64,6 +64,10 @@ typedef struct {
 #define VGA_FLAG_NO_ALIGN 1u     /* `map` without --also-align: chains only (src/map.rs:154) */
 #define VGA_FLAG_KEEP_DEBUG 2u   /* also return anchors / sorted order / f / pred / subgraphs (tests) */
 #define VGA_FLAG_CHAIN_SCORES 4u /* also return ca_id / ca_score (not needed by the GAF writers) */
+/* POA band granularity: the band of every DP row is widened to multiples of 8 / 16 columns, as upstream abPOA's SIMD vectors do
+ * (8 = int16 lanes of SSE4.1 ... 16 = AVX2); default 1.  A compatibility switch for comparisons with a real abPOA build. */
+#define VGA_FLAG_BAND_GRAN8 0x100u
+#define VGA_FLAG_BAND_GRAN16 0x200u
 
 /* per-read alignment status (aln_status) */
 #define VGA_ALN_PLACEHOLDER 0    /* no chain: GAFAlignment::from_placeholder_chain (src/align.rs:913-930) */

@@ -342,7 +342,7 @@ void nodes_edges(const Index& ix, const std::vector<u64>& handles, std::vector<s
 // abPOA's recurrences and value-driven backtrack.  Every tie-break below is part of the definition
 // the CUDA path must reproduce.
 // ---------------------------------------------------------------------------------------------
-const int32_t NEG_INF = -(1 << 29);
+const int32_t NEG_INF_32 = -(1 << 29);
 // ORC_BAND_DUMP=<file>: one line per DP row (row, beg, end, #pred rows, pred is the previous row, qlen) — band statistics for
 // kernel design; single-threaded runs only
 static FILE* g_band_dump = getenv("ORC_BAND_DUMP") ? fopen(getenv("ORC_BAND_DUMP"), "w") : nullptr;
@@ -366,6 +366,9 @@ void poa_align(const std::vector<std::string>& labels, const std::vector<std::pa
     const int32_t S = (int32_t)labels.size();
     const int32_t oe1 = P.o1 + P.e1, oe2 = P.o2 + P.e2, e1 = P.e1, e2 = P.e2;
     const int32_t w = P.wb + (int32_t)(P.wf * (float)qlen);
+    // compatibility switches (oracle.h): score width of the -inf sentinel, band granularity
+    const int32_t NEG_INF = (P.flags & ORC_FLAG_INT16_SCORES) ? INT16_MIN + std::max(P.mismatch, std::max(oe1, oe2)) : NEG_INF_32;
+    const int32_t gmask = (P.flags & ORC_FLAG_BAND_GRAN16) ? 15 : (P.flags & ORC_FLAG_BAND_GRAN8) ? 7 : 0;
     std::vector<int32_t> row_start(S + 1, 0);
     for (int32_t s = 0; s < S; s++) row_start[s + 1] = row_start[s] + (int32_t)labels[s].size();
     const int32_t nrows = row_start[S];
@@ -386,6 +389,7 @@ void poa_align(const std::vector<std::string>& labels, const std::vector<std::pa
         Row& r = rows[0];
         r.beg = 0;
         r.end = std::min(qlen, std::max(0, qlen - remain_src) + w);
+        r.end = std::min(qlen, r.end | gmask);                       // band granularity (g = 1: unchanged)
         int32_t W = r.end + 1;
         r.H.assign(W, NEG_INF); r.E1.assign(W, NEG_INF); r.E2.assign(W, NEG_INF);
         r.H[0] = 0; r.E1[0] = -oe1; r.E2[0] = -oe2;
@@ -414,6 +418,10 @@ void poa_align(const std::vector<std::string>& labels, const std::vector<std::pa
             for (int32_t p : pr) { min_pb = std::min(min_pb, rows[p].beg); max_pe = std::max(max_pe, rows[p].end); }
             beg = std::max(beg, min_pb);
             end = std::min(end, max_pe + 1);
+            // band granularity: widened to vector boundaries, clipped again on the right (every begin is a multiple of g,
+            // so the widened begin stays inside the predecessors' bands)
+            beg &= ~gmask;
+            end = std::min(std::min(qlen, end | gmask), max_pe + 1);
             if (beg > end) { R.status = ST_BAND_ERR; return; }
             Row& cur = rows[i];
             cur.beg = beg; cur.end = end;
@@ -831,6 +839,8 @@ const char* orc_results_gaf(orc_results_t* R, const orc_index_t* o, const char* 
             b = e == std::string::npos ? all.size() : e + 1;
         }
     }
+    const bool cs_prefix = !(which & 2);          // which: bit 0 = alignments file, bit 1 = cs string without its "cs:Z:" tag (ORC_FLAG_NO_CS_PREFIX)
+    which &= 1;
     std::string& out = R->gaf[which ? 1 : 0];
     out.clear();
     auto placeholder = [&](u32 r) {
@@ -857,7 +867,7 @@ const char* orc_results_gaf(orc_results_t* R, const orc_index_t* o, const char* 
         } else {
             uint8_t st = R->aln_status[r];
             if (st == ST_PLACEHOLDER) { placeholder(r); continue; }
-            std::string path, cs = "cs:Z:", cg;
+            std::string path, cs = cs_prefix ? "cs:Z:" : "", cg;
             for (u64 p = R->aln_path_off[r]; p < R->aln_path_off[r + 1]; p++) {
                 u64 h = R->aln_path[p];
                 path += ((h & 1) ? "<" : ">") + std::to_string(h >> 1);                          // :1127-1133

@@ -39,6 +39,13 @@ typedef struct {
 #define ORC_FLAG_NO_ALIGN 1u        /* chains only (map without --also-align) */
 #define ORC_FLAG_KEEP_DEBUG 2u      /* keep per-read anchors / sorted order / f / pred / subgraphs */
 #define ORC_FLAG_LITERAL_EXTEND 4u  /* extend_range_chain_2 exactly as written (no visited set) */
+/* abPOA-compatibility switches of the POA definition.  Real abPOA could not be run here, so each
+ * choice it might make differently is a switch that flips a constant, not a kernel: */
+#define ORC_FLAG_BAND_GRAN8 0x100u  /* band of every row widened to multiples of 8 columns (SIMD vector of 8 int16 lanes) ... */
+#define ORC_FLAG_BAND_GRAN16 0x200u /* ... or of 16 columns (AVX2); same bits as VGA_FLAG_BAND_GRAN8 / 16, the CUDA path follows */
+#define ORC_FLAG_INT16_SCORES 0x400u /* -inf is INT16_MIN + the largest single-step penalty (upstream's int16 score width) instead of
+                                        -2^29: only differs from the default when a reachable score comes near -32768 */
+#define ORC_FLAG_NO_CS_PREFIX 0x800u /* alignments GAF: the cs string without its "cs:Z:" tag (rs-abPOA's format is [RECALLED]) */
 
 void orc_default_params(orc_params_t* p);
 

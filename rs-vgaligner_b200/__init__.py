@@ -58,6 +58,7 @@ class VgaStats(C.Structure):
 
 
 VGA_FLAG_NO_ALIGN, VGA_FLAG_KEEP_DEBUG, VGA_FLAG_CHAIN_SCORES = 1, 2, 4
+VGA_FLAG_BAND_GRAN8, VGA_FLAG_BAND_GRAN16 = 0x100, 0x200
 ALN_PLACEHOLDER, ALN_OK, ALN_EMPTY, ALN_TRACE_ERR, ALN_BAND_ERR, ALN_UNSUPPORTED, ALN_TOO_WIDE = range(7)
 
 GPU_SYMBOLS = ["vga_init", "vga_device_count", "vga_index_upload", "vga_index_free", "vga_index_image_size",

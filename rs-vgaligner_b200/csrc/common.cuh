@@ -130,6 +130,19 @@ __host__ __device__ static inline u64 kmer_slot_hash(u64 key) {
 static const i32 POA_NEG_INF = -(1 << 29);   // same sentinel as the oracle
 static const i32 POA_DEEP = -(1 << 30);      // generator value of masked cells (never wins a max)
 
+// Band granularity (VGA_FLAG_BAND_GRAN8 / 16): upstream abPOA computes whole SIMD vectors, so its effective band
+// begins and ends on vector boundaries.  After the band of the row is known (adaptive rule + clipping to the predecessors), it is
+// widened to multiples of g = gmask + 1 columns and clipped again on the right; gmask = 0 leaves it as it is.  Every band begin is
+// then a multiple of g (the source row begins at 0), so the widened begin never leaves the predecessors' bands.
+__host__ __device__ static inline void band_round(i32& beg, i32& end, i32 gmask, i32 qlen, i32 max_pe) {
+    beg &= ~gmask;
+    i32 e = end | gmask;
+    if (e > qlen) e = qlen;
+    if (e > max_pe + 1) e = max_pe + 1;
+    end = e;
+}
+__host__ __device__ static inline i32 band_round_end0(i32 end0, i32 gmask, i32 qlen) { const i32 e = end0 | gmask; return e > qlen ? qlen : e; }
+
 // per DP row: band, trace location and the reference score the row's trace words are relative to
 // toff: pool offset in 4-word (16 B) units; prow: row of the first predecessor (relative to the item's
 // row_base); meta: number of predecessor rows (low 24 bits, 0 = virtual source) | graph base << 24;

@@ -110,6 +110,7 @@ struct PoaBuffers {
     i32 long_mode;           // kernel family of class 3 for this call (poa_long_mode)
     i32 qmax_short;          // longest read among the items of the short-read classes (sizes the pair kernel's shared memory)
     i32 qmax_wide;           // longest read among the items of a wide-class launch (sizes its shared-memory row)
+    i32 bgran_mask;          // band granularity - 1 (0, 7 or 15; band_round in common.cuh)
 };
 // kernel classes: 0..1 = short reads on the 16x2 kernel (k_poa_pair.cu; 1 = with the per-row range check); 2 = short reads, 32 lanes
 // (k_poa_short.cu); 3..7 = SLIDE C=8,12,16,24,32 (k_poa.cu); 8 = bands wider than 1024 columns (k_poa_wide.cu).  VGA_POA_PAIR=0 puts the 8/16/32-lane kernels of k_poa_short.cu on 0..2.
@@ -136,6 +137,7 @@ struct TraceBuffers {
     u32* out_runs;           // per item region at out_base, capacity nrows+qlen+2, written back to front
     u32* out_path;           // per item region at node_base, capacity S, written back to front
     i32 match, mismatch, o1, e1, o2, e2, wb; float wf;
+    i32 bgran_mask;
 };
 int launch_poa_trace(const DevIndex& ix, const TraceBuffers& b, cudaStream_t st);
 

@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
         NodeState* __restrict__ nst = b.nd_state + nb;
         RowInfo* __restrict__ rows = b.rows + it.row_base;
         const i32 remain_src = b.nd_remain_last[nb] + (i32)(rs[1] - rs[0]) - 1 + 1;
-        const i32 end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+        const i32 end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);
         u32 status = VGA_ALN_OK;
         // FIXED instances keep absolute H as int16: every DP step loses at most max(mismatch, o1+e1), so
         // reachable scores are >= -that*(rows+qlen); longer alignments go to a SLIDE instance
@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(POA_WARPS * 32) poa_fill_kernel(DevIndex ix, P
                 end = imin(qlen, imax(mpr, r) + wband);
                 beg = imax(beg, min_pb);
                 end = imin(end, max_pe + 1);
+                band_round(beg, end, b.bgran_mask, qlen, max_pe);
                 if (beg > end) status = VGA_ALN_BAND_ERR;
                 const i32 W = end - beg + 1;
                 const i32 cbb = SLIDE ? beg / C : 0;
@@ -369,7 +370,7 @@ __global__ void __launch_bounds__(128) poa_trace_kernel(DevIndex ix, TraceBuffer
     const i32 qlen = (i32)it.qlen;
     const i32 wband = b.wb + (i32)(b.wf * (float)qlen);
     const i32 remain_src = b.nd_remain_last[nb] + (i32)(rs[1] - rs[0]) - 1 + 1;
-    const i32 end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+    const i32 end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);
     const u32 cap = it.nrows + it.qlen + 2;
     u32* runs = b.out_runs + it.out_base;
     u32* path = b.out_path + nb;

@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
         if (S == 0 || nrows == 0) status = VGA_ALN_EMPTY;
         else {
             const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
-            end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+            end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);
         }
         for (u32 row = 0; row < nrows && status == VGA_ALN_OK; row++) {
             if ((row & 31) == 0) metas = (row + lane < nrows) ? b.row_meta[row_base + row + lane] : 0u;
@@ -226,6 +226,7 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
             const i32 r = qlen - (i32)(meta >> 11);
             beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
             end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
+            band_round(beg, end, b.bgran_mask, qlen, max_pe);
             const i32 W = end - beg + 1;
             const int cr = long_pick_cr(W);
             if (beg > end) status = VGA_ALN_BAND_ERR;

@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 } else {
                     {   // band end of the virtual source row: max_remain of the first row + 1
                         const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
-                        end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+                        end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);
                     }
                     // selectors of the read: pair p = (block p / 4, word p % 4) holds columns 8*blk - 8 + word and + 4 (query base j-1)
                     __syncwarp(gm);
@@ -461,6 +461,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
             const i32 r = qlen - (i32)(meta >> 11);
             beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
             end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
+            band_round(beg, end, b.bgran_mask, qlen, max_pe);
             const i32 W = end - beg + 1;
             const i32 nblocks = ((end + 8) >> 3) - ((beg + 8) >> 3) + 1;
             if (beg > end) status = VGA_ALN_BAND_ERR;

@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
             }
             {   // band end of the virtual source row: max_remain of the first row + 1
                 const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
-                end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+                end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);
             }
             // query profile: score of column j (query base j-1) against A, C, T, G (order of the 2-bit code (c >> 1) & 3)
             __syncwarp(gm);
@@ -287,6 +287,7 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
         const i32 r = qlen - (i32)(meta >> 11);
         beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
         end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
+        band_round(beg, end, b.bgran_mask, qlen, max_pe);
         const i32 W = end - beg + 1;
         int cr = pick_cr<G>(W);
         if (beg > end) status = VGA_ALN_BAND_ERR;

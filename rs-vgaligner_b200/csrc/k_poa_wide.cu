@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(PW_THREADS) poa_fill_wide_kernel(DevIndex ix, 
         else if (qlen + 2 * WPAD + 8 > lbuf) status = VGA_ALN_TOO_WIDE;     // the read does not fit the shared-memory row
         else {
             const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
-            end0 = imin(qlen, imax(0, qlen - remain_src) + wband);
+            end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);
             for (i32 j = (i32)tid; j <= qlen + 1; j += PW_THREADS) smq[j + WPAD] = (j >= 1 && j <= qlen) ? q[j - 1] : (u8)0;
             if (tid == 0) smh[WPAD - 1] = POA_NEG_INF;                        // column -1: M(i,0) does not exist
         }
@@ -248,6 +248,7 @@ __global__ void __launch_bounds__(PW_THREADS) poa_fill_wide_kernel(DevIndex ix, 
             const i32 r = qlen - (i32)(meta >> 11);
             beg = imax(imax(0, imin(mpl, r) - wband), min_pb);
             end = imin(imin(qlen, imax(mpr, r) + wband), max_pe + 1);
+            band_round(beg, end, b.bgran_mask, qlen, max_pe);
             const i32 W = end - beg + 1;
             const i32 CR = imax(3, (W + PW_THREADS - 1) / PW_THREADS) | 1;
             if (beg > end) status = VGA_ALN_BAND_ERR;

@@ -672,6 +672,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     pb.row_meta = d_row_meta;
     pb.match = P.match; pb.mismatch = P.mismatch; pb.o1 = P.o1; pb.e1 = P.e1; pb.o2 = P.o2; pb.e2 = P.e2; pb.wb = P.wb; pb.wf = P.wf;
     pb.qmax_short = 0; pb.nb_hint = 3;
+    pb.bgran_mask = (P.flags & VGA_FLAG_BAND_GRAN16) ? 15 : (P.flags & VGA_FLAG_BAND_GRAN8) ? 7 : 0;
     pb.work_ctr = ctr + 2; pb.pool_ctr = (unsigned long long*)(ctr + 4);
     TraceBuffers tbuf;
     memset(&tbuf, 0, sizeof(tbuf));
@@ -679,6 +680,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     tbuf.nd_row_start = sub.nd_row_start; tbuf.nd_src = sub.nd_src; tbuf.nd_pred_off = sub.nd_pred_off; tbuf.nd_pred = sub.nd_pred;
     tbuf.nd_remain_last = sub.nd_remain_last; tbuf.rows = pb.rows;
     tbuf.out_runs = w->b[B_OUTRUNS].get<u32>(tot[3]); tbuf.out_path = w->b[B_OUTPATH].get<u32>(tot[0]);
+    tbuf.bgran_mask = (P.flags & VGA_FLAG_BAND_GRAN16) ? 15 : (P.flags & VGA_FLAG_BAND_GRAN8) ? 7 : 0;
     tbuf.match = P.match; tbuf.mismatch = P.mismatch; tbuf.o1 = P.o1; tbuf.e1 = P.e1; tbuf.o2 = P.o2; tbuf.e2 = P.e2; tbuf.wb = P.wb; tbuf.wf = P.wf;
     // estimated trace words per item and its kernel class; inside a class the large items go first
     // (persistent warps pull work in list order, so the long alignments do not end up as a tail)

@@ -99,6 +99,7 @@ struct Job {
     const char* seqs;
     const uint64_t* off;
     int which;
+    bool cs_prefix;   // alignments file: the cs string with its "cs:Z:" tag (rs-abPOA's exact format is [RECALLED]: a switch, like the oracle's)
 };
 
 static inline char* put_placeholder(char* p, const Job& J, uint32_t r) {
@@ -183,7 +184,8 @@ static void format_alignments(const Job& J, uint32_t r0, uint32_t r1, Buf& out, 
         p = put_u64(p, R.aln_end_off[r]);
         p = PUT_LIT(p, "\t0\t");
         p = put_u64(p, R.aln_n_aligned[r]);
-        p = PUT_LIT(p, "\t255\tas:i:-30 cs:Z:");
+        p = PUT_LIT(p, "\t255\tas:i:-30 ");
+        if (J.cs_prefix) p = PUT_LIT(p, "cs:Z:");
         // walk the path's bases: label of a forward handle is a slice of seq_fwd, of a reverse handle the mirrored slice
         // of seq_rev (seq_from_handle, src/index.rs:503-533)
         const char* q = J.seqs + J.off[r];
@@ -240,7 +242,9 @@ char* gaf_format(const FlatIndex& ix, const GafTables& tb, const VgaResultsView*
     Names names;
     names.joined = names_joined; names.base = name_base;
     names.index(n);
-    Job J{&ix, &tb, R, &names, seqs, off, which};
+    const bool cs_prefix = !(which & 2);      // which: bit 0 = alignments file, bit 1 = no "cs:Z:" tag
+    which &= 1;
+    Job J{&ix, &tb, R, &names, seqs, off, which, cs_prefix};
     int T = threads > 0 ? threads : (int)std::max(1u, std::thread::hardware_concurrency());
     // ranges of equal output volume
     auto weight = [&](uint32_t r) -> uint64_t {

@@ -351,7 +351,7 @@ static const GafTables* tables_of(const vgah_index_t* h) {
 
 char* vgah_gaf_raw(const vgah_index_t* h, const VgaResultsView* R, const char* names_joined, uint64_t name_base, const char* seqs,
                    const uint64_t* seq_off, int which, int threads, uint64_t* len, uint64_t* n_failed) {
-    if (!h || !R || !seq_off || (which != 0 && which != 1)) { set_err("vgah_gaf: bad argument"); return nullptr; }
+    if (!h || !R || !seq_off || (which < 0 || which > 3 || which == 2)) { set_err("vgah_gaf: bad argument"); return nullptr; }
     try {
         char* c = gaf_format(h->ix, *tables_of(h), R, names_joined, name_base, seqs, seq_off, which, threads, len, n_failed);
         if (!c) set_err("vgah_gaf: out of memory");

@@ -58,7 +58,7 @@ void vgah_free_str(char*);
 
 /* GAF text from the C ABI's result arrays: GAFAlignment::{from_chain, from_placeholder_chain,
  * to_string} (src/align.rs:762-1027) and generate_alignment (src/align.rs:1096-1168).
- * which: 0 = chains file, 1 = alignments file. */
+ * which: 0 = chains file, 1 = alignments file, 3 = alignments file with the cs string without its "cs:Z:" tag. */
 char* vgah_gaf(const vgah_index_t*, const VgaResultsView* res, const vgah_reads_t* reads, int which, uint64_t* len);
 /* Same from plain arrays, formatted on `threads` host threads (0 = all cores): names_joined is '\n' separated or NULL
  * ("read<name_base+i>"); *n_failed counts reads whose device alignment did not complete (status other than OK or

@@ -122,3 +122,57 @@ def test_generated_names():
     r = R()
     r.seqs, r.offsets, r.names, r.n = reads.seqs, reads.offsets, names, reads.n
     assert got.decode() == o.gaf(oi, r, 1)
+
+
+def test_hand_derived_lines_of_the_worked_example():
+    """test.gfa, k = 4, read seq0.  Both GAF writers (the host's parallel one and the oracle's) against lines
+    derived BY HAND from the reference's record code, not from either writer:
+      chains record      src/align.rs:892-910 — query_start = first anchor's query_begin (1), query_end = last anchor's query_end
+                         (11 + 4), one "(>node:offset,>node:offset)," per anchor from AnchorPosOnGraph (src/chain.rs:89-127: the
+                         chain's anchors are (qb,tb,te) = (1,15,20), (10,21,25), (11,22,26); linearisation starts of nodes 7, 9, 10,
+                         11 are 15, 17, 21, 23, so 15 -> >7:0, 20-1 -> >9:2, 21 -> >10:0, 25-1 -> >11:1, 22 -> >10:1, 26-1 -> >11:2),
+                         six zero columns (path_length .. mapping_quality = min(f64::MIN as u64, 254) = 0), notes
+      alignments record  src/align.rs:1145-1167 — query_length = 31, 0, 31, '+', ">id" per path node, |abpoa_nodes|,
+                         aln_start_offset, aln_end_offset, 0, n_aligned_bases, 255, "as:i:-30 " + cs + ",cg:Z:" + cigar
+    The numbers of the alignments record are read from the result arrays; its cigar is rebuilt here from the run-length ops."""
+    ix = vg.Index.build(fixture_path("test.gfa"), 4)
+    reads = vg.read_seqs_from_file(fixture_path("single-read-test.fa"))
+    oi = orc.OracleIndex(ix)
+    o = oi.map_reads(reads, orc.default_params(), n_threads=1)
+    chains_line = "seq0\t31\t1\t15\t+\t(>7:0,>9:2),(>10:0,>11:1),(>10:1,>11:2),\t0\t0\t0\t0\t0\t0\tta:Z:chain,n_anchors: 3\n"
+    view = vg.view_from_arrays(o, reads.n)
+    host_chains, _ = vg.gaf_text(ix, view, 0, reads.seqs, reads.offsets, reads.names)
+    assert host_chains.decode() == chains_line
+    assert o.gaf(oi, reads, 0) == chains_line
+    # alignments record, assembled from the arrays by the rules above
+    path = "".join((">" if h % 2 == 0 else "<") + str(h // 2) for h in o.aln_path.tolist())
+    cigar, last = [], None
+    for r in o.aln_runs.tolist():
+        op, n = "MMDI"[r >> 28], r & 0xFFFFFFF
+        if cigar and cigar[-1][0] == op:
+            cigar[-1][1] += n
+        else:
+            cigar.append([op, n])
+    cigar = "".join("%d%s" % (n, op) for op, n in cigar)
+    host_aln, _ = vg.gaf_text(ix, view, 1, reads.seqs, reads.offsets, reads.names)
+    for text in (host_aln.decode(), o.gaf(oi, reads, 1)):
+        f = text.rstrip("\n").split("\t")
+        assert f[:5] == ["seq0", "31", "0", "31", "+"] and f[5] == path == ">6>7>9>10>11>12>13>14>16>17"
+        assert f[6:12] == [str(int(o.aln_path_len[0])), str(int(o.aln_start_off[0])), str(int(o.aln_end_off[0])), "0",
+                           str(int(o.aln_n_aligned[0])), "255"]
+        assert f[12].startswith("as:i:-30 ") and f[12].endswith(",cg:Z:" + cigar) and cigar == "5M3I6M1D17M"
+        assert text.endswith("\n") and text.count("\n") == 1
+
+
+def test_cs_prefix_switch_in_both_writers():
+    """which | 2: the alignments record's cs string without its "cs:Z:" tag (rs-abPOA's exact format is [RECALLED]; the switch
+    exists in the oracle's writer and in the host's so a comparison with the real binary flips a constant)."""
+    ix = vg.Index.build(fixture_path("test.gfa"), 4)
+    reads = vg.read_seqs_from_file(fixture_path("single-read-test.fa"))
+    oi = orc.OracleIndex(ix)
+    o = oi.map_reads(reads, orc.default_params(), n_threads=1)
+    view = vg.view_from_arrays(o, reads.n)
+    with_tag = vg.gaf_text(ix, view, 1, reads.seqs, reads.offsets, reads.names)[0].decode()
+    without = vg.gaf_text(ix, view, 3, reads.seqs, reads.offsets, reads.names)[0].decode()
+    assert "as:i:-30 cs:Z:" in with_tag and with_tag.replace("as:i:-30 cs:Z:", "as:i:-30 ") == without
+    assert o.gaf(oi, reads, 3) == without and o.gaf(oi, reads, 1) == with_tag

@@ -243,6 +243,26 @@ def test_range_checked_pair_class_rebases_its_planes(monkeypatch):
     assert ((o.aln_status == 1) & (o.aln_cells > 150 * 6000)).sum() >= 10      # subgraphs far beyond the a-priori int16 bound
 
 
+@pytest.mark.parametrize("gran", ["VGA_FLAG_BAND_GRAN8", "VGA_FLAG_BAND_GRAN16"])
+def test_band_granularity_switch(synth, gran):
+    """The abPOA-compatibility switch for SIMD-vector band rounding, in every fill kernel family (16x2 short reads, long reads
+    on the shared-memory kernel, HLA graph with merges): CUDA path = oracle at granularity 8 and 16."""
+    vflag, oflag = getattr(vg, gran), getattr(orc, gran.replace("VGA_", ""))
+    ix = vg.Index.build(fixture_path("graphs/17-DRB1-3123-smooth.gfa"), 11)
+    cases = [(ix, vg.simulate_reads(ix, 1500, 150, 0.01, 0.0005, 0.0005, 0.1, 41), {}),
+             (synth, vg.simulate_reads(synth, 1500, 150, 0.01, 0.0005, 0.0005, 0.1, 42), {}),
+             (synth, vg.simulate_reads(synth, 10, 10000, 0.04, 0.03, 0.03, 0.1, 43), {}),
+             (synth, vg.simulate_reads(synth, 80, 1000, 0.03, 0.01, 0.01, 0.1, 44), dict(best_n=3, min_anchors=2))]
+    for index, reads, kw in cases:
+        gp = vg.default_params(flags=vg.VGA_FLAG_KEEP_DEBUG | vflag, **kw)
+        op = orc.default_params(flags=orc.FLAG_KEEP_DEBUG | oflag, **kw)
+        g = vg.map_reads(index, reads, params=gp)
+        o = orc.OracleIndex(index).map_reads(reads, op, n_threads=8)
+        assert_same(g, o, ALN)
+        base = orc.OracleIndex(index).map_reads(reads, orc.default_params(**kw), n_threads=8)
+        assert int(o.aln_cells.sum()) > int(base.aln_cells.sum())          # the band really is wider
+
+
 def test_medium_reads_and_best_n(synth):
     reads = vg.simulate_reads(synth, 300, 1000, 0.03, 0.01, 0.01, 0.0, 9)
     g, o = both(synth, reads, best_n=3, min_anchors=2)

@@ -167,3 +167,45 @@ def test_score_matches_unbanded_dp_and_traceback_rescoring(seed):
     if rb.aln_status[0] == 1:
         assert rb.aln_score[0] <= r.aln_score[0]
         assert rb.aln_cells[0] <= r.aln_cells[0]
+
+
+# ---- abPOA-compatibility switches: constants a later comparison with real abPOA flips
+def _rand_case(rng, n_nodes=12, qlen=60):
+    labels = ["".join(rng.choice(list("ACGT"), size=int(rng.integers(1, 9)))) for _ in range(n_nodes)]
+    edges = [(i, i + 1) for i in range(n_nodes - 1)] + [(i, i + 2) for i in range(0, n_nodes - 2, 3)]
+    edges.sort()
+    q = "".join(rng.choice(list("ACGT"), size=qlen))
+    return labels, edges, q
+
+
+def test_band_granularity_widens_the_band_and_never_lowers_the_score():
+    """ORC_FLAG_BAND_GRAN8 / 16: every row's band is widened to vector boundaries, so the cells of granularity 1 are a subset
+    (cell counts grow, the score cannot drop), and with a band that already spans the read all three agree."""
+    rng = np.random.default_rng(5)
+    grew = 0
+    for _ in range(30):
+        labels, edges, q = _rand_case(rng)
+        r1 = orc.poa_align(labels, edges, q)
+        r8 = orc.poa_align(labels, edges, q, orc.default_params(flags=orc.FLAG_BAND_GRAN8))
+        r16 = orc.poa_align(labels, edges, q, orc.default_params(flags=orc.FLAG_BAND_GRAN16))
+        if r1.aln_status[0] != 1:
+            continue
+        assert r8.aln_status[0] == 1 and r16.aln_status[0] == 1
+        assert r1.aln_cells[0] <= r8.aln_cells[0] <= r16.aln_cells[0]
+        assert r1.aln_score[0] <= r8.aln_score[0] <= r16.aln_score[0]
+        grew += int(r16.aln_cells[0] > r1.aln_cells[0])
+        wide = orc.default_params(wb=1000)
+        w8 = orc.default_params(wb=1000, flags=orc.FLAG_BAND_GRAN8)
+        a, b = orc.poa_align(labels, edges, q, wide), orc.poa_align(labels, edges, q, w8)
+        assert a.aln_score[0] == b.aln_score[0] and np.array_equal(a.aln_runs, b.aln_runs)
+    assert grew > 10
+
+
+def test_int16_sentinel_changes_nothing_while_scores_are_far_from_it():
+    rng = np.random.default_rng(6)
+    for _ in range(20):
+        labels, edges, q = _rand_case(rng)
+        a = orc.poa_align(labels, edges, q)
+        b = orc.poa_align(labels, edges, q, orc.default_params(flags=orc.FLAG_INT16_SCORES))
+        for f in ("aln_status", "aln_score", "aln_runs", "aln_path", "aln_cells"):
+            assert np.array_equal(getattr(a, f), getattr(b, f)), f
