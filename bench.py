@@ -253,6 +253,15 @@ def gpu_record(G, name, wl, args):
         t_bcast = time.perf_counter() - t0
         ix._gpu = gix
     nbytes = ix.image_size()
+    # GPU index build of the same graph (vga_index_build_device; the tests compare its arrays with the host build's)
+    t_build_dev = None
+    if rank == 0 and not args.no_index_build:
+        try:
+            t0 = time.perf_counter()
+            ms_dev = vg.index_build_device(ix)[4]
+            t_build_dev = {"call_s": time.perf_counter() - t0, "device_ms": ms_dev}
+        except vg.VgaError as e:
+            t_build_dev = {"unsupported": str(e)}
 
     # ---- reads: contiguous shard [rank*n/world, (rank+1)*n/world) of ONE seeded read set (one RNG stream per read)
     total = wl["reads"]
@@ -433,7 +442,7 @@ def gpu_record(G, name, wl, args):
            "gpu_launches": int(sum(sumf(acc, "kernel_launches") for acc in dev_steps)),
            "aligned_fraction": total_aligned / total_reads, "stage_ms": stage,
            "roofline": roof_poa if stage["ms_poa"] >= stage["ms_seed"] else roof_seed, "roofline_poa": roof_poa, "roofline_lookup": roof_seed,
-           "setup": {"index_build_or_load_s": t_index, "index_image_bytes": nbytes, "index_broadcast_s": t_bcast,
+           "setup": {"index_build_or_load_s": t_index, "index_image_bytes": nbytes, "index_broadcast_s": t_bcast, "index_build_on_gpu": t_build_dev,
                      "read_simulation_s": float(red[3]), "wall_s_timed_region": t_wall},
            "counts": {k: sumf(last, k) for k in ("n_probes", "n_anchors", "n_chains", "n_alignments", "poa_cells", "lookup_bytes")}}
     if e2e:
@@ -487,6 +496,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-gaf", action="store_true")
+    ap.add_argument("--no-index-build", action="store_true", help="skip the GPU index build measurement of the setup section")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))

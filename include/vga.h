@@ -160,6 +160,23 @@ int vga_index_import_device(const void* dev_blob, uint64_t bytes, vga_index_t** 
 int vga_comm_unique_id(void* id_bytes);
 int vga_index_broadcast(vga_index_t** ix, const void* id_bytes, int rank, int world);
 
+/* GPU index build (reference src/index.rs:109-281): k-mer walks (src/kmer.rs:347-505), stable sort + consecutive dedup
+ * (:298-301) and the position table (:816-928) on the device.  The host passes the linearised graph (seq_fwd, NodeRef, edges —
+ * the first fields of VgaIndexView; src/utils.rs:81-146 stays on the host) and gets the table arrays of VgaIndexView back,
+ * identical to what the reference's build produces (defaults max_furcations = max_degree = 100).  Graphs whose walks explode
+ * (cyclic, out-degree in the tens) or that reach the reference's degree limits return VGA_ERR_UNSUPPORTED: build those on the host. */
+typedef struct {
+    uint64_t seq_len, n_nodes, n_edges;
+    const uint8_t* seq_fwd;
+    const uint64_t* node_ref;   /* 3 * (n_nodes + 1) */
+    const uint64_t* edges;
+} VgaGraphView;
+typedef struct vga_index_build vga_index_build_t;
+int vga_index_build_device(const VgaGraphView* graph, uint32_t k, vga_index_build_t** out);
+/* fills `view` with the graph's pointers and the built table (borrowed from `b`); *ms_device = device time of the build */
+int vga_index_build_view(const vga_index_build_t* b, const VgaGraphView* graph, uint32_t k, VgaIndexView* view, float* ms_device);
+int vga_index_build_free(vga_index_build_t* b);
+
 void vga_default_params(VgaParams* p);
 /* Map one batch: reads as concatenated bytes + n_reads+1 offsets (host memory).  Blocking. */
 int vga_map_batch(vga_index_t* ix, const char* seqs, const uint64_t* seq_off, uint32_t n_reads,

@@ -64,7 +64,8 @@ ALN_PLACEHOLDER, ALN_OK, ALN_EMPTY, ALN_TRACE_ERR, ALN_BAND_ERR, ALN_UNSUPPORTED
 GPU_SYMBOLS = ["vga_init", "vga_device_count", "vga_index_upload", "vga_index_free", "vga_index_image_size",
                "vga_index_image_copy_to_device", "vga_index_import_device", "vga_default_params", "vga_map_batch",
                "vga_map_batch_device", "vga_results_view", "vga_results_stats", "vga_results_free",
-               "vga_last_error", "vga_measure_int32_peak", "vga_comm_unique_id", "vga_index_broadcast"]
+               "vga_last_error", "vga_measure_int32_peak", "vga_comm_unique_id", "vga_index_broadcast", "vga_index_build_device",
+               "vga_index_build_view", "vga_index_build_free"]
 
 HASH_FN = C.CFUNCTYPE(C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p)     # vgah_hash_fn: (kmer bytes, k, user) -> key hash
 
@@ -489,6 +490,32 @@ def map_reads(index, inputs, bandwidth=50, max_gap=1000, chain_min_n_anchors=3, 
             gaf_name = out_prefix if out_prefix.endswith(".gaf") else out_prefix + "-alignments.gaf"
             with open(gaf_name, "w") as f:
                 f.write(res.gaf(1))
+    return res
+
+
+class VgaGraphView(C.Structure):
+    _fields_ = [("seq_len", C.c_uint64), ("n_nodes", C.c_uint64), ("n_edges", C.c_uint64), ("seq_fwd", C.c_void_p),
+                ("node_ref", u64p), ("edges", u64p)]
+
+
+def index_build_device(index, k=None):
+    """vga_index_build_device: the k-mer table of `Index::build` on the GPU from the linearised graph of `index` (seq_fwd, NodeRef,
+    edges).  Returns (key_kmer2bit, key_offset, tab_start, tab_end, device milliseconds); raises VgaError(-4) for graphs the
+    device build does not admit (cyclic / high-degree: build those on the host)."""
+    L = gpu_lib()
+    v = index.view
+    g = VgaGraphView(v.seq_len, v.n_nodes, v.n_edges, C.cast(v.seq_fwd, C.c_void_p), v.node_ref, v.edges)
+    out = C.c_void_p()
+    L.vga_index_build_device.argtypes = [C.POINTER(VgaGraphView), C.c_uint32, C.POINTER(C.c_void_p)]
+    L.vga_index_build_view.argtypes = [C.c_void_p, C.POINTER(VgaGraphView), C.c_uint32, C.POINTER(VgaIndexView), C.POINTER(C.c_float)]
+    L.vga_index_build_free.argtypes = [C.c_void_p]
+    kk = int(k or v.k)
+    _check(L.vga_index_build_device(C.byref(g), kk, C.byref(out)), "vga_index_build_device")
+    bv, ms = VgaIndexView(), C.c_float()
+    _check(L.vga_index_build_view(out, C.byref(g), kk, C.byref(bv), C.byref(ms)), "vga_index_build_view")
+    res = (_arr(bv.key_kmer2bit, bv.n_keys, np.uint64), _arr(bv.key_offset, bv.n_keys, np.uint64),
+           _arr(bv.tab_start, bv.n_table, np.uint64), _arr(bv.tab_end, bv.n_table, np.uint64), ms.value)
+    L.vga_index_build_free(out)
     return res
 
 

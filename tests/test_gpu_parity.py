@@ -429,3 +429,27 @@ def test_n_gpus_through_the_c_abi_equal_one_gpu(synth):
         assert np.array_equal(np.concatenate([getattr(p, f) for p in parts]), getattr(one, f)), f
     for which in (0, 1):
         assert "".join(p.gaf(which) for p in parts) == one.gaf(which)
+
+
+@pytest.mark.parametrize("graph,k", [("test.gfa", 3), ("test.gfa", 4), ("test.gfa", 11), ("graphs/19-MICB-4227-smooth.gfa", 11),
+                                     ("graphs/2-DRB1-3123.gfa", 11), ("graphs/17-DRB1-3123-smooth.gfa", 11), ("synth", 15)])
+def test_gpu_index_build_equals_the_host_build(graph, k, synth):
+    """GPU index build (k-mer walks, stable sort + consecutive dedup, position table) against host/index_build.cpp — itself pinned
+    on the reference's index vectors (tests/test_oracle_golden.py): every key, offset and table entry incl. the delimiters, on
+    graphs with N runs (2-DRB1-3123), reverse links (17-DRB1-3123-smooth) and bubbles."""
+    ix = synth if graph == "synth" else vg.Index.build(fixture_path(graph), k)
+    keys, koff, ts, te, ms = vg.index_build_device(ix, k)
+    n, nt = ix.view.n_keys, ix.view.n_table
+    assert len(keys) == n and len(ts) == nt
+    assert np.array_equal(keys, np.ctypeslib.as_array(ix.view.key_kmer2bit, shape=(n,)))
+    hs, he, ho = ix.table()
+    assert np.array_equal(koff, ho) and np.array_equal(ts, hs) and np.array_equal(te, he)
+    assert ms > 0
+
+
+def test_gpu_index_build_refuses_walk_explosions():
+    """5-B3106 (cyclic, microsatellite loops with out-degree 17): 17^10 walks from one start — the device build returns
+    VGA_ERR_UNSUPPORTED instead of running for minutes; such graphs are built on the host."""
+    ix = vg.Index.build(fixture_path("graphs/5-B3106.gfa"), 11)
+    with pytest.raises(vg.VgaError):
+        vg.index_build_device(ix, 11)
