@@ -28,7 +28,7 @@ $(PKG)/libvgaligner_gpu.so: $(GPU_OBJS)
 
 # ---- host library (index build, reads, GAF writer) ----
 host: $(PKG)/libvga_host.so
-HOST_SRC  := $(HOST)/index_build.cpp $(HOST)/host_api.cpp $(HOST)/gaf_writer.cpp $(HOST)/key_derive.cpp
+HOST_SRC  := $(HOST)/index_build.cpp $(HOST)/host_api.cpp $(HOST)/gaf_writer.cpp $(HOST)/key_derive.cpp $(HOST)/idx_file.cpp
 $(PKG)/libvga_host.so: $(HOST_SRC) $(HOST)/flat_index.h $(HOST)/vga_host.h include/vga.h
 	$(CXX) $(CXXFLAGS) -O3 -pthread -shared -o $@ $(HOST_SRC)
 

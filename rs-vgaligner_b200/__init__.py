@@ -92,6 +92,7 @@ def host_lib():
         L.vgah_index_build_text.argtypes = [C.c_char_p, C.c_uint32, C.c_uint64, C.c_uint64]
         L.vgah_index_load.argtypes = [C.c_char_p]
         L.vgah_index_save.argtypes = [C.c_void_p, C.c_char_p]
+        L.vgah_index_save_idx.argtypes = [C.c_void_p, C.c_char_p]
         L.vgah_index_free.argtypes = [C.c_void_p]
         L.vgah_index_view.argtypes = [C.c_void_p, C.POINTER(VgaIndexView)]
         L.vgah_index_keys.argtypes = [C.c_void_p, u64p]
@@ -198,6 +199,11 @@ class Index:
     def load_from_file(cls, path):
         return cls(host_lib().vgah_index_load(os.fsencode(path)))
 
+    def store_as_idx(self, path):
+        """the reference's own index file (bincode of `Index`, src/index.rs:284-305; layout in host/idx_file.cpp)"""
+        if host_lib().vgah_index_save_idx(self._h, os.fsencode(path)) != 0:
+            raise VgaError(host_lib().vgah_last_error().decode())
+
     def store_in_file(self, path):
         if host_lib().vgah_index_save(self._h, os.fsencode(path)) != 0:
             raise VgaError(host_lib().vgah_last_error().decode())
@@ -249,11 +255,12 @@ class Index:
         v.key_kmer2bit = None                  # not available to the walk
         if n_keys is not None:
             v.n_keys = min(int(n_keys), self.view.n_keys)
-        kh = np.ascontiguousarray(key_hash, dtype=np.uint64)
+        kh = np.ascontiguousarray(key_hash if key_hash is not None else np.zeros(1), dtype=np.uint64)
         out = np.zeros(v.n_keys, dtype=np.uint64)
         amb, hop = C.c_uint64(), C.c_uint64()
-        cb = HASH_FN(lambda p, k, _u: int(hash_fn(C.string_at(p, k))) & 0xFFFFFFFFFFFFFFFF)
-        rc = host_lib().vgah_derive_keys(C.byref(v), kh.ctypes.data_as(u64p), cb, None, out.ctypes.data_as(u64p), C.byref(amb), C.byref(hop))
+        cb = HASH_FN(lambda p, k, _u: int(hash_fn(C.string_at(p, k))) & 0xFFFFFFFFFFFFFFFF) if hash_fn is not None else HASH_FN(0)
+        rc = host_lib().vgah_derive_keys(C.byref(v), kh.ctypes.data_as(u64p) if hash_fn is not None else None, cb, None,
+                                         out.ctypes.data_as(u64p), C.byref(amb), C.byref(hop))
         if rc != 0:
             raise VgaError("vgah_derive_keys failed (%d)" % rc)
         return out, amb.value, hop.value

@@ -70,6 +70,10 @@ FlatIndex build_index(const HashGraph& g, uint32_t k, uint64_t max_furcations = 
 void save_index(const FlatIndex& ix, const std::string& path);
 FlatIndex load_index(const std::string& path);
 
+// The reference's own index file (bincode of `Index`, reference src/index.rs:284-305): idx_file.cpp
+FlatIndex load_idx(const std::string& path);
+void save_idx(const FlatIndex& ix, const std::string& path, const std::vector<uint64_t>& key_hash);
+
 std::string reverse_complement(const std::string& s);  // reference src/dna.rs:5-40
 // 2-bit packing; returns false when the k-mer has a byte outside uppercase ACGT.
 bool pack_kmer(const char* s, uint32_t k, uint64_t* out);

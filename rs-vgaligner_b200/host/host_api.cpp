@@ -89,8 +89,31 @@ vgah_index_t* vgah_index_build_text(const char* gfa_text, uint32_t k, uint64_t m
     } catch (std::exception& e) { set_err(e.what()); return nullptr; }
 }
 
+static bool ends_with(const std::string& s, const char* suf) {
+    const size_t n = strlen(suf);
+    return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+
+// `.idx` = the reference's bincode file (Index::load_from_file, src/index.rs:296-305); anything else = this repository's container
 vgah_index_t* vgah_index_load(const char* path) {
-    try { return wrap(load_index(path)); } catch (std::exception& e) { set_err(e.what()); return nullptr; }
+    try {
+        const std::string p(path);
+        return wrap(ends_with(p, ".idx") ? load_idx(p) : load_index(p));
+    } catch (std::exception& e) { set_err(e.what()); return nullptr; }
+}
+
+int vgah_index_save_idx(const vgah_index_t* h, const char* path) {
+    try {
+        // stand-in for the ahash keys of a real file: FNV-1a of the k-mer strings (opaque to every reader)
+        std::vector<uint64_t> hs(h->ix.key_kmer.size());
+        for (size_t i = 0; i < hs.size(); i++) {
+            uint64_t x = 0xcbf29ce484222325ull;
+            for (char c : h->ix.key_kmer[i]) x = (x ^ (uint8_t)c) * 0x100000001b3ull;
+            hs[i] = x;
+        }
+        save_idx(h->ix, path, hs);
+        return 0;
+    } catch (std::exception& e) { set_err(e.what()); return -1; }
 }
 
 int vgah_index_save(const vgah_index_t* h, const char* path) {

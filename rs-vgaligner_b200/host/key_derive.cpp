@@ -9,7 +9,11 @@
 // (start, end) alone does not identify the k-mer — the two alleles of a SNP bubble give two k-mers with the same first
 // and last position — so the candidates are told apart by the key's own hash: the caller passes its hash function
 // (the Rust host: `generate_hash`; the tests: any 64-bit string hash, applied to the same strings when the keys were made).
+// A host without the hash function (the C++ `.idx` reader: ahash is not reproducible outside Rust) passes hash = NULL and
+// gets the same keys from the ORDER of the table instead (the rank rule at the end of vgah_derive_keys).
+#include <algorithm>
 #include <cstring>
+#include <map>
 #include <set>
 #include <string>
 #include <vector>
@@ -97,13 +101,15 @@ struct Walker {
 
 extern "C" int vgah_derive_keys(const VgaIndexView* view, const uint64_t* key_hash, vgah_hash_fn hash, void* user,
                                 uint64_t* key_kmer2bit_out, uint64_t* n_ambiguous, uint64_t* n_hopping) {
-    if (!view || !key_hash || !hash || !key_kmer2bit_out || !view->seq_fwd || !view->node_ref || !view->key_offset ||
+    if (!view || (hash && !key_hash) || !key_kmer2bit_out || !view->seq_fwd || !view->node_ref || !view->key_offset ||
         !view->tab_start || !view->tab_end)
         return VGA_ERR_INVALID;
     const Walker W(*view);
     const uint32_t k = view->k;
     uint64_t amb = 0, hop = 0;
     std::set<std::string> found;
+    std::vector<uint64_t> pending;                                            // keys left to the rank rule (no hash function given)
+    std::map<std::pair<uint64_t, uint64_t>, std::vector<std::string>> cand;    // their candidate k-mers by first position pair
     for (uint64_t i = 0; i < view->n_keys; i++) {
         const uint64_t off = view->key_offset[i];
         if (off >= view->n_table) return VGA_ERR_INVALID;
@@ -120,13 +126,45 @@ extern "C" int vgah_derive_keys(const VgaIndexView* view, const uint64_t* key_ha
         if (!rev && !(e & vga::POS_REV_BIT) && (e & ~vga::POS_REV_BIT) - p != k) hop++;
         const std::string* pick = nullptr;
         const size_t distinct = found.size();
-        for (const std::string& c : found)
-            if (hash(c.data(), k, user) == key_hash[i]) { pick = &c; break; }
         if (distinct > 1) amb++;
+        if (distinct == 1) pick = &*found.begin();
+        else if (hash) {
+            for (const std::string& c : found)
+                if (hash(c.data(), k, user) == key_hash[i]) { pick = &c; break; }
+        } else if (distinct > 1) {
+            // no hash function on this host: resolved below by rank (keys are stored in sorted k-mer order)
+            pending.push_back(i);
+            cand[{s, e}] = std::vector<std::string>(found.begin(), found.end());
+            continue;
+        }
         if (!pick) return VGA_ERR_INVALID;                            // no walk reproduces the key: not this index's table
         uint64_t packed = 0;
         if (!vga::pack_kmer(pick->data(), k, &packed)) return VGA_ERR_UNSUPPORTED;   // index k-mers are ACGT only (N handles are dropped)
         key_kmer2bit_out[i] = packed;
+    }
+    if (!pending.empty()) {
+        // Rank rule.  Every k-mer that walks from `start` to `end` is a key of the index and has (start, end) in its run, and
+        // nothing else has: the keys whose run holds a position pair P, in index order, are the candidate k-mers of P in sorted
+        // order (the table is built from the k-mers sorted by their bytes, reference src/kmer.rs:298, 816-928).
+        std::map<std::pair<uint64_t, uint64_t>, std::vector<uint64_t>> holders;
+        for (auto& c : cand) holders[c.first];
+        for (uint64_t i = 0; i < view->n_keys; i++) {
+            for (uint64_t x = view->key_offset[i]; x < view->n_table && view->tab_start[x] != vga::POS_DELIM; x++) {
+                auto it = holders.find({view->tab_start[x], view->tab_end[x]});
+                if (it != holders.end() && (it->second.empty() || it->second.back() != i)) it->second.push_back(i);
+            }
+        }
+        for (uint64_t i : pending) {
+            const uint64_t off = view->key_offset[i];
+            const std::pair<uint64_t, uint64_t> P{view->tab_start[off], view->tab_end[off]};
+            const std::vector<uint64_t>& hs = holders[P];
+            const std::vector<std::string>& cs = cand[P];
+            if (hs.size() != cs.size()) return VGA_ERR_INVALID;      // the table does not come from this graph's k-mer walks
+            const size_t rank = std::lower_bound(hs.begin(), hs.end(), i) - hs.begin();
+            uint64_t packed = 0;
+            if (rank >= cs.size() || !vga::pack_kmer(cs[rank].data(), k, &packed)) return VGA_ERR_INVALID;
+            key_kmer2bit_out[i] = packed;
+        }
     }
     if (n_ambiguous) *n_ambiguous = amb;
     if (n_hopping) *n_hopping = hop;

@@ -18,7 +18,8 @@ const char* vgah_last_error(void);
 /* `vgaligner index` (reference src/subcommands/index_main.rs:11-87, src/index.rs:109-281) */
 vgah_index_t* vgah_index_build_file(const char* gfa_path, uint32_t k, uint64_t max_furcations, uint64_t max_degree);
 vgah_index_t* vgah_index_build_text(const char* gfa_text, uint32_t k, uint64_t max_furcations, uint64_t max_degree);
-vgah_index_t* vgah_index_load(const char* path);
+vgah_index_t* vgah_index_load(const char* path);   /* "*.idx": the reference's bincode file (idx_file.cpp); otherwise the .vgidx container */
+int vgah_index_save_idx(const vgah_index_t*, const char* path);   /* writes a `.idx` (bincode layout of `Index`, see idx_file.cpp) */
 int vgah_index_save(const vgah_index_t*, const char* path);
 void vgah_index_free(vgah_index_t*);
 int vgah_index_view(const vgah_index_t*, VgaIndexView* view);       /* borrowed pointers into the index */
@@ -28,7 +29,8 @@ const char* vgah_index_seq_rev(const vgah_index_t*);                /* Index.seq
 /* Key derivation (`Index::walk_kmer`): the 2-bit packed k-mer of every key, recovered from what a `.idx`
  * holds — the key's first table position (key_offset, tab_start/tab_end), seq_fwd, node_ref, edges — plus the key's own hash
  * to tell apart k-mers that share their first and last position (the alleles of a bubble).  view->key_kmer2bit is not read.
- * hash: the function the keys were made with (Rust host: generate_hash, reference src/kmer.rs:931-934).
+ * hash: the function the keys were made with (Rust host: generate_hash, reference src/kmer.rs:931-934); NULL: no hash function on this
+ * host — ambiguous keys are told apart by their rank among the keys that share the position pair (the table is in sorted k-mer order).
  * n_ambiguous: keys whose (start, end) admitted more than one k-mer; n_hopping: forward keys with end - start != k. */
 typedef uint64_t (*vgah_hash_fn)(const char* kmer, uint32_t k, void* user);
 int vgah_derive_keys(const VgaIndexView* view, const uint64_t* key_hash, vgah_hash_fn hash, void* user,

@@ -151,6 +151,10 @@ def test_keys_rebuilt_from_table_positions_only(graph, k, n_keys):
     assert np.array_equal(got, want)
     if k >= 4 and graph != "test.gfa":
         assert n_hop > 0 and n_amb > 0          # both situations occur on the HLA graphs
+    # a host without the hash function (the C++ .idx reader): the same keys from the order of the table alone
+    if n_keys is None:
+        got2, _, _ = ix.derive_keys(None, None, n)
+        assert np.array_equal(got2, want)
 
 
 def test_multinode_kmer_positions_are_walkable():
@@ -164,3 +168,52 @@ def test_multinode_kmer_positions_are_walkable():
     got, n_amb, n_hop = ix.derive_keys(np.array([_fnv(x) for x in ks], dtype=np.uint64), _fnv)
     assert np.array_equal(got, np.ctypeslib.as_array(ix.view.key_kmer2bit, shape=(n,)))
     assert n_hop >= 1
+
+
+# ---- `.idx` reader (reference src/index.rs:284-305, src/serialization.rs:34-54; layout in host/idx_file.cpp)
+@pytest.mark.parametrize("graph,k", [("test.gfa", 4), ("test.gfa", 11), ("graphs/19-MICB-4227-smooth.gfa", 11)])
+def test_idx_file_round_trip(tmp_path, graph, k):
+    """An index written in the bincode layout of the reference's `Index` and read back: every array the C ABI borrows is
+    identical — including the 2-bit keys, which a `.idx` does not store (its keys are ahash values): the reader derives them
+    from the table positions and the table's order."""
+    ix = vg.Index.build(fixture_path(graph), k)
+    path = str(tmp_path / "graph.idx")
+    ix.store_as_idx(path)
+    back = vg.Index.load_from_file(path)
+    a, b = ix.view, back.view
+    assert (a.k, a.seq_len, a.n_nodes, a.n_edges, a.n_keys, a.n_table) == (b.k, b.seq_len, b.n_nodes, b.n_edges, b.n_keys, b.n_table)
+    assert ix.seq_fwd == back.seq_fwd and ix.seq_rev == back.seq_rev
+    assert np.array_equal(ix.node_ref, back.node_ref) and np.array_equal(ix.edges, back.edges)
+    for x, y in zip(ix.table(), back.table()):
+        assert np.array_equal(x, y)
+    n = a.n_keys
+    assert np.array_equal(np.ctypeslib.as_array(a.key_kmer2bit, shape=(n,)), np.ctypeslib.as_array(b.key_kmer2bit, shape=(n,)))
+    assert ix.keys_bytes() == back.keys_bytes()
+
+
+def test_idx_reader_does_not_depend_on_the_third_party_layouts(tmp_path):
+    """The inner layouts of seq_bv (bv crate) and bhpf (boomphf) are recalled, not verified.  The reader must find its way
+    without them: a file whose seq_bv and bhpf fields are replaced by garbage of another size still loads identically, and a
+    truncated or sampled file is refused with an error."""
+    ix = vg.Index.build(fixture_path("test.gfa"), 4)
+    path = str(tmp_path / "a.idx")
+    ix.store_as_idx(path)
+    raw = open(path, "rb").read()
+    L = ix.view.seq_len
+    bv_at = 16 + 8 + L + 8 + L
+    nb = (L + 1 + 63) // 64
+    bv_len = 1 + 8 + 8 * nb + 8
+    n_keys = ix.view.n_keys
+    graph_len = 8 + 8 + 8 * ix.view.n_edges + 8 + 8 + 24 * (ix.view.n_nodes + 1) + 16
+    bh_at = bv_at + bv_len + graph_len
+    bh_len = 16 + 8 + 8 * n_keys
+    mangled = raw[:bv_at] + b"\\x07" * 37 + raw[bv_at + bv_len:bh_at] + b"\\xee" * 1001 + raw[bh_at + bh_len:]
+    p2 = str(tmp_path / "b.idx")
+    open(p2, "wb").write(mangled)
+    back = vg.Index.load_from_file(p2)
+    for x, y in zip(ix.table(), back.table()):
+        assert np.array_equal(x, y)
+    assert ix.keys_bytes() == back.keys_bytes() and np.array_equal(ix.edges, back.edges)
+    open(p2, "wb").write(raw[:-40])
+    with pytest.raises(vg.VgaError):
+        vg.Index.load_from_file(p2)
