@@ -66,6 +66,13 @@ typedef struct {
 #define VGA_FLAG_CHAIN_SCORES 4u /* also return ca_id / ca_score (not needed by the GAF writers) */
 /* POA band granularity: the band of every DP row is widened to multiples of 8 / 16 columns, as upstream abPOA's SIMD vectors do
  * (8 = int16 lanes of SSE4.1 ... 16 = AVX2); default 1.  A compatibility switch for comparisons with a real abPOA build. */
+/* Anchors of every orientation (`anchors_for_query(.., only_forward = false)`, reference src/chain.rs:154-156): reverse-strand
+ * positions become anchors, are sorted Reverse-first (src/chain.rs:386-389) and chain only with anchors of the same orientation
+ * (src/chain.rs:277-287).  Needs an index uploaded with VGA_INDEX_ALL_ORIENTATIONS; ca_tb / ca_te carry the orientation in
+ * bit 31.  Chains with a reverse-strand anchor are not aligned (aln_status = VGA_ALN_UNSUPPORTED): the reference's Reverse / Both
+ * ranges subtract forward node starts from reverse-strand positions (src/align.rs:536-547 with src/index.rs:461-480), which is
+ * not a defined computation. */
+#define VGA_FLAG_ALL_ORIENTATIONS 0x1000u
 #define VGA_FLAG_BAND_GRAN8 0x100u
 #define VGA_FLAG_BAND_GRAN16 0x200u
 
@@ -146,6 +153,10 @@ int vga_device_count(void);
  * rank 0 uploads, copies the image into a byte tensor (vga_index_image_copy_to_device), broadcasts,
  * and every other rank adopts its copy with vga_index_import_device. */
 int vga_index_upload(const VgaIndexView* view, vga_index_t** out);
+/* flags: VGA_INDEX_ALL_ORIENTATIONS keeps every table position (orientation in bit 31 of the device words) instead of the
+ * forward/forward ones `map_reads` uses (src/map.rs:62); such an index serves vga_map_batch only with VGA_FLAG_ALL_ORIENTATIONS. */
+#define VGA_INDEX_ALL_ORIENTATIONS 1u
+int vga_index_upload_ex(const VgaIndexView* view, uint32_t flags, vga_index_t** out);
 int vga_index_free(vga_index_t* ix);
 int vga_index_image_size(const vga_index_t* ix, uint64_t* bytes);
 int vga_index_image_copy_to_device(const vga_index_t* ix, void* dev_dst);

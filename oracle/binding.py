@@ -19,7 +19,7 @@ class OrcParams(C.Structure):
 
 
 FLAG_NO_ALIGN, FLAG_KEEP_DEBUG, FLAG_LITERAL_EXTEND = 1, 2, 4
-FLAG_BAND_GRAN8, FLAG_BAND_GRAN16, FLAG_INT16_SCORES, FLAG_NO_CS_PREFIX = 0x100, 0x200, 0x400, 0x800
+FLAG_BAND_GRAN8, FLAG_BAND_GRAN16, FLAG_INT16_SCORES, FLAG_NO_CS_PREFIX, FLAG_ALL_ORIENTATIONS = 0x100, 0x200, 0x400, 0x800, 0x1000
 REV_BIT = 1 << 63
 _lib = None
 

@@ -587,7 +587,7 @@ struct ReadResult {
 
 void map_one(const Index& ix, const char* read, u64 len, const orc_params_t& P, ReadResult& rr) {
     std::vector<Anchor> anchors;
-    anchors_for_query(ix, read, len, true, anchors);                        // src/map.rs:62
+    anchors_for_query(ix, read, len, !(P.flags & ORC_FLAG_ALL_ORIENTATIONS), anchors);   // src/map.rs:62 passes only_forward = true
     rr.n_anchors = (u32)anchors.size();
     const bool dbg = P.flags & ORC_FLAG_KEEP_DEBUG;
     if (dbg) rr.anchors_emitted = anchors;
@@ -661,8 +661,8 @@ struct orc_results {
         for (const Chain& c : rr.chains) {
             if (c.placeholder) continue;     // a placeholder is represented by zero chains
             for (const Anchor& a : c.anchors) {
-                ca_id.push_back((u32)a.id); ca_qb.push_back((u32)a.qb); ca_tb.push_back((u32)a.tb);
-                ca_te.push_back((u32)a.te); ca_score.push_back(a.f);
+                ca_id.push_back((u32)a.id); ca_qb.push_back((u32)a.qb); ca_tb.push_back((u32)a.tb | (a.tb_rev ? 0x80000000u : 0u));
+                ca_te.push_back((u32)a.te | (a.te_rev ? 0x80000000u : 0u)); ca_score.push_back(a.f);
             }
             chain_anchor_off.push_back(ca_id.size());
         }
@@ -677,7 +677,8 @@ struct orc_results {
         aln_score.push_back(rr.aln.score); aln_cells.push_back(rr.aln.cells);
         if (dbg) {
             for (const Anchor& a : rr.anchors_emitted) {
-                dbg_qb.push_back((u32)a.qb); dbg_tb.push_back((u32)a.tb); dbg_te.push_back((u32)a.te);
+                dbg_qb.push_back((u32)a.qb); dbg_tb.push_back((u32)a.tb | (a.tb_rev ? 0x80000000u : 0u));
+                dbg_te.push_back((u32)a.te | (a.te_rev ? 0x80000000u : 0u));
             }
             dbg_sorted.insert(dbg_sorted.end(), rr.cdbg.sorted.begin(), rr.cdbg.sorted.end());
             dbg_f.insert(dbg_f.end(), rr.cdbg.f.begin(), rr.cdbg.f.end());
@@ -855,10 +856,13 @@ const char* orc_results_gaf(orc_results_t* R, const orc_index_t* o, const char* 
                 u64 b = R->chain_anchor_off[c], e = R->chain_anchor_off[c + 1];
                 std::string path;
                 for (u64 a = b; a < e; a++) {        // AnchorPosOnGraph::new (src/chain.rs:89-127)
-                    u64 tb = R->ca_tb[a], tei = (u64)R->ca_te[a] - 1;
-                    u64 h1 = ix.handle_from_seqpos(false, tb), h2 = ix.handle_from_seqpos(false, tei);
-                    path += "(>" + std::to_string(h1 >> 1) + ":" + std::to_string(tb - ix.select(h1 >> 1)) + ",>" +
-                            std::to_string(h2 >> 1) + ":" + std::to_string(tei - ix.select(h2 >> 1)) + "),";
+                    // bit 31 = Reverse.  AnchorPosOnGraph::new subtracts the FORWARD start of the node (get_bv_select) also from a
+                    // reverse-strand position (src/chain.rs:96-121): u64 arithmetic, wrapping as a release build does
+                    const bool r1 = R->ca_tb[a] >> 31, r2 = R->ca_te[a] >> 31;
+                    u64 tb = R->ca_tb[a] & 0x7fffffffu, tei = (u64)(R->ca_te[a] & 0x7fffffffu) - 1;
+                    u64 h1 = ix.handle_from_seqpos(r1, tb), h2 = ix.handle_from_seqpos(r2, tei);
+                    path += std::string("(") + (r1 ? "<" : ">") + std::to_string(h1 >> 1) + ":" + std::to_string(tb - ix.select(h1 >> 1)) + "," +
+                            (r2 ? "<" : ">") + std::to_string(h2 >> 1) + ":" + std::to_string(tei - ix.select(h2 >> 1)) + "),";
                 }
                 out += nm[r] + "\t" + std::to_string(qlen) + "\t" + std::to_string(R->ca_qb[b]) + "\t" +
                        std::to_string(R->ca_qb[e - 1] + ix.k) + "\t+\t" + path + "\t0\t0\t0\t0\t0\t0\t" +

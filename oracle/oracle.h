@@ -41,6 +41,8 @@ typedef struct {
 #define ORC_FLAG_LITERAL_EXTEND 4u  /* extend_range_chain_2 exactly as written (no visited set) */
 /* abPOA-compatibility switches of the POA definition.  Real abPOA could not be run here, so each
  * choice it might make differently is a switch that flips a constant, not a kernel: */
+#define ORC_FLAG_ALL_ORIENTATIONS 0x1000u /* anchors_for_query(.., only_forward = false), src/chain.rs:154-156; positions carry the
+                                            orientation in bit 31 of ca_tb / ca_te; chains with a reverse anchor are not aligned */
 #define ORC_FLAG_BAND_GRAN8 0x100u  /* band of every row widened to multiples of 8 columns (SIMD vector of 8 int16 lanes) ... */
 #define ORC_FLAG_BAND_GRAN16 0x200u /* ... or of 16 columns (AVX2); same bits as VGA_FLAG_BAND_GRAN8 / 16, the CUDA path follows */
 #define ORC_FLAG_INT16_SCORES 0x400u /* -inf is INT16_MIN + the largest single-step penalty (upstream's int16 score width) instead of

@@ -58,14 +58,15 @@ class VgaStats(C.Structure):
 
 
 VGA_FLAG_NO_ALIGN, VGA_FLAG_KEEP_DEBUG, VGA_FLAG_CHAIN_SCORES = 1, 2, 4
-VGA_FLAG_BAND_GRAN8, VGA_FLAG_BAND_GRAN16 = 0x100, 0x200
+VGA_FLAG_BAND_GRAN8, VGA_FLAG_BAND_GRAN16, VGA_FLAG_ALL_ORIENTATIONS = 0x100, 0x200, 0x1000
+VGA_INDEX_ALL_ORIENTATIONS = 1
 ALN_PLACEHOLDER, ALN_OK, ALN_EMPTY, ALN_TRACE_ERR, ALN_BAND_ERR, ALN_UNSUPPORTED, ALN_TOO_WIDE = range(7)
 
 GPU_SYMBOLS = ["vga_init", "vga_device_count", "vga_index_upload", "vga_index_free", "vga_index_image_size",
                "vga_index_image_copy_to_device", "vga_index_import_device", "vga_default_params", "vga_map_batch",
                "vga_map_batch_device", "vga_results_view", "vga_results_stats", "vga_results_free",
                "vga_last_error", "vga_measure_int32_peak", "vga_comm_unique_id", "vga_index_broadcast", "vga_index_build_device",
-               "vga_index_build_view", "vga_index_build_free"]
+               "vga_index_build_view", "vga_index_build_free", "vga_index_upload_ex"]
 
 HASH_FN = C.CFUNCTYPE(C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p)     # vgah_hash_fn: (kmer bytes, k, user) -> key hash
 
@@ -140,6 +141,7 @@ def gpu_lib():
         L.vga_last_error.restype = C.c_char_p
         L.vga_init.argtypes = [C.c_int]
         L.vga_index_upload.argtypes = [C.POINTER(VgaIndexView), C.POINTER(C.c_void_p)]
+        L.vga_index_upload_ex.argtypes = [C.POINTER(VgaIndexView), C.c_uint32, C.POINTER(C.c_void_p)]
         L.vga_index_free.argtypes = [C.c_void_p]
         L.vga_index_image_size.argtypes = [C.c_void_p, u64p]
         L.vga_index_image_copy_to_device.argtypes = [C.c_void_p, C.c_void_p]
@@ -273,7 +275,7 @@ class Index:
             if device is not None:
                 _check(L.vga_init(int(device)), "vga_init")
             out = C.c_void_p()
-            _check(L.vga_index_upload(C.byref(self.view), C.byref(out)), "vga_index_upload")
+            _check(L.vga_index_upload_ex(C.byref(self.view), int(getattr(self, "upload_flags", 0)), C.byref(out)), "vga_index_upload_ex")
             self._gpu = out
         return self._gpu
 

@@ -60,7 +60,8 @@ struct IndexHeader {
     u64 n_buckets;
     u64 off_pos2;       // uint2[n_pos2]   {start, end} of fwd/fwd entries, table order; a run with more than 30 entries is
     u64 n_pos2;         //                 preceded by a header element {count, 0}
-    u64 pad[4];
+    u64 all_orient;     // 1: the table holds positions of every orientation (bit 31 of pos_tb / pos_te = Reverse)
+    u64 pad[3];
 };
 static const u64 INDEX_MAGIC = 0x3358444947414756ull;  // "VGAGIDX3" (slot keys in bit-plane form; compact bucket table)
 

@@ -28,7 +28,8 @@ static const u32 FULLM = 0xffffffffu;
 // score of an anchor is turned back into the f64 the reference stores (one division per anchor).
 __device__ __forceinline__ i32 score_pair(u32 qb_a, u32 tb_a, u32 te_a, double f_a, u32 qb_b, u32 tb_b, u32 te_b,
                                           u32 k, u32 max_gap, const double* __restrict__ gapcost) {
-    if (qb_a >= qb_b || te_a >= te_b) return INT_MIN;                 // :277-311
+    // all four positions must share their orientation (bit 31), :280-283; equal orientations compare like plain positions
+    if (qb_a >= qb_b || te_a >= te_b || (((tb_a ^ te_a) | (tb_a ^ tb_b) | (te_a ^ te_b)) >> 31)) return INT_MIN;   // :277-311
     const u32 ql = qb_b - qb_a;                                       // :313 (both terms are equal)
     const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;          // :324-327
     const u32 ted = te_b - te_a;                                      // :328-331
@@ -48,7 +49,7 @@ __device__ __forceinline__ i32 score_pair(u32 qb_a, u32 tb_a, u32 te_a, double f
 // is replaced by INT_MIN at the end, so two evaluations can be interleaved by the scheduler.
 __device__ __forceinline__ i32 score_pair_nb(bool live, u32 qb_a, u32 tb_a, u32 te_a, double f_a, u32 qb_b, u32 tb_b, u32 te_b,
                                              u32 k, u32 max_gap, const double* __restrict__ gapcost) {
-    live = live && qb_a < qb_b && te_a < te_b;
+    live = live && qb_a < qb_b && te_a < te_b && !(((tb_a ^ te_a) | (tb_a ^ tb_b) | (te_a ^ te_b)) >> 31);
     const u32 ql = qb_b - qb_a;
     const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
     const u32 ted = te_b - te_a;
@@ -69,7 +70,7 @@ __device__ __forceinline__ i32 score_pair_nb(bool live, u32 qb_a, u32 tb_a, u32 
 // the f64 rounding error of a rounding boundary, which the host checks when it builds K (vga_api.cu upload_gapcost).
 __device__ __forceinline__ i32 score_pair_int(bool live, u32 qb_a, u32 tb_a, u32 te_a, i32 r_a, u32 qb_b, u32 tb_b, u32 te_b,
                                               u32 k, u32 max_gap, const i32* __restrict__ sK) {
-    live = live && qb_a < qb_b && te_a < te_b;
+    live = live && qb_a < qb_b && te_a < te_b && !(((tb_a ^ te_a) | (tb_a ^ tb_b) | (te_a ^ te_b)) >> 31);
     const u32 ql = qb_b - qb_a;
     const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
     const u32 ted = te_b - te_a;
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
             u32 np2 = 32;
             while (np2 < n) np2 <<= 1;
             for (u32 i = lane; i < np2; i += 32)
-                keys[i] = i < n ? (((unsigned long long)b.a_te[base + i] << 32) | i) : ~0ull;
+                keys[i] = i < n ? (((unsigned long long)(b.a_te[base + i] ^ 0x80000000u) << 32) | i) : ~0ull;     // Reverse first
             __syncwarp();
             for (u32 k2 = 2; k2 <= np2; k2 <<= 1) {
                 for (u32 j = k2 >> 1; j > 0; j >>= 1) {
@@ -162,7 +163,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                     const u32 id = FUSED ? (u32)keys[ii] : b.sidx[base + ii];
                     rq[ii % RING] = b.a_qb[base + id];
                     rtb[ii % RING] = b.a_tb[base + id];
-                    rte[ii % RING] = FUSED ? (u32)(keys[ii] >> 32) : b.a_te[base + id];
+                    rte[ii % RING] = FUSED ? ((u32)(keys[ii] >> 32) ^ 0x80000000u) : b.a_te[base + id];
                 }
             };
             stage(0); stage(32);
@@ -176,7 +177,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                 const u32 s1 = (ia - d1) % RING, s2 = (ia - d2) % RING;
                 auto one = [&](bool live, u32 sj, bool& v, i32& t, i32& ra) {
                     const u32 qb_a = rq[sj], tb_a = rtb[sj], te_a = rte[sj];
-                    live = live && qb_a < qb_b && te_a < te_b;
+                    live = live && qb_a < qb_b && te_a < te_b && !(((tb_a ^ te_a) | (tb_a ^ tb_b) | (te_a ^ te_b)) >> 31);
                     const u32 ql = qb_b - qb_a;
                     const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
                     const u32 tl = min(tbd, te_b - te_a);
@@ -232,7 +233,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                     const u32 id = FUSED ? (u32)keys[ii] : b.sidx[base + ii];
                     rq[ii % RING] = b.a_qb[base + id];
                     rtb[ii % RING] = b.a_tb[base + id];
-                    rte[ii % RING] = FUSED ? (u32)(keys[ii] >> 32) : b.a_te[base + id];
+                    rte[ii % RING] = FUSED ? ((u32)(keys[ii] >> 32) ^ 0x80000000u) : b.a_te[base + id];
                 }
                 __syncwarp();
             }

@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
         i32 cbase = 0;                               // column at buffer index LPAD
         i32 qfill = -1;                              // query bytes of columns cbase .. qfill are staged
         i32 end0 = 0;
-        if (S == 0 || nrows == 0) status = VGA_ALN_EMPTY;
+        if (S == 0 || nrows == 0) status = it.status == VGA_ALN_UNSUPPORTED ? VGA_ALN_UNSUPPORTED : VGA_ALN_EMPTY;   // K4 refused the chain (reverse-strand anchors)
         else {
             const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
             end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);

@@ -386,7 +386,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 cells = 0; row = 0; s = 0; o = 0; ppb = 0; ppe = -1; lpos = 0; rpos = 0; mxrow = 0; ref = 0;
                 custom_base = 0xffffffffu;
                 phase = PH_ROW;
-                if (S == 0 || nrows == 0) { status = VGA_ALN_EMPTY; finish(); }
+                if (S == 0 || nrows == 0) { status = it.status == VGA_ALN_UNSUPPORTED ? VGA_ALN_UNSUPPORTED : VGA_ALN_EMPTY; finish(); }   // K4 refused the chain (reverse-strand anchors)
                 // absolute H is kept as int16 (trace words and shared memory): every DP step loses at most
                 // max(mismatch, o1+e1), so reachable scores are >= -that*(rows+qlen); other alignments go to the general kernel
                 else if (qlen + 2 > ncols - 8 || (!CHK && (i64)imax(b.mismatch, POE1) * ((i64)nrows + qlen) > PAIR_SCORE_LIMIT)) {

@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(PG_WARPS * 32, PG_MIN_CTAS) poa_fill_group_ker
             cells = 0; row = 0; s = 0; o = 0; ppb = 0; ppe = -1; lpos = 0; rpos = 0; mxrow = 0;
             custom_base = 0xffffffffu;
             active = true;
-            if (S == 0 || nrows == 0) { status = VGA_ALN_EMPTY; finish(); continue; }
+            if (S == 0 || nrows == 0) { status = it.status == VGA_ALN_UNSUPPORTED ? VGA_ALN_UNSUPPORTED : VGA_ALN_EMPTY; finish(); continue; }
             // absolute H is kept as int16 (trace words and shared memory): every DP step loses at most
             // max(mismatch, o1+e1), so reachable scores are >= -that*(rows+qlen); other alignments go to the general kernel
             if (qlen >= 256 || (i64)imax(b.mismatch, oe1) * ((i64)nrows + qlen) > SHORT_SCORE_LIMIT) {

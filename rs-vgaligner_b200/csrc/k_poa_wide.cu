@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(PW_THREADS) poa_fill_wide_kernel(DevIndex ix, 
         u32 s = 0, o = 0;
         i32 beg = 0, end = 0, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
         i32 end0 = 0;
-        if (S == 0 || nrows == 0) status = VGA_ALN_EMPTY;
+        if (S == 0 || nrows == 0) status = it.status == VGA_ALN_UNSUPPORTED ? VGA_ALN_UNSUPPORTED : VGA_ALN_EMPTY;
         else if (qlen + 2 * WPAD + 8 > lbuf) status = VGA_ALN_TOO_WIDE;     // the read does not fit the shared-memory row
         else {
             const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;

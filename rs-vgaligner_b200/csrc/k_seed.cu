@@ -154,7 +154,8 @@ seed_emit_kernel(DevIndex ix, u32 n, const u64* __restrict__ read_koff, const u3
                 a_qb[abase + id] = i;                      // query_begin = i, query_end = i + k
                 a_tb[abase + id] = tb;
                 a_te[abase + id] = te;
-                if (big) { sort_key[abase + id] = te; sort_val[abase + id] = id; }
+                // sort key: Reverse before Forward, then the position (src/chain.rs:386-389); bit 31 of te is the orientation
+                if (big) { sort_key[abase + id] = te ^ 0x80000000u; sort_val[abase + id] = id; }
             }
             carry += __shfl_sync(0xffffffffu, incl, 31);
         }

@@ -139,11 +139,24 @@ __global__ void __launch_bounds__(SUB_WARPS * 32) sub_count_kernel(DevIndex ix, 
         AlignItem it = b.items[w];
         const u64 cb = b.chain_anchor_off[it.chain], ce = b.chain_anchor_off[it.chain + 1];
         // ---- find_range_chain (:286-308): min/max handle over anchor starts and inclusive ends
-        u32 mn = 0xffffffffu, mx = 0;
+        u32 mn = 0xffffffffu, mx = 0, rev_any = 0;
         for (u64 m = cb + lane; m < ce; m += 32) {
-            const u32 n1 = ix.pos2node[b.ca_tb[m]], n2 = ix.pos2node[b.ca_te[m] - 1];
+            const u32 tb = b.ca_tb[m], te = b.ca_te[m];
+            rev_any |= (tb | te) >> 31;
+            if ((tb | te) >> 31) continue;
+            const u32 n1 = ix.pos2node[tb], n2 = ix.pos2node[te - 1];
             mn = min(mn, min(n1, n2));
             mx = max(mx, max(n1, n2));
+        }
+        if (__any_sync(0xffffffffu, rev_any)) {
+            // RangeOrient::Reverse / Both (src/align.rs:365-387): only reachable with VGA_FLAG_ALL_ORIENTATIONS; not aligned (vga.h)
+            if (lane == 0) {
+                AlignItem* o = b.items + w;
+                o->S = 0; o->nrows = 0; o->E = 0; o->qlen = (u32)(b.seq_off[it.read + 1] - b.seq_off[it.read]); o->q_off = b.seq_off[it.read];
+                o->ext_off = 0; o->ext_cnt = 0; o->min_node = 1; o->max_node = 0;
+                o->status = VGA_ALN_UNSUPPORTED;
+            }
+            continue;
         }
         mn = __reduce_min_sync(0xffffffffu, mn);
         mx = __reduce_max_sync(0xffffffffu, mx);

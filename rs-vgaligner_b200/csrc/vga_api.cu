@@ -687,7 +687,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     poa_begin_batch();
     const int NCLS = poa_class_count();
     std::vector<u64> est(NI);
-    std::vector<std::vector<u32>> cls(NCLS);
+    std::vector<std::vector<u32>> cls(NCLS + 1);       // [NCLS]: chains K4 refused (no subgraph: VGA_ALN_UNSUPPORTED stays), never launched
     u64 est_total = 0;
     u64 sum_rows = 0, sum_q = 0;
     // Host side of the classification, spread over a few threads for big batches (1.2 M items took 11 ms on one thread —
@@ -695,7 +695,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     // histograms turn into per-thread write positions, so the lists come out exactly as the serial loop built them.
     {
         const int NB = 48;
-        const size_t NK = (size_t)NCLS * NB;
+        const size_t NK = (size_t)(NCLS + 1) * NB;
         u32 NT = NI >= 200000 ? std::min<u32>(8, std::max<u32>(1, std::thread::hardware_concurrency())) : 1;
         if (const char* e = getenv("VGA_CLASSIFY_THREADS")) { const int v = atoi(e); if (v >= 1 && v <= 64) NT = (u32)v; }   // tests
         if (NT > NI) NT = 1;
@@ -721,6 +721,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             u64 et = 0, sr = 0, sq = 0, qm = 0;
             for (u32 i = i0; i < i1; i++) {
                 const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
+                if (h_meta[2ull * NI + i] == 0) { est[i] = 0; key[i] = (u32)(NCLS * NB); h[key[i]]++; continue; }
                 const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
                 const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
                 // rows are stored from an 8-column boundary (trace_col0); no kernel computes a band wider than 1024 columns
@@ -743,7 +744,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         // position of thread t's first item of key k inside its class list: items of smaller keys of the class, then the
         // same key in the threads before t
         std::vector<u32> start((size_t)NT * NK);
-        for (int ci = 0; ci < NCLS; ci++) {
+        for (int ci = 0; ci <= NCLS; ci++) {
             u32 run = 0;
             for (int kb = 0; kb < NB; kb++)
                 for (u32 t = 0; t < NT; t++) {
@@ -1149,6 +1150,10 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
     if (params->bandwidth == 0 || params->bandwidth > 96) { set_error("chaining bandwidth must be in 1..96"); return VGA_ERR_UNSUPPORTED; }
     if (params->best_n == 0 || params->min_anchors == 0) { set_error("best_n and min_anchors must be >= 1"); return VGA_ERR_INVALID; }
     if (params->max_gap > (1u << 24)) { set_error("max_gap too large"); return VGA_ERR_UNSUPPORTED; }
+    if (((params->flags & VGA_FLAG_ALL_ORIENTATIONS) != 0) != (ix->hdr.all_orient != 0)) {
+        set_error("VGA_FLAG_ALL_ORIENTATIONS needs an index uploaded with VGA_INDEX_ALL_ORIENTATIONS (and such an index serves nothing else)");
+        return VGA_ERR_INVALID;
+    }
     {   // the 32-bit trace word keeps E'/F relative to H in 3 + 5 bit fields (k_poa.cu): bounds on the gap model
         const VgaParams& q = *params;
         if (q.match < 0 || q.mismatch < 0 || q.e1 < 1 || q.e2 < 1 || q.o1 < 0 || q.o2 < 0 || q.o1 > 6 || q.o2 > 30 ||

@@ -53,7 +53,7 @@ void resolve_pointers(vga_index* ix) {
     d.pos2 = (const uint2*)(b + h.off_pos2);
 }
 
-static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader& hdr) {
+static int build_image(const VgaIndexView* v, bool keep_all, std::vector<u8>& img, IndexHeader& hdr) {
     if (!v || !v->seq_fwd || !v->node_ref || (v->n_edges && !v->edges)) {
         set_error("vga_index_upload: null pointer in view");
         return VGA_ERR_INVALID;
@@ -76,10 +76,13 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
             if (p >= v->n_table) { set_error("kmer_pos_table run without delimiter"); return VGA_ERR_INVALID; }
             u64 s = v->tab_start[p], e = v->tab_end[p];
             if (s == VGA_POS_DELIM && e == VGA_POS_DELIM) break;
-            if (!(s & VGA_POS_REV) && !(e & VGA_POS_REV)) {
+            if (keep_all || (!(s & VGA_POS_REV) && !(e & VGA_POS_REV))) {
                 // start > end is legal: a forward/forward k-mer may cross reverse handles (17-DRB1-3123-smooth has such links)
-                if (s >= L || e > L || e == 0) { set_error("k-mer position outside the linearisation"); return VGA_ERR_INVALID; }
-                ptb.push_back((u32)s); pte.push_back((u32)e); cnt++;
+                const u64 sp = s & ~VGA_POS_REV, ep = e & ~VGA_POS_REV;
+                if (sp >= L || ep > L || ep == 0) { set_error("k-mer position outside the linearisation"); return VGA_ERR_INVALID; }
+                ptb.push_back((u32)sp | ((s & VGA_POS_REV) ? 0x80000000u : 0u));
+                pte.push_back((u32)ep | ((e & VGA_POS_REV) ? 0x80000000u : 0u));
+                cnt++;
             }
             p++;
         }
@@ -93,7 +96,7 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
     const char* ct_env = getenv("VGA_TABLE_COMPACT");
     // by default only for tables that would not stay in L2 as 16-byte slots (measured: C4 seed stage 7.8 -> 6.0 ms per 2 M reads,
     // C5 6.8 -> 5.6 ms; on the L2-resident 2.8 MB table of C2 the longer probe body costs 0.39 -> 0.44 ms; gpurun_out/r02g)
-    const bool compact = v->k <= 16 && L < (1ull << 26) && ptb.size() + ents.size() < (1ull << 26) && !ents.empty() &&
+    const bool compact = !keep_all && v->k <= 16 && L < (1ull << 26) && ptb.size() + ents.size() < (1ull << 26) && !ents.empty() &&
                          (ct_env ? atoi(ct_env) != 0 : ents.size() >= (1u << 20));
     if (!compact) while (n_slots < 2 * ents.size()) n_slots <<= 1;            // the compact table replaces the slots
     if (n_slots > (1ull << 32)) { set_error("k-mer table too large"); return VGA_ERR_UNSUPPORTED; }
@@ -149,6 +152,7 @@ static int build_image(const VgaIndexView* v, std::vector<u8>& img, IndexHeader&
     place(hdr.off_pos_tb, compact ? 0 : 4 * ptb.size());
     place(hdr.off_pos_te, compact ? 0 : 4 * pte.size());
     hdr.n_buckets = n_buckets; hdr.n_pos2 = pos2.size() / 2;
+    hdr.all_orient = keep_all ? 1 : 0;
     place(hdr.off_buckets, 64 * n_buckets);
     place(hdr.off_pos2, 4 * pos2.size());
     hdr.bytes = o;
@@ -242,14 +246,17 @@ static int require_device() {
     return VGA_OK;
 }
 
-int vga_index_upload(const VgaIndexView* view, vga_index_t** out) {
+int vga_index_upload(const VgaIndexView* view, vga_index_t** out) { return vga_index_upload_ex(view, 0, out); }
+
+int vga_index_upload_ex(const VgaIndexView* view, uint32_t flags, vga_index_t** out) {
     if (!out) { set_error("vga_index_upload: out is null"); return VGA_ERR_INVALID; }
+    if (flags & ~VGA_INDEX_ALL_ORIENTATIONS) { set_error("vga_index_upload_ex: unknown flag"); return VGA_ERR_INVALID; }
     *out = nullptr;
     int rc = require_device();
     if (rc != VGA_OK) return rc;
     std::vector<u8> img;
     IndexHeader hdr;
-    rc = build_image(view, img, hdr);
+    rc = build_image(view, (flags & VGA_INDEX_ALL_ORIENTATIONS) != 0, img, hdr);
     if (rc != VGA_OK) return rc;
     vga_index* ix = new vga_index();
     try {

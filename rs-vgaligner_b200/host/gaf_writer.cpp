@@ -132,13 +132,17 @@ static void format_chains(const Job& J, uint32_t r0, uint32_t r1, Buf& out) {
             p = put_u64(p, (uint64_t)R.ca_qb[e - 1] + k);
             p = PUT_LIT(p, "\t+\t");
             for (uint64_t a = b; a < e; a++) {
-                const uint64_t tb = R.ca_tb[a], tei = (uint64_t)R.ca_te[a] - 1;      // get_end_seqpos_inclusive, src/chain.rs:65-70
-                const uint32_t n1 = J.tb->pos2node[tb], n2 = J.tb->pos2node[tei];
-                *p++ = '('; *p++ = '>';
+                // bit 31 = Reverse (only with VGA_FLAG_ALL_ORIENTATIONS).  The node of a reverse-strand position p is the node of the
+                // forward position L - 1 - p (handle_from_seqpos, src/index.rs:403-405); AnchorPosOnGraph::new subtracts the node's
+                // FORWARD start also from a reverse-strand position (src/chain.rs:96-121): u64 arithmetic, wrapping like a release build
+                const bool r1 = R.ca_tb[a] >> 31, r2 = R.ca_te[a] >> 31;
+                const uint64_t tb = R.ca_tb[a] & 0x7fffffffu, tei = (uint64_t)(R.ca_te[a] & 0x7fffffffu) - 1;      // get_end_seqpos_inclusive, src/chain.rs:65-70
+                const uint32_t n1 = J.tb->pos2node[r1 ? J.ix->seq_len - 1 - tb : tb], n2 = J.tb->pos2node[r2 ? J.ix->seq_len - 1 - tei : tei];
+                *p++ = '('; *p++ = r1 ? '<' : '>';
                 p = put_u64(p, n1);
                 *p++ = ':';
                 p = put_u64(p, tb - J.tb->starts[n1 - 1]);
-                *p++ = ','; *p++ = '>';
+                *p++ = ','; *p++ = r2 ? '<' : '>';
                 p = put_u64(p, n2);
                 *p++ = ':';
                 p = put_u64(p, tei - J.tb->starts[n2 - 1]);

@@ -453,3 +453,29 @@ def test_gpu_index_build_refuses_walk_explosions():
     ix = vg.Index.build(fixture_path("graphs/5-B3106.gfa"), 11)
     with pytest.raises(vg.VgaError):
         vg.index_build_device(ix, 11)
+
+
+def test_reverse_strand_anchors_and_chains():
+    """`only_forward = false` (reference src/chain.rs:154-156): an index uploaded with every table position, anchors of both
+    strands, Reverse-first sort, chaining within one orientation; chains GAF with '<' positions.  Half of the reads are reverse
+    complemented, so most chains of those lie on the reverse strand; their alignment is refused (VGA_ALN_UNSUPPORTED), forward
+    chains align as always."""
+    for graph, k in (("graphs/19-MICB-4227-smooth.gfa", 11), ("graphs/17-DRB1-3123-smooth.gfa", 11), ("test.gfa", 4)):
+        ix = vg.Index.build(fixture_path(graph), k)
+        ix.upload_flags = vg.VGA_INDEX_ALL_ORIENTATIONS
+        reads = vg.simulate_reads(ix, 1500, 150 if k == 11 else 30, 0.01, 0.0005, 0.0005, 0.5, 51)
+        gp = vg.default_params(flags=vg.VGA_FLAG_KEEP_DEBUG | vg.VGA_FLAG_ALL_ORIENTATIONS)
+        op = orc.default_params(flags=orc.FLAG_KEEP_DEBUG | orc.FLAG_ALL_ORIENTATIONS)
+        g = vg.map_reads(ix, reads, params=gp)
+        oi = orc.OracleIndex(ix)
+        o = oi.map_reads(reads, op, n_threads=8)
+        assert_same(g, o, SEED + SORT + CHAIN + ALN)
+        assert g.gaf(0) == o.gaf(oi, reads, 0)
+        if k == 11:
+            assert (g.ca_tb >> 31).sum() > 1000 and (g.aln_status == vg.ALN_UNSUPPORTED).sum() > 100
+            assert (g.aln_status == vg.ALN_OK).sum() > 100
+            assert ",<" in g.gaf(0)
+        # the forward-only default on the same reads: a flag / index mismatch is an error, not a silent fallback
+        with pytest.raises(vg.VgaError):
+            vg.map_reads(ix, reads, params=vg.default_params())
+        ix.free_device()

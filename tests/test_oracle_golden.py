@@ -262,3 +262,28 @@ def test_literal_extension_equals_memoised():
     assert a.dbg_edges.tolist() == b.dbg_edges.tolist()
     assert a.aln_runs.tolist() == b.aln_runs.tolist()
     assert (a.aln_status == 1).sum() > 10
+
+
+def test_all_orientations_through_map_reads():
+    """ORC_FLAG_ALL_ORIENTATIONS = anchors_for_query(.., only_forward = false) (src/chain.rs:154-156) inside the per-read driver:
+    the reverse complement of a read that chains on the forward strand chains on the reverse strand, with the orientation in
+    bit 31 of ca_tb / ca_te, and is not aligned; the chains record spells reverse handles with '<' (src/align.rs:856-888)."""
+    ix = vg.Index.build(fixture_path("graphs/19-MICB-4227-smooth.gfa"), 11)
+    fwd = ix.seq_fwd[1000:1150]
+    rc = fwd[::-1].translate(str.maketrans("ACGT", "TGCA"))
+
+    class R:
+        n = 2
+        names = ["f", "r"]
+        seqs = np.frombuffer((fwd + rc).encode(), dtype=np.uint8).copy()
+        offsets = np.array([0, 150, 300], dtype=np.uint64)
+    oi = orc.OracleIndex(ix)
+    a = oi.map_reads(R, orc.default_params(), n_threads=1)
+    b = oi.map_reads(R, orc.default_params(flags=orc.FLAG_ALL_ORIENTATIONS), n_threads=1)
+    assert a.chain_off.tolist() == [0, 1, 1] and a.aln_status.tolist() == [1, 0]          # forward only: the reverse read is a placeholder
+    assert b.chain_off.tolist()[1] >= 1 and b.chain_off.tolist()[2] > b.chain_off.tolist()[1]
+    lo = int(b.chain_anchor_off[b.chain_off[1]])
+    assert (b.ca_tb[lo:] >> 31).all() and (b.ca_te[lo:] >> 31).all()
+    assert b.aln_status.tolist() == [1, 5]                                                  # VGA_ALN_UNSUPPORTED = 5
+    line = b.gaf(oi, R, 0).split("\n")[-2]
+    assert line.startswith("r\t150\t") and "(<" in line and ",<" in line
