@@ -543,8 +543,13 @@ static int g_pair = getenv("VGA_POA_PAIR") ? atoi(getenv("VGA_POA_PAIR")) : 1;
 // measured 125 ms against 74 ms on the SLIDE kernel for those items (gpurun_out/r02l).  Few items mean two or three warps per SM,
 // so what counts is the latency of ONE row, and an 8-lane step of ~550 dependent instructions is longer than a 32-lane SLIDE row.
 // VGA_POA_CHK=1 enables it (read per batch: the tests run both).
-static int g_pair_chk = 0;
-void poa_begin_batch() { const char* e = getenv("VGA_POA_CHK"); g_pair_chk = e ? atoi(e) : 0; }
+static int g_pair_chk = 0, g_force_wide = 0;
+void poa_begin_batch() {
+    const char* e = getenv("VGA_POA_CHK");
+    g_pair_chk = e ? atoi(e) : 0;
+    e = getenv("VGA_POA_WIDE");
+    g_force_wide = e ? atoi(e) == 1 : 0;
+}
 // long reads (and everything else that is not a short-read class) run on the shared-memory kernel of k_poa_long.cu as
 // class 3; VGA_POA_LONG=0 restores the register-resident SLIDE instances on classes 3..7 (A/B measurements)
 // The shared-memory kernel wins on throughput (work proportional to the band, 64 registers), the register-resident
@@ -559,7 +564,7 @@ static int g_short_w8 = getenv("VGA_POA_W8") ? atoi(getenv("VGA_POA_W8")) : 0;
 int poa_class_count() { return 9; }
 bool poa_pair_active() { return g_pair != 0; }
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode) {
-    if (const char* e = getenv("VGA_POA_WIDE")) { if (atoi(e) == 1) return 8; }      // tests: every alignment on the CTA-per-alignment kernel
+    if (g_force_wide) return 8;                                                      // tests (VGA_POA_WIDE=1): every alignment on the CTA-per-alignment kernel
     if (g_pair) {
         if (poa_pair_ok(qlen, nrows, P)) return 0;
         if (g_pair_chk && poa_pair_checked_ok(qlen, nrows, P)) return 1;

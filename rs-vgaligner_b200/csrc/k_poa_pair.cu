@@ -633,14 +633,9 @@ int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n
     // row has ~9 blocks and 4 lanes x 2 blocks waste fewer block slots (C4: fill 170 -> 141 ms per 2 M reads, gpurun_out/r02d)
     const int g = genv ? genv : (nbmax >= 3 ? 8 : 4);
     if (cls == 1) launch_pair<8, 3, 4, true>(ix, b, n_sms, st);      // subgraphs far longer than the read: most rows at full band width
-    else if (g == 4) {
-        static const int minb = getenv("VGA_POA_MINB") ? atoi(getenv("VGA_POA_MINB")) : 4;     // A/B: CTAs per SM the register budget is cut for
-        if (nbmax <= 2) {
-            if (minb == 5) launch_pair<4, 2, 5, false>(ix, b, n_sms, st);
-            else if (minb == 6) launch_pair<4, 2, 6, false>(ix, b, n_sms, st);
-            else launch_pair<4, 2, 4, false>(ix, b, n_sms, st);
-        } else launch_pair<4, 3, 4, false>(ix, b, n_sms, st);
-    }
+    // (tried: the same instance cut to 102 / 85 registers for 5 / 6 CTAs per SM, with and without reloading E' in sweep 2b:
+    // 137-144 ms and 160-197 ms against 139 ms per 2 M reads of C4 — spills cost more than the extra warps hide; gpurun_out/r02i, r02r)
+    else if (g == 4) { if (nbmax <= 2) launch_pair<4, 2, 4, false>(ix, b, n_sms, st); else launch_pair<4, 3, 4, false>(ix, b, n_sms, st); }
     else if (g == 2) { if (nbmax <= 2) launch_pair<2, 2, 4, false>(ix, b, n_sms, st); else launch_pair<2, 3, 4, false>(ix, b, n_sms, st); }
     else if (nbmax == 1) launch_pair<8, 1, 4, false>(ix, b, n_sms, st);
     else if (nbmax == 2) launch_pair<8, 2, 4, false>(ix, b, n_sms, st);

@@ -66,6 +66,10 @@ struct vga_workspace {
     u64 pool_capped_words = 0;  // size the trace pool was cut to by free memory (0: never cut)
     double gap_k = -1, gap_max = -1;
     bool gap_int_ok = false;
+    // host-side scratch of the item classification, kept across calls (fresh vectors of this size cost milliseconds of page faults)
+    std::vector<u64> h_est;
+    std::vector<u32> h_key;
+    std::vector<std::vector<u32>> h_cls;
 };
 
 namespace vga {
@@ -686,8 +690,11 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     // (persistent warps pull work in list order, so the long alignments do not end up as a tail)
     poa_begin_batch();
     const int NCLS = poa_class_count();
-    std::vector<u64> est(NI);
-    std::vector<std::vector<u32>> cls(NCLS + 1);       // [NCLS]: chains K4 refused (no subgraph: VGA_ALN_UNSUPPORTED stays), never launched
+    std::vector<u64>& est = w->h_est;
+    est.resize(NI);
+    std::vector<std::vector<u32>>& cls = w->h_cls;     // [NCLS]: chains K4 refused (no subgraph: VGA_ALN_UNSUPPORTED stays), never launched
+    cls.resize(NCLS + 1);
+    for (auto& l : cls) l.clear();
     u64 est_total = 0;
     u64 sum_rows = 0, sum_q = 0;
     // Host side of the classification, spread over a few threads for big batches (1.2 M items took 11 ms on one thread —
@@ -712,10 +719,13 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             for (u32 i = i0; i < i1; i++) nl += poa_short_ok(h_meta[NI + i], h_meta[i], P) ? 0 : 1;
             part[(size_t)t * 8] = nl;
         });
+        tl_mark("classify: long count");
         u64 n_long = 0;
         for (u32 t = 0; t < NT; t++) n_long += part[(size_t)t * 8];
         pb.long_mode = poa_long_mode(n_long, w->n_sms);
-        std::vector<u32> key(NI), hist((size_t)NT * NK, 0);
+        std::vector<u32>& key = w->h_key;
+        key.resize(NI);
+        std::vector<u32> hist((size_t)NT * NK, 0);
         par([&](u32 t, u32 i0, u32 i1) {
             u32* h = hist.data() + (size_t)t * NK;
             u64 et = 0, sr = 0, sq = 0, qm = 0;
@@ -741,6 +751,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             est_total += pt[1]; sum_rows += pt[2]; sum_q += pt[3];
             if ((i64)pt[4] > (i64)pb.qmax_short) pb.qmax_short = (i32)pt[4];
         }
+        tl_mark("classify: keys");
         // position of thread t's first item of key k inside its class list: items of smaller keys of the class, then the
         // same key in the threads before t
         std::vector<u32> start((size_t)NT * NK);
@@ -759,6 +770,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             for (u32 i = i0; i < i1; i++) cls[key[i] / NB][st_t[key[i]]++] = i;
         });
     }
+    tl_mark("classify: lists");
     // subgraphs much longer than their reads spend most rows at full band width: worth the 3-block step body (more registers)
     pb.nb_hint = sum_rows >= 3 * sum_q ? 3 : 2;
     const u64 warp_slack = (u64)w->n_sms * 64 * 8192;
@@ -914,7 +926,9 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         // tracebacks; an overflow is handled like any other (IT_RETRY_POOL: trace, start the pool over, rerun).  Tried and
         // dropped: learning the factor from the previous wave (overflows and reruns cost more than fuller waves gain) and
         // accounting the real use instead of the estimate (leaves room for tiny follow-up waves that cannot fill the machine).
-        const double scale = ci >= 3 ? 0.62 : 1.0;
+        // Short-read classes: 0.34-0.43 of the estimate on C2 / C3 / C4 (the estimate assumes the widest band on every row, most
+        // rows are narrower), admitted at 0.55: a 1 M-read call of C4 needs 2 waves instead of 4.
+        const double scale = ci >= 3 ? 0.62 : 0.55;
         auto cost = [&](u32 it) { return (u64)((double)(est[it] + est[it] / 4) * scale) + 64; };
         while (pos < list.size()) {
             // take a wave whose estimate fits what is left of the pool
