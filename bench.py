@@ -418,6 +418,12 @@ def gpu_record(G, name, wl, args):
         traffic["source"] = tj.get("source")
     except Exception:
         pass
+    def per_unit(key):
+        """DRAM bytes per algorithmic unit (cell / lookup byte) of the profiled launch (profiles/traffic.json, regenerated by
+        tools/make_profiles.py from the ncu captures of the current build); scaled to this run's launches below"""
+        b, u = traffic.get(key + "_bytes_per_launch"), traffic.get(key + "_units_in_launch")
+        return b / u if b and u else None
+
     cells = sumf(last, "poa_cells")
     poa_ms, poa_launches = mean("ms_poa"), max(1, sumf(last, "poa_launches"))
     gcups = cells / (poa_ms * 1e-3) / 1e9 if poa_ms > 0 else 0.0
@@ -425,15 +431,16 @@ def gpu_record(G, name, wl, args):
     kern = "poa_fill_seg_kernel / poa_fill_pair_kernel (short reads)" if wl["length"] < 246 else "poa_fill_long_kernel (long reads)"
     roof_poa = {"kernel": kern + ": all fill launches of a step", "bound": "int32_alu", "achieved": gcups, "peak": gcups_peak,
                 "unit": "GCUPS", "frac": gcups / gcups_peak if gcups_peak else None,
-                "traffic": traffic.get("poa_fill_bytes_per_launch"), "traffic_source": traffic.get("source"),
+                "traffic": per_unit("poa_fill") * (cells / poa_launches) if per_unit("poa_fill") else None, "traffic_source": traffic.get("source"),
+                "traffic_note": traffic.get("poa_fill_note"),
                 "peak_source": "measured here: %.1f T int32 op/s (IADD+IMNMX streams) / 17 ops per cell" % (G.int32_peak / 1e12),
                 "launches_per_step": poa_launches, "ms_per_launch": poa_ms / poa_launches, "cells_per_launch": cells / poa_launches}
     seed_ms = mean("ms_seed")
     lbytes = sumf(last, "lookup_bytes")
     gbs = lbytes / (seed_ms * 1e-3) / 1e9 if seed_ms > 0 else 0.0
     roof_seed = {"kernel": "seed_count_kernel+seed_emit_kernel (K1 stage)", "bound": "hbm", "achieved": gbs, "peak": hbm_peak,
-                 "unit": "GB/s", "frac": gbs / hbm_peak, "traffic": traffic.get("seed_bytes_per_launch"),
-                 "traffic_source": traffic.get("source"), "peak_source": hbm_src, "ms_per_step": seed_ms, "bytes_per_step": lbytes}
+                 "unit": "GB/s", "frac": gbs / hbm_peak, "traffic": per_unit("seed") * lbytes if per_unit("seed") else None,
+                 "traffic_source": traffic.get("source"), "traffic_note": traffic.get("seed_note"), "peak_source": hbm_src, "ms_per_step": seed_ms, "bytes_per_step": lbytes}
     stage_keys = ("ms_h2d", "ms_seed", "ms_sort", "ms_chain", "ms_subgraph", "ms_poa", "ms_trace", "ms_d2h", "ms_total")
     stage = {k: mean(k) for k in stage_keys}
     rec = {"value": total_reads * K / (ms_dev_max * 1e-3), "ms_per_step": ms_dev_max / K,

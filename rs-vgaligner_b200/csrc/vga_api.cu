@@ -839,9 +839,10 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
                 const int nc = poa_class_wider(ci, pb.long_mode);
                 if (nc == 8) {
                     // the band left the 1024 columns of the warp kernels: nothing bounds it but the read.  Measured on C5's
-                    // reverse-strand reads (random k-mer hits chained): 0.07-0.1 of rows x read length
+                    // reverse-strand reads (random k-mer hits chained): 0.07-0.1 of rows x read length (0.19 of rows x (read / 4 + 1024),
+                    // which cut the 1.1 k such alignments of a 12.5 k-read call into three waves)
                     const u64 nr = h_meta[it], ql = h_meta[NI + it];
-                    est[it] = std::max<u64>(est[it], nr * (ql / 4 + 1024));
+                    est[it] = std::max<u64>(est[it], nr * (ql / 8 + 256));
                 }
                 if (nc >= 0) cls[nc].push_back(it); else done++;
             }
