@@ -1,9 +1,9 @@
 #!/bin/bash
-# One GPU-box visit that produces everything profiles/ holds for a round.  usage: tools/gpu_evidence.sh <tag>   (gpurun, 1 GPU)
+# One GPU-box visit that produces everything profiles/ holds for a round.  usage: tools/gpu_evidence.sh <tag> <git sha>   (gpurun, 1 GPU)
 #   parity tests + smoke, the default bench line (C4 10 M reads + C5 record), C2 / C3a / C3b lines, the reference arm,
 #   ncu launch list of a short default bench, ncu --set full of the dominant kernels on the CURRENT build, host timelines.
 TAG=${1:-rXX}; O=gpurun_out; mkdir -p $O
-git rev-parse HEAD > $O/${TAG}_sha.txt 2>/dev/null || echo unknown > $O/${TAG}_sha.txt
+echo "${2:-unknown}" > $O/${TAG}_sha.txt      # the box has no .git: the caller passes the SHA of the tree it sends
 timeout 1500 python -m pytest tests -m gpu -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 $O/${TAG}_pytest.log
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
 timeout 1200 python bench.py --steps 3 --warmup 3 > $O/${TAG}_bench_default.json 2> $O/${TAG}_bench_default.err; echo "bench default rc=$?"
