@@ -92,6 +92,7 @@ int launch_sub_count(const DevIndex& ix, const SubBuffers& b, cudaStream_t st);
 int launch_sub_fill(const DevIndex& ix, const SubBuffers& b, cudaStream_t st);
 int launch_sub_rowmeta(const DevIndex& ix, const SubBuffers& b, u32* row_meta, cudaStream_t st);   // per-row records (k_subgraph.cu)
 
+struct TraceBuffers;
 struct PoaBuffers {
     u32 n_items;             // entries of work[]
     const u32* work;         // item indices to process in this launch
@@ -120,10 +121,10 @@ int poa_class_count();
 bool poa_pair_active();    // classes 0..1 run on the 16x2 kernel (plane trace rows); false with VGA_POA_PAIR=0
 int poa_class_for(i64 qlen, i64 nrows, i64 west, const VgaParams& P, int long_mode);
 int poa_class_wider(int cls, int long_mode);    // -1: none
-int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
+int launch_poa_fill(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st, const TraceBuffers* fused_tb = nullptr);
 int launch_poa_fill_short(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);
 bool poa_short_ok(i64 qlen, i64 nrows, const VgaParams& P);   // read short enough and scores within int16
-int launch_poa_fill_long(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st);              // k_poa_long.cu
+int launch_poa_fill_long(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st, const TraceBuffers* fused_tb = nullptr);   // k_poa_long.cu
 int launch_poa_fill_wide(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st);              // k_poa_wide.cu
 int launch_poa_fill_pair(const DevIndex& ix, const PoaBuffers& b, int cls, int n_sms, cudaStream_t st);   // k_poa_pair.cu
 bool poa_pair_checked_ok(i64 qlen, i64 nrows, const VgaParams& P);   // same, scores checked per row instead of bounded a priori

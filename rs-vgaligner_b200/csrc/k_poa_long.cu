@@ -18,14 +18,17 @@
 // Roofline: INT32 ALU issue.  Algorithmic work = band cells.
 #include <climits>
 #include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 #include "internal.h"
+#include "k_poa_trace.cuh"
 
 namespace vga {
 
 static const int PL_WARPS = 2;              // warps per CTA (7.8 KB of shared memory each)
 static const u64 LONG_POOL_CHUNK = 8192;    // trace words a warp takes from the pool per refill
+static const u64 LONG_ARENA_MIN = 4u << 20;  // fused kernel: smallest useful arena (words): a 10 kb alignment writes 3-4 M
 static const int LPAD = 8;                  // buffer index of column cbase (column cbase-1 .. are guards)
 static const int WIN = 1280;                // columns of the window (bands are at most 1024 + the odd block size slack)
 static const int LBUF = LPAD + WIN + 8;     // index of column beg + 32*CR + 1 stays below LPAD + WIN (re-anchoring rule below)
@@ -168,7 +171,12 @@ __device__ __forceinline__ int long_pick_cr(i32 W) {
     return W > 1024 ? 0 : (((W + 31) >> 5) | 1) < 3 ? 3 : (((W + 31) >> 5) | 1);
 }
 
-__global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex ix, PoaBuffers b) {
+// FUSED: every warp owns a private arena of the trace pool (arena_words from arena 0 of warp 0 on), fills an alignment into it and
+// traces it right away (lane 0; k_poa_trace.cuh) before it takes the next one — no waves, no traceback launches that leave the
+// machine to a few thousand threads, no host round trip between fill and traceback.  An alignment that does not fit the arena ends
+// as IT_RETRY_POOL and goes through the wave path afterwards.
+template <bool FUSED>
+__global__ void __launch_bounds__(PL_WARPS * 32, FUSED ? 12 : 12) poa_fill_long_kernel(DevIndex ix, PoaBuffers b, TraceBuffers tb, u64 arena_words) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     LongSmem& sm = ((LongSmem*)dyn_smem)[threadIdx.x >> 5];
     const u32 lane = threadIdx.x & 31;
@@ -176,12 +184,14 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
     K.e1 = b.e1; K.e2 = b.e2; K.oe1 = b.o1 + b.e1; K.oe2 = b.o2 + b.e2; K.o1 = b.o1; K.o2 = b.o2;
     K.smatch = b.match; K.smis = -b.mismatch;
     u64 pool_cur = 0, pool_end = 0;                 // this warp's current chunk of the trace pool (words)
+    const u64 arena_base = FUSED ? ((u64)blockIdx.x * PL_WARPS + (threadIdx.x >> 5)) * arena_words : 0;
     for (;;) {
         // ---- next (read, chain) of the work list
         u32 wi = 0;
         if (lane == 0) wi = atomicAdd(b.work_ctr, 1u);
         wi = __shfl_sync(FULLW, wi, 0);
         if (wi >= b.n_items) break;
+        if (FUSED) { pool_cur = arena_base; pool_end = arena_base + arena_words; }     // the arena starts over with every alignment
         const u32 w = b.work[wi];
         const AlignItem it = b.items[w];
         const i32 qlen = (i32)it.qlen;
@@ -234,12 +244,15 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
             // pool space: one trace word per band cell, rows stored from an 8-column boundary (trace_col0)
             const u64 need = (u64)((W + (beg & 7) + 3) & ~3);
             if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
-                unsigned long long got = 0;
-                const u64 take = need > LONG_POOL_CHUNK ? need : LONG_POOL_CHUNK;
-                if (lane == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
-                got = __shfl_sync(FULLW, got, 0);
-                if (got + take > b.pool_words) status = IT_RETRY_POOL;
-                else { pool_cur = got; pool_end = got + take; }
+                if (FUSED) status = IT_RETRY_POOL;            // larger than the arena: the wave path takes it
+                else {
+                    unsigned long long got = 0;
+                    const u64 take = need > LONG_POOL_CHUNK ? need : LONG_POOL_CHUNK;
+                    if (lane == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
+                    got = __shfl_sync(FULLW, got, 0);
+                    if (got + take > b.pool_words) status = IT_RETRY_POOL;
+                    else { pool_cur = got; pool_end = got + take; }
+                }
             }
             if (status != VGA_ALN_OK) break;
             u32* __restrict__ tr = b.pool + pool_cur + (beg & 7);
@@ -377,26 +390,46 @@ __global__ void __launch_bounds__(PL_WARPS * 32) poa_fill_long_kernel(DevIndex i
             out->n_runs = 0; out->n_path = 0; out->path_len = 0; out->start_off = 0; out->end_off = 0; out->n_aligned = 0;
         }
         __syncwarp();
+        if (FUSED && status == VGA_ALN_OK) {
+            if (lane == 0) poa_trace_one<false>(tb, w);        // rows, trace words and the record above are visible after the barrier
+            __syncwarp();
+        }
     }
 }
 
-int launch_poa_fill_long(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st) {
-    if (b.n_items == 0) return 0;
+template <bool FUSED>
+static int launch_long(const DevIndex& ix, const PoaBuffers& b, const TraceBuffers& tb, int n_sms, cudaStream_t st) {
     int per_sm = 0;
     const size_t smem_bytes = (size_t)PL_WARPS * sizeof(LongSmem);
     static bool attr_set = false;
     if (!attr_set) {
-        VGA_CUDA(cudaFuncSetAttribute(poa_fill_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        VGA_CUDA(cudaFuncSetAttribute(poa_fill_long_kernel<FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
         attr_set = true;
     }
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, poa_fill_long_kernel, PL_WARPS * 32, smem_bytes);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, poa_fill_long_kernel<FUSED>, PL_WARPS * 32, smem_bytes);
     if (per_sm < 1) per_sm = 1;
     long long ctas = (long long)n_sms * per_sm;
     const long long need = ((long long)b.n_items + PL_WARPS - 1) / PL_WARPS;
     if (ctas > need) ctas = need;
     if (ctas < 1) ctas = 1;
-    poa_fill_long_kernel<<<(unsigned)ctas, PL_WARPS * 32, smem_bytes, st>>>(ix, b);
+    u64 arena = 0;
+    if (FUSED) {
+        // one arena per resident warp; an alignment larger than its arena is left to the wave path (IT_RETRY_POOL).  Fewer, larger
+        // arenas when the pool is small for the machine: at least LONG_ARENA_MIN words each
+        arena = (b.pool_words / (u64)(ctas * PL_WARPS)) & ~(u64)3;
+        while (arena < LONG_ARENA_MIN && ctas > 1) { ctas = (ctas + 1) / 2; arena = (b.pool_words / (u64)(ctas * PL_WARPS)) & ~(u64)3; }
+    }
+    poa_fill_long_kernel<FUSED><<<(unsigned)ctas, PL_WARPS * 32, smem_bytes, st>>>(ix, b, tb, arena);
     return 1;
+}
+
+// fused_tb != NULL: fill + traceback per warp in private arenas of the pool (the pool must hold nothing that still awaits a traceback)
+int launch_poa_fill_long(const DevIndex& ix, const PoaBuffers& b, int n_sms, cudaStream_t st, const TraceBuffers* fused_tb) {
+    if (b.n_items == 0) return 0;
+    if (fused_tb) return launch_long<true>(ix, b, *fused_tb, n_sms, st);
+    TraceBuffers none;
+    memset(&none, 0, sizeof(none));
+    return launch_long<false>(ix, b, none, n_sms, st);
 }
 
 }  // namespace vga

@@ -220,6 +220,8 @@ __global__ void __launch_bounds__(SUB_WARPS * 32) sub_count_kernel(DevIndex ix, 
             o->S = S; o->nrows = rows; o->E = E; o->qlen = qlen; o->q_off = b.seq_off[it.read];
             o->ext_off = eoff; o->ext_cnt = n_ext; o->min_node = mn; o->max_node = mx;
             o->status = IT_PENDING;
+            // row records keep max_remain in 21 bits (sub_rowmeta_kernel): a subgraph of 2^21 rows or more is refused, not clamped
+            if (rows >= (1u << 21)) { o->S = 0; o->nrows = 0; o->E = 0; o->ext_cnt = 0; o->min_node = 1; o->max_node = 0; o->status = VGA_ALN_UNSUPPORTED; }
         }
     }
 }

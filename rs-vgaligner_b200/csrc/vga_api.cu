@@ -931,6 +931,40 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         // rows are narrower), admitted at 0.55: a 1 M-read call of C4 needs 2 waves instead of 4.
         const double scale = ci >= 3 ? 0.62 : 0.55;
         auto cost = [&](u32 it) { return (u64)((double)(est[it] + est[it] / 4) * scale) + 64; };
+        // Long reads on the shared-memory kernel: ONE fused launch first — every warp fills an alignment into its private arena of
+        // the pool and traces it right away (k_poa_long.cu).  No waves, no traceback launches of a few thousand threads, no host
+        // round trips in between; alignments larger than an arena come back as pool retries and take the wave path below.
+        {
+            const char* fe = getenv("VGA_POA_FUSED");
+            if (ci == 3 && pb.long_mode && !list.empty() && (fe ? atoi(fe) != 0 : true)) {
+                flush_trace();                                   // the arenas take the whole pool: nothing may wait in it
+                const u32 nw = (u32)list.size();
+                VGA_CUDA(cudaMemcpyAsync(d_work, list.data(), 4ull * nw, cudaMemcpyHostToDevice, st));
+                VGA_CUDA(cudaMemsetAsync(ctr + 2, 0, 4, st));
+                pb.n_items = nw; pb.work = d_work;
+                VGA_CUDA(cudaEventRecord(w->ev[8], st));
+                c.launches += launch_poa_fill(dv, pb, ci, w->n_sms, st, &tbuf);
+                stage_check(st, "poa_fill (fused long reads)");
+                R.stats.poa_launches++;
+                VGA_CUDA(cudaEventRecord(w->ev[9], st));
+                item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
+                c.launches++;
+                queue_chain_d2h();
+                VGA_CUDA(cudaMemcpyAsync(h_status.data(), d_status, 4ull * nw, cudaMemcpyDeviceToHost, st));
+                VGA_CUDA(cudaStreamSynchronize(st));
+                float a = 0;
+                cudaEventElapsedTime(&a, w->ev[8], w->ev[9]);
+                ms_fill += a;
+                std::vector<u32> again;
+                u32 done = 0;
+                absorb(ci, list.data(), nw, h_status.data(), true, again, done);
+                if (host_timeline()) fprintf(stderr, "[vga] poa fill+trace class 3 (fused, per-warp arenas): %u items, %.3f ms, %zu left to the wave path\n", nw, a, again.size());
+                list.swap(again);
+                VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
+                pool_acc = warp_slack;
+                used_prev = 0;
+            }
+        }
         while (pos < list.size()) {
             // take a wave whose estimate fits what is left of the pool
             const u64 first = cost(list[pos]);

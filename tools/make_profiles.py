@@ -45,7 +45,7 @@ traffic = {"source": "ncu --set full captures of tools/gpu_evidence.sh %s, tree 
            "dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel on the named workload size, and the algorithmic units of "
            "that same launch (cells / lookup bytes from a bench run with the same --reads): bench.py scales bytes per unit to its own launches"}
 for wl, reads, key, rep, unit_key in (("C4", 250000, "poa_fill", "pair_C4", "poa_cells"), ("C2", 100000, "poa_fill", "pair_C2", "poa_cells"),
-                                      ("C5", 12500, "poa_fill", "long_C5", "poa_cells"), ("C4", 1000000, "seed", "seed_count_C4", "lookup_bytes")):
+                                      ("C4", 1000000, "seed", "seed_count_C4", "lookup_bytes")):      # C5: a launch is one wave of several, not scaled
     r = raw(os.path.join(G, "%s_full_%s.ncu-rep" % (tag, rep)))
     cj = os.path.join(G, "%s_counts_%s_%d.json" % (tag, wl, reads))
     if r is None or not os.path.exists(cj):
