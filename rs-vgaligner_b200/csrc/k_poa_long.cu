@@ -28,6 +28,7 @@ namespace vga {
 
 static const int PL_WARPS = 2;              // warps per CTA (7.8 KB of shared memory each)
 static const u64 LONG_POOL_CHUNK = 8192;    // trace words a warp takes from the pool per refill
+static const u64 LONG_OVF_CHUNK = 1u << 18;  // fused kernel: words an alignment takes from the overflow region at a time
 static const u64 LONG_ARENA_MIN = 4u << 20;  // fused kernel: smallest useful arena (words): a 10 kb alignment writes 3-4 M
 static const int LPAD = 8;                  // buffer index of column cbase (column cbase-1 .. are guards)
 static const int WIN = 1280;                // columns of the window (bands are at most 1024 + the odd block size slack)
@@ -173,8 +174,9 @@ __device__ __forceinline__ int long_pick_cr(i32 W) {
 
 // FUSED: every warp owns a private arena of the trace pool (arena_words from arena 0 of warp 0 on), fills an alignment into it and
 // traces it right away (lane 0; k_poa_trace.cuh) before it takes the next one — no waves, no traceback launches that leave the
-// machine to a few thousand threads, no host round trip between fill and traceback.  An alignment that does not fit the arena ends
-// as IT_RETRY_POOL and goes through the wave path afterwards.
+// machine to a few thousand threads, no host round trip between fill and traceback.  An alignment that outgrows its arena goes on
+// in a shared overflow region (a quarter of the pool, bump-allocated); only when that is exhausted it ends as IT_RETRY_POOL and goes
+// through the wave path afterwards.
 template <bool FUSED>
 __global__ void __launch_bounds__(PL_WARPS * 32, FUSED ? 12 : 12) poa_fill_long_kernel(DevIndex ix, PoaBuffers b, TraceBuffers tb, u64 arena_words) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
@@ -244,15 +246,15 @@ __global__ void __launch_bounds__(PL_WARPS * 32, FUSED ? 12 : 12) poa_fill_long_
             // pool space: one trace word per band cell, rows stored from an 8-column boundary (trace_col0)
             const u64 need = (u64)((W + (beg & 7) + 3) & ~3);
             if (status == VGA_ALN_OK && pool_cur + need > pool_end) {
-                if (FUSED) status = IT_RETRY_POOL;            // larger than the arena: the wave path takes it
-                else {
-                    unsigned long long got = 0;
-                    const u64 take = need > LONG_POOL_CHUNK ? need : LONG_POOL_CHUNK;
-                    if (lane == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
-                    got = __shfl_sync(FULLW, got, 0);
-                    if (got + take > b.pool_words) status = IT_RETRY_POOL;
-                    else { pool_cur = got; pool_end = got + take; }
-                }
+                // FUSED: the arena is full — the alignment goes on in chunks of the shared overflow region behind the arenas (the
+                // counter starts there); when that is exhausted too, the wave path takes the alignment
+                unsigned long long got = 0;
+                const u64 chunk = FUSED ? LONG_OVF_CHUNK : LONG_POOL_CHUNK;
+                const u64 take = need > chunk ? need : chunk;
+                if (lane == 0) got = atomicAdd(b.pool_ctr, (unsigned long long)take);
+                got = __shfl_sync(FULLW, got, 0);
+                if (got + take > b.pool_words) status = IT_RETRY_POOL;
+                else { pool_cur = got; pool_end = got + take; }
             }
             if (status != VGA_ALN_OK) break;
             u32* __restrict__ tr = b.pool + pool_cur + (beg & 7);
@@ -416,8 +418,11 @@ static int launch_long(const DevIndex& ix, const PoaBuffers& b, const TraceBuffe
     if (FUSED) {
         // one arena per resident warp; an alignment larger than its arena is left to the wave path (IT_RETRY_POOL).  Fewer, larger
         // arenas when the pool is small for the machine: at least LONG_ARENA_MIN words each
-        arena = (b.pool_words / (u64)(ctas * PL_WARPS)) & ~(u64)3;
-        while (arena < LONG_ARENA_MIN && ctas > 1) { ctas = (ctas + 1) / 2; arena = (b.pool_words / (u64)(ctas * PL_WARPS)) & ~(u64)3; }
+        const u64 arena_words_total = b.pool_words / 4 * 3;          // a quarter of the pool is the shared overflow region
+        arena = (arena_words_total / (u64)(ctas * PL_WARPS)) & ~(u64)3;
+        while (arena < LONG_ARENA_MIN && ctas > 1) { ctas = (ctas + 1) / 2; arena = (arena_words_total / (u64)(ctas * PL_WARPS)) & ~(u64)3; }
+        const unsigned long long ovf_base = (unsigned long long)arena * (u64)(ctas * PL_WARPS);
+        VGA_CUDA(cudaMemcpyAsync(b.pool_ctr, &ovf_base, 8, cudaMemcpyHostToDevice, st));
     }
     poa_fill_long_kernel<FUSED><<<(unsigned)ctas, PL_WARPS * 32, smem_bytes, st>>>(ix, b, tb, arena);
     return 1;

@@ -226,13 +226,18 @@ __global__ void item_sizes_kernel(const AlignItem* items, u32 n, u64* s0, u64* s
     s0[i] = it.S + 1; s1[i] = it.E; s2[i] = it.nrows; s3[i] = (u64)it.nrows + it.qlen + 2;
 }
 
+// s_out bit 31: the chain's anchors cover less than an eighth of the read — on long reads the mark of a chain through random k-mer
+// hits (reverse-strand reads), whose band will leave the 1024 columns of the warp kernels: such an alignment is started on the wide
+// kernel right away (a routing hint only: every class computes the same alignment)
 __global__ void item_bases_kernel(AlignItem* items, u32 n, const u64* o0, const u64* o1, const u64* o2, const u64* o3,
-                                  u32* nrows_out, u32* qlen_out, u32* s_out) {
+                                  const u64* chain_anchor_off, u32 k, u32* nrows_out, u32* qlen_out, u32* s_out) {
     u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     AlignItem& it = items[i];
     it.node_base = (u32)o0[i]; it.pred_base = (u32)o1[i]; it.row_base = (u32)o2[i]; it.out_base = (u32)o3[i];
-    nrows_out[i] = it.nrows; qlen_out[i] = it.qlen; s_out[i] = it.S;
+    const u64 n_anc = chain_anchor_off[it.chain + 1] - chain_anchor_off[it.chain];
+    const u32 sparse = n_anc * k * 8 < (u64)it.qlen ? 0x80000000u : 0u;
+    nrows_out[i] = it.nrows; qlen_out[i] = it.qlen; s_out[i] = it.S | sparse;
 }
 
 __global__ void item_status_kernel(const AlignItem* items, const u32* work, u32 n, u32* status) {
@@ -644,7 +649,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     tl_mark("sizes scanned");
     u32* d_nrows = w->b[B_RCNT].get<u32>(3ull * NI);
     item_bases_kernel<<<(NI + 255) / 256, 256, 0, st>>>(items, NI, szo, szo + (NI + 1), szo + 2ull * (NI + 1), szo + 3ull * (NI + 1),
-                                                        d_nrows, d_nrows + NI, d_nrows + 2ull * NI);
+                                                        cg.chain_anchor_off, dv.k, d_nrows, d_nrows + NI, d_nrows + 2ull * NI);
     c.launches++;
     // rows / read length / size class of every item go to the host now: the classification below runs on the host while
     // sub_fill and sub_rowmeta run on the device
@@ -731,13 +736,17 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             u64 et = 0, sr = 0, sq = 0, qm = 0;
             for (u32 i = i0; i < i1; i++) {
                 const i64 nrows = h_meta[i], qlen = h_meta[NI + i];
-                if (h_meta[2ull * NI + i] == 0) { est[i] = 0; key[i] = (u32)(NCLS * NB); h[key[i]]++; continue; }
+                if ((h_meta[2ull * NI + i] & 0x7fffffffu) == 0) { est[i] = 0; key[i] = (u32)(NCLS * NB); h[key[i]]++; continue; }
                 const i64 wband = P.wb + (i64)(P.wf * (float)qlen);
                 const i64 west = std::min<i64>(qlen + 1, 2 * wband + 1 + std::llabs(nrows - qlen) + 8);
                 // rows are stored from an 8-column boundary (trace_col0); no kernel computes a band wider than 1024 columns
                 est[i] = (u64)(nrows * (std::min<i64>(west, 1024) + 12));
                 if (qlen < 256) { if ((u64)qlen > qm) qm = (u64)qlen; sr += (u64)nrows; sq += (u64)qlen; }
-                const int ci = poa_class_for(qlen, nrows, west, P, pb.long_mode);
+                int ci = poa_class_for(qlen, nrows, west, P, pb.long_mode);
+                if (ci >= 3 && ci < 8 && qlen >= 2048 && (h_meta[2ull * NI + i] >> 31)) {
+                    ci = 8;                                                  // sparse chain on a long read: the wide kernel from the start
+                    est[i] = std::max<u64>(est[i], (u64)nrows * ((u64)qlen / 8 + 256));
+                }
                 et += est[i];
                 const int lb = 63 - __builtin_clzll(est[i] | 1);            // floor(log2)
                 key[i] = (u32)(ci * NB + (NB - 1 - std::min(lb, NB - 1)));
