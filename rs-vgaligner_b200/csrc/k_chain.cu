@@ -101,17 +101,17 @@ __device__ __forceinline__ double div1000(i32 r) {
 // reduction per anchor when the scores fit 25 bits, which they always do in the fused kernel).
 template <bool FUSED, bool INTDP>
 __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b, bool two_pass_on) {
-    __shared__ u32 s_q[CHAIN_WARPS][RING], s_tb[CHAIN_WARPS][RING], s_te[CHAIN_WARPS][RING];
+    __shared__ u32 s_q[INTDP ? 1 : CHAIN_WARPS][INTDP ? 1 : RING], s_tb[INTDP ? 1 : CHAIN_WARPS][INTDP ? 1 : RING], s_te[INTDP ? 1 : CHAIN_WARPS][INTDP ? 1 : RING];
+    __shared__ uint4 s_ring[INTDP ? CHAIN_WARPS : 1][INTDP ? RING : 1];      // INTDP: {query_begin, target_begin, target_end, score} of a staged anchor: one 16-byte load per predecessor
     __shared__ double s_f[INTDP ? 1 : CHAIN_WARPS][INTDP ? 1 : RING];
-    __shared__ i32 s_r[INTDP ? CHAIN_WARPS : 1][INTDP ? RING : 1];
 
     __shared__ unsigned long long s_key[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
     __shared__ u8 s_pd[FUSED ? CHAIN_WARPS : 1][FUSED ? CHAIN_SMAX : 1];
     const u32 lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
     const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u32 n_warps = (gridDim.x * blockDim.x) >> 5;
-    u32* rq = s_q[wl]; u32* rtb = s_tb[wl]; u32* rte = s_te[wl]; double* rf = s_f[INTDP ? 0 : wl];
-    i32* rri = s_r[INTDP ? wl : 0];
+    u32* rq = s_q[INTDP ? 0 : wl]; u32* rtb = s_tb[INTDP ? 0 : wl]; u32* rte = s_te[INTDP ? 0 : wl]; double* rf = s_f[INTDP ? 0 : wl];
+    uint4* ring = s_ring[INTDP ? wl : 0];
     unsigned long long* keys = s_key[FUSED ? wl : 0];
     // integer score of sorted anchor i: kept in the HIGH word of keys[i] (its te) once the anchor has been staged into the
     // ring (a block of 32 is staged before any score of that block is written), the low word (anchor id) stays
@@ -161,9 +161,8 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                 const u32 ii = first + lane;
                 if (ii < n) {
                     const u32 id = FUSED ? (u32)keys[ii] : b.sidx[base + ii];
-                    rq[ii % RING] = b.a_qb[base + id];
-                    rtb[ii % RING] = b.a_tb[base + id];
-                    rte[ii % RING] = FUSED ? ((u32)(keys[ii] >> 32) ^ 0x80000000u) : b.a_te[base + id];
+                    const u32 te = FUSED ? ((u32)(keys[ii] >> 32) ^ 0x80000000u) : b.a_te[base + id];
+                    ring[ii % RING] = make_uint4(b.a_qb[base + id], b.a_tb[base + id], te, 0u);
                 }
             };
             stage(0); stage(32);
@@ -172,11 +171,11 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
             bool v1 = false, v2 = false;                                 // operands of the anchor about to be scored
             i32 t1 = 0, t2 = 0, ra1 = 0, ra2 = 0;
             auto prefetch = [&](u32 ia) {                                // operands of anchor ia (its predecessors ia-2 .. are in the ring)
-                const u32 sa = ia % RING;
-                const u32 qb_b = rq[sa], tb_b = rtb[sa], te_b = rte[sa];
-                const u32 s1 = (ia - d1) % RING, s2 = (ia - d2) % RING;
+                const uint4 eb = ring[ia % RING];
+                const u32 qb_b = eb.x, tb_b = eb.y, te_b = eb.z;
                 auto one = [&](bool live, u32 sj, bool& v, i32& t, i32& ra) {
-                    const u32 qb_a = rq[sj], tb_a = rtb[sj], te_a = rte[sj];
+                    const uint4 ea = ring[sj];
+                    const u32 qb_a = ea.x, tb_a = ea.y, te_a = ea.z;
                     live = live && qb_a < qb_b && te_a < te_b && !(((tb_a ^ te_a) | (tb_a ^ tb_b) | (te_a ^ te_b)) >> 31);
                     const u32 ql = qb_b - qb_a;
                     const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
@@ -184,10 +183,10 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                     const u32 g = ql > tl ? ql - tl : tl - ql;
                     v = live && g <= b.max_gap;
                     t = (i32)(min(min(ql, tl), b.k) * 1000u) - __ldg(b.gapcost_i + min(g, b.max_gap));
-                    ra = rri[sj];
+                    ra = (i32)ea.w;
                 };
-                one(d1 <= b.bandwidth && d1 <= ia, s1, v1, t1, ra1);
-                one(d2 <= b.bandwidth && d2 <= ia, s2, v2, t2, ra2);
+                one(d1 <= b.bandwidth && d1 <= ia, (ia - d1) % RING, v1, t1, ra1);
+                one(d2 <= b.bandwidth && d2 <= ia, (ia - d2) % RING, v2, t2, ra2);
             };
             i32 r_prev = rk;
             for (u32 i = 0; i < n; i++) {
@@ -216,7 +215,7 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                 if (m > r_max) r_max = m;                                // :445-447 (all proposals)
                 r_prev = r_i;
                 if (lane == 0) {
-                    rri[i % RING] = r_i;
+                    ((i32*)&ring[i % RING])[3] = r_i;
                     b.f[base + i] = div1000(r_i);                        // :360-363
                     if (FUSED) { rr2[2 * i + 1] = r_i; pd[i] = p < 0 ? 0 : (u8)dmin; }
                     else b.pred[base + i] = p;
