@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
     u32 w = 0, nb = 0, S = 0, pred_base = 0, row_base = 0, nrows = 0;
     i32 qlen = 0, wband = 0, end0 = 0;
     const u8* __restrict__ q = nullptr;
-    u32 row = 0, s = 0, o = 0, meta = 0;
+    u32 row = 0, s = 0, o = 0, meta = 0, meta_next = 0;
     i32 beg = 0, end = -1, ppb = 0, ppe = -1, lpos = 0, rpos = 0, mxrow = 0;
     i32 ref = 0;                                    // CHK instances: the planes and trace words of a row hold score - ref (RowInfo.ref)
     i32 bdone = 0, nblocks_row = 1, rl = 0, rr = 0;
@@ -394,7 +394,8 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                     finish();
                 } else {
                     {   // band end of the virtual source row: max_remain of the first row + 1
-                        const i32 remain_src = (i32)(b.row_meta[row_base] >> 11) + 1;
+                        meta_next = b.row_meta[row_base];
+                        const i32 remain_src = (i32)(meta_next >> 11) + 1;
                         end0 = band_round_end0(imin(qlen, imax(0, qlen - remain_src) + wband), b.bgran_mask, qlen);
                     }
                     // selectors of the read: pair p = (block p / 4, word p % 4) holds columns 8*blk - 8 + word and + 4 (query base j-1)
@@ -408,11 +409,11 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 }
             }
         }
-        // ---- B: row prologue (groups that start a DP row).  The row record (sub_rowmeta_kernel) comes by a plain cached load
-        // that every lane of the group issues for the same address; the lines it will need are pulled into L1 a few dozen rows
-        // ahead by prefetches, which have no destination register.  (A register prefetch — load G rows ahead, consume later —
-        // stalls on the warp-wide scoreboard whenever ANOTHER group of the warp has just issued its own: 10 % of all stall
-        // samples of this kernel sat on that dependency, profiles/r02_pair_stalls.txt.)
+        // ---- B: row prologue (groups that start a DP row).  The row record (sub_rowmeta_kernel) comes by a cached load that every
+        // lane of the group issues for the same address, one row ahead; the lines it will need are pulled into L1 a few dozen
+        // rows ahead by prefetches, which have no destination register.  (Round 1 loaded G rows at a time and shuffled; the
+        // shuffle then waited on the warp-wide scoreboard for whatever load ANOTHER group of the warp had just issued: 10 % of
+        // all stall samples.  A load consumed in the same prologue waits just as long: profiles/r02_pair_stalls.txt, L426.)
         if (phase == PH_ROW) {
             if ((row & 31u) == 0 && gl == 0) {
                 const u32* nx = b.row_meta + row_base + row + 32;
@@ -420,7 +421,10 @@ __global__ void __launch_bounds__(PP_WARPS * 32, MINB) poa_fill_pair_kernel(DevI
                 if (row + 32 < nrows) asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
                 if (row + 64 < nrows) asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + 32));
             }
-            meta = __ldca(b.row_meta + row_base + row);
+            // one row ahead: the record of row + 1 is requested now and consumed by the next prologue of this group, at least one
+            // step body later (an L1 / L2 hit by then: 32 records per 128-byte line)
+            meta = meta_next;
+            if (row + 1 < nrows) meta_next = __ldca(b.row_meta + row_base + row + 1);
         }
         if (phase == PH_ROW) {
             const u32 base = meta & 0xffu, kind = (meta >> 8) & 3u;
