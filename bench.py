@@ -428,7 +428,8 @@ def gpu_record(G, name, wl, args):
     poa_ms, poa_launches = mean("ms_poa"), max(1, sumf(last, "poa_launches"))
     gcups = cells / (poa_ms * 1e-3) / 1e9 if poa_ms > 0 else 0.0
     gcups_peak = G.int32_peak / 17.0 / 1e9
-    kern = "poa_fill_seg_kernel / poa_fill_pair_kernel (short reads)" if wl["length"] < 246 else "poa_fill_long_kernel (long reads)"
+    kern = ("poa_fill_pair_kernel (16x2 fill, short reads)" if wl["length"] < 246 else
+            "poa_fill_long_kernel (fused fill + traceback per warp) + poa_fill_wide_kernel (bands beyond 1024 columns)")
     roof_poa = {"kernel": kern + ": all fill launches of a step", "bound": "int32_alu", "achieved": gcups, "peak": gcups_peak,
                 "unit": "GCUPS", "frac": gcups / gcups_peak if gcups_peak else None,
                 "traffic": per_unit("poa_fill") * (cells / poa_launches) if per_unit("poa_fill") else None, "traffic_source": traffic.get("source"),

@@ -175,6 +175,32 @@ def test_synthetic_long_reads(synth):
     assert (g.aln_status == vg.ALN_OK).sum() >= 12
 
 
+def test_long_reads_through_waves_instead_of_the_fused_kernel(synth, monkeypatch):
+    """VGA_POA_FUSED=0: the shared-memory long-read kernel as fill waves + traceback launches (the path pool retries of the fused
+    per-warp kernel fall back to), with the pool capped so that several waves are needed."""
+    monkeypatch.setenv("VGA_POA_LONG", "1")
+    monkeypatch.setenv("VGA_POA_FUSED", "0")
+    reads = vg.simulate_reads(synth, 20, 10000, 0.04, 0.03, 0.03, 0.1, 17)
+    g, o = both(synth, reads)
+    check_all(g, o)
+    monkeypatch.setenv("VGA_POOL_MAX_WORDS", str(148 * 64 * 8192 + 30_000_000))
+    g2, _ = both(synth, reads)
+    check_all(g2, o)
+    assert g2.stats["poa_launches"] > g.stats["poa_launches"]
+
+
+def test_fused_long_read_kernel_with_a_small_pool(synth, monkeypatch):
+    """The fused fill + traceback kernel when arenas are small: alignments outgrow their arena into the shared overflow region,
+    and when that is exhausted they come back as pool retries and take the wave path — same results."""
+    monkeypatch.setenv("VGA_POA_LONG", "1")
+    reads = vg.simulate_reads(synth, 40, 10000, 0.04, 0.03, 0.03, 0.1, 19)
+    g, o = both(synth, reads)
+    check_all(g, o)
+    monkeypatch.setenv("VGA_POOL_MAX_WORDS", str(148 * 64 * 8192 + 60_000_000))
+    g2, _ = both(synth, reads)
+    check_all(g2, o)
+
+
 @pytest.mark.parametrize("family", ["0", "1"])
 def test_long_read_kernel_families(synth, monkeypatch, family):
     """Both fill kernels for alignments outside the short-read classes — register-resident SLIDE instances (0) and the
