@@ -271,7 +271,8 @@ def gpu_record(G, name, wl, args):
     t_sim = time.time() - t0
     n_reads, n_bases = reads.n, int(reads.offsets[-1])
     batch = max(1, min(args.batch_reads or wl["batch"], n_reads))
-    cuts = list(range(0, n_reads, batch)) + [n_reads]
+    n_calls = (n_reads + batch - 1) // batch            # equal calls: a short last call would run the device half empty
+    cuts = [n_reads * i // n_calls for i in range(n_calls + 1)]
     log("%s rank %d: %d reads [%d, %d), %d calls per step, index %.1f s, reads %.1f s" % (name, rank, n_reads, lo, hi, len(cuts) - 1, t_index, t_sim))
 
     h_seqs_pageable = np.ascontiguousarray(reads.seqs)
