@@ -10,7 +10,7 @@ PKG       := rs-vgaligner_b200
 CSRC      := $(PKG)/csrc
 HOST      := $(PKG)/host
 BUILD     := build
-GPU_OBJS  := $(BUILD)/vga_multi.o $(BUILD)/vga_index.o $(BUILD)/vga_api.o $(BUILD)/k_seed.o $(BUILD)/k_chain.o $(BUILD)/k_subgraph.o $(BUILD)/k_poa.o $(BUILD)/k_poa_short.o $(BUILD)/k_poa_pair.o $(BUILD)/k_poa_long.o $(BUILD)/k_poa_wide.o $(BUILD)/k_index_build.o
+GPU_OBJS  := $(BUILD)/vga_multi.o $(BUILD)/vga_index.o $(BUILD)/vga_api.o $(BUILD)/k_seed.o $(BUILD)/k_chain.o $(BUILD)/k_subgraph.o $(BUILD)/k_poa.o $(BUILD)/k_poa_short.o $(BUILD)/k_poa_pair.o $(BUILD)/k_poa_long.o $(BUILD)/k_poa_wide.o $(BUILD)/k_index_build.o $(BUILD)/vga_noalloc.o
 
 all: host oracle gpu cli
 

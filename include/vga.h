@@ -195,6 +195,16 @@ int vga_map_batch(vga_index_t* ix, const char* seqs, const uint64_t* seq_off, ui
 /* Same with the reads already resident on the index's device 0 (device-timed benchmark leg). */
 int vga_map_batch_device(vga_index_t* ix, const char* dev_seqs, const uint64_t* dev_seq_off, uint32_t n_reads,
                          uint64_t n_bases, const VgaParams* params, vga_results_t** out);
+/* Anchors per read (the K1 counting stage; equal to VgaResultsView.n_anchors of vga_map_batch) WITHOUT any device allocation.
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  Reads and offsets are resident on the index's device, and so
+ * is the output dev_n_anchors[n_reads]; n_bases = dev_seq_off[n_reads] - dev_seq_off[0].  The stage's scratch is a fixed device
+ * array of VGA_NOALLOC_SCRATCH_BYTES inside the library (held by every GPU that loads it, until exit): a call needs
+ * 8 * (n_reads + 1) + 8 * n_bases bytes of it and is rejected with VGA_ERR_INVALID beyond that.  Every call shares the array:
+ * calls that overlap on one GPU race (calls of one process are serialised by the library).  Blocking. */
+#define VGA_NOALLOC_SCRATCH_BYTES (64u << 20)
+int vga_seed_count_noalloc(vga_index_t* ix, const char* dev_seqs, const uint64_t* dev_seq_off, uint32_t n_reads,
+                           uint64_t n_bases, uint32_t* dev_n_anchors);
 int vga_results_view(const vga_results_t* r, VgaResultsView* view);
 int vga_results_stats(const vga_results_t* r, VgaStats* stats);
 int vga_results_free(vga_results_t* r);

@@ -66,7 +66,7 @@ GPU_SYMBOLS = ["vga_init", "vga_device_count", "vga_index_upload", "vga_index_fr
                "vga_index_image_copy_to_device", "vga_index_import_device", "vga_default_params", "vga_map_batch",
                "vga_map_batch_device", "vga_results_view", "vga_results_stats", "vga_results_free",
                "vga_last_error", "vga_measure_int32_peak", "vga_comm_unique_id", "vga_index_broadcast", "vga_index_build_device",
-               "vga_index_build_view", "vga_index_build_free", "vga_index_upload_ex"]
+               "vga_index_build_view", "vga_index_build_free", "vga_index_upload_ex", "vga_seed_count_noalloc"]
 
 HASH_FN = C.CFUNCTYPE(C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p)     # vgah_hash_fn: (kmer bytes, k, user) -> key hash
 
@@ -151,6 +151,7 @@ def gpu_lib():
                                     C.POINTER(C.c_void_p)]
         L.vga_map_batch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64,
                                            C.POINTER(VgaParams), C.POINTER(C.c_void_p)]
+        L.vga_seed_count_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p]
         L.vga_results_view.argtypes = [C.c_void_p, C.POINTER(VgaResultsView)]
         L.vga_results_stats.argtypes = [C.c_void_p, C.POINTER(VgaStats)]
         L.vga_results_free.argtypes = [C.c_void_p]
