@@ -83,21 +83,22 @@ class ClockSampler(threading.Thread):
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, gpu):
+    def __init__(self, gpu, n_gpus=1):
+        """gpu: this rank's local ordinal; n_gpus > 1 (rank 0 of a multi-rank run): sample ALL local GPUs round-robin from this one
+        thread — eight ranks each polling NVML at 50 Hz contend with every rank's CUDA calls for the driver's locks."""
         super().__init__(daemon=True)
         self.gpu, self.rows, self.stop_flag = gpu, [], False
-        self.nvml = None
+        self.nvml, self.handles, self.turn, self.max_mhz = None, [], 0, {}
         try:
             import pynvml
             pynvml.nvmlInit()
-            # LOCAL_RANK indexes the visible devices; honour CUDA_VISIBLE_DEVICES when it lists ordinals
+            # local ordinals index the visible devices; honour CUDA_VISIBLE_DEVICES when it lists ordinals
             vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            idx = gpu
-            if vis:
-                parts = [x.strip() for x in vis.split(",") if x.strip()]
-                if gpu < len(parts) and parts[gpu].isdigit():
-                    idx = int(parts[gpu])
-            self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            parts = [x.strip() for x in vis.split(",") if x.strip()] if vis else []
+            for g in (range(n_gpus) if n_gpus > 1 else [gpu]):
+                idx = int(parts[g]) if g < len(parts) and parts[g].isdigit() else g
+                self.handles.append(pynvml.nvmlDeviceGetHandleByIndex(idx))
+            self.handle = self.handles[0]
             self.nvml = pynvml
         except Exception:
             self.nvml = None
@@ -105,8 +106,12 @@ class ClockSampler(threading.Thread):
     def sample(self):
         if self.nvml is not None:
             n = self.nvml
+            self.turn = (self.turn + 1) % len(self.handles)
+            self.handle = self.handles[self.turn]
             sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
-            mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+            if self.turn not in self.max_mhz:
+                self.max_mhz[self.turn] = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+            mx = self.max_mhz[self.turn]
             pw = n.nvmlDeviceGetPowerUsage(self.handle) / 1000.0
             r = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
                 else n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
@@ -134,8 +139,8 @@ class ClockSampler(threading.Thread):
         reasons = sorted({self.NAMES[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
         pw = [float(r[2]) for r in self.rows if len(r) > 2]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.rows), "power_w_max": max(pw) if pw else None,
-                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
+                "samples": len(self.rows), "power_w_max": max(pw) if pw else None, "gpus_sampled": max(1, len(self.handles)),
+                "sm_min_mhz": sm[0] if sm else None, "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 class Sub:
@@ -339,8 +344,9 @@ def gpu_record(G, name, wl, args):
         return per_step, walls
 
     # ---- device-resident leg (value)
-    sampler = ClockSampler(G.local_rank)
-    sampler.start()
+    sampler = ClockSampler(G.local_rank, world) if rank == 0 and not os.environ.get("VGA_BENCH_NO_SAMPLER") else None     # rank 0 watches every GPU of the box
+    if sampler:
+        sampler.start()
     t_wall0 = time.perf_counter()
     dev_steps, dev_walls = leg(call_device, args.steps, args.warmup)
     t_wall = time.perf_counter() - t_wall0
@@ -353,7 +359,7 @@ def gpu_record(G, name, wl, args):
         pin_steps, pin_walls = leg(call_host(h_seqs.data_ptr(), h_offs.data_ptr()), e2e_steps, max(1, min(args.warmup, 2)))
         pg_steps, pg_walls = leg(call_host(h_seqs_pageable.ctypes.data, h_offs_np.ctypes.data), e2e_steps, 1)
         e2e = (sum(pin_walls), sum(pg_walls), e2e_steps, pin_steps)
-    clocks = sampler.summary()
+    clocks = sampler.summary() if sampler else None
 
     # ---- one batch end to end INCLUDING both GAF texts (bounded: one batch)
     gaf = None
