@@ -36,7 +36,7 @@ GRAPHS = os.path.join(ROOT, "tests", "golden", "graphs")
 WORKLOADS = {
     "C2": dict(graph="2-DRB1-3123.gfa", k=11, reads=100000, length=150, err=(0.01, 0.0005, 0.0005), seed=77, batch=100000,
                desc="HLA-zoo DRB1-3123 graph, k=11, 100k simulated 150bp reads"),
-    "C3a": dict(graph="17-DRB1-3123-smooth.gfa", k=11, reads=1000000, length=150, err=(0.01, 0.0005, 0.0005), seed=77, batch=125000,
+    "C3a": dict(graph="17-DRB1-3123-smooth.gfa", k=11, reads=1000000, length=150, err=(0.01, 0.0005, 0.0005), seed=77, batch=1000000,
                 desc="HLA-zoo 17-DRB1-3123-smooth, k=11, 1M simulated 150bp reads"),
     "C3b": dict(graph="19-MICB-4227-smooth.gfa", k=11, reads=1000000, length=150, err=(0.01, 0.0005, 0.0005), seed=77, batch=250000,
                 desc="HLA-zoo 19-MICB-4227-smooth, k=11, 1M simulated 150bp reads"),
