@@ -170,40 +170,57 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
             const u32 d1 = lane + 1, d2 = lane + 33;
             bool v1 = false, v2 = false;                                 // operands of the anchor about to be scored
             i32 t1 = 0, t2 = 0, ra1 = 0, ra2 = 0;
-            auto prefetch = [&](u32 ia) {                                // operands of anchor ia (its predecessors ia-2 .. are in the ring)
+            i32 far_ub = INT_MIN;                                        // warp-uniform: best predecessor score at distances 33 .. bandwidth
+            auto one = [&](u32 ia, bool live, u32 sj, bool& v, i32& t, i32& ra) {
                 const uint4 eb = ring[ia % RING];
                 const u32 qb_b = eb.x, tb_b = eb.y, te_b = eb.z;
-                auto one = [&](bool live, u32 sj, bool& v, i32& t, i32& ra) {
-                    const uint4 ea = ring[sj];
-                    const u32 qb_a = ea.x, tb_a = ea.y, te_a = ea.z;
-                    live = live && qb_a < qb_b && te_a < te_b && !(((tb_a ^ te_a) | (tb_a ^ tb_b) | (te_a ^ te_b)) >> 31);
-                    const u32 ql = qb_b - qb_a;
-                    const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
-                    const u32 tl = min(tbd, te_b - te_a);
-                    const u32 g = ql > tl ? ql - tl : tl - ql;
-                    v = live && g <= b.max_gap;
-                    t = (i32)(min(min(ql, tl), b.k) * 1000u) - __ldg(b.gapcost_i + min(g, b.max_gap));
-                    ra = (i32)ea.w;
-                };
-                one(d1 <= b.bandwidth && d1 <= ia, (ia - d1) % RING, v1, t1, ra1);
-                one(d2 <= b.bandwidth && d2 <= ia, (ia - d2) % RING, v2, t2, ra2);
+                const uint4 ea = ring[sj];
+                const u32 qb_a = ea.x, tb_a = ea.y, te_a = ea.z;
+                live = live && qb_a < qb_b && te_a < te_b && !(((tb_a ^ te_a) | (tb_a ^ tb_b) | (te_a ^ te_b)) >> 31);
+                const u32 ql = qb_b - qb_a;
+                const u32 tbd = tb_b > tb_a ? tb_b - tb_a : tb_a - tb_b;
+                const u32 tl = min(tbd, te_b - te_a);
+                const u32 g = ql > tl ? ql - tl : tl - ql;
+                v = live && g <= b.max_gap;
+                t = (i32)(min(min(ql, tl), b.k) * 1000u) - __ldg(b.gapcost_i + min(g, b.max_gap));
+                ra = (i32)ea.w;
+            };
+            // The far half of the window (distances 33 .. bandwidth) is only BOUNDED ahead of time: a pair scores at most its
+            // predecessor's score + 1000 k (gap costs are >= 0), and a far predecessor replaces a near one only with a strictly
+            // higher score (ties keep the nearest).  In a collinear run of anchors the near half always wins, so the far pairs are
+            // evaluated only when the bound says they could matter (chain starts, gaps in the run).
+            auto prefetch = [&](u32 ia) {                                // operands of anchor ia (its predecessors ia-2 .. are in the ring)
+                one(ia, d1 <= b.bandwidth && d1 <= ia, (ia - d1) % RING, v1, t1, ra1);
+                const bool live2 = d2 <= b.bandwidth && d2 <= ia;
+                far_ub = __reduce_max_sync(FULLM, live2 ? ((const i32*)&ring[(ia - d2) % RING])[3] : INT_MIN);
             };
             i32 r_prev = rk;
             for (u32 i = 0; i < n; i++) {
                 if (lane == 0) ra1 = r_prev;                             // predecessor i-1: just computed
-                const i32 a1 = v1 ? ra1 + t1 : INT_MIN, a2 = v2 ? ra2 + t2 : INT_MIN;
+                const i32 a1 = v1 ? ra1 + t1 : INT_MIN;
                 i32 m;
                 u32 dmin;
                 if (FUSED) {
                     // |score| < 2^25 here (at most CHAIN_SMAX anchors of at most 32 bases, gap costs below 2^21): the score and the
                     // nearest-predecessor rule (ties keep the smallest distance) travel as ONE key through one reduction
-                    const i32 k1 = v1 ? a1 * 64 + (64 - (i32)d1) : INT_MIN, k2 = v2 ? a2 * 64 + (64 - (i32)d2) : INT_MIN;
-                    const i32 km = __reduce_max_sync(FULLM, max(k1, k2));
+                    const i32 k1 = v1 ? a1 * 64 + (64 - (i32)d1) : INT_MIN;
+                    i32 km = __reduce_max_sync(FULLM, k1);
+                    if (far_ub != INT_MIN && (km == INT_MIN || far_ub + rk > (km >> 6))) {          // warp-uniform
+                        one(i, d2 <= b.bandwidth && d2 <= i, (i - d2) % RING, v2, t2, ra2);
+                        const i32 k2 = v2 ? (ra2 + t2) * 64 + (64 - (i32)d2) : INT_MIN;
+                        km = max(km, __reduce_max_sync(FULLM, k2));
+                    }
                     m = km == INT_MIN ? INT_MIN : (km >> 6);
                     dmin = 64u - (u32)(km & 63);
                 } else {
+                    i32 a2 = INT_MIN;
+                    const i32 m1 = __reduce_max_sync(FULLM, a1);
+                    if (far_ub != INT_MIN && (m1 == INT_MIN || (i64)far_ub + rk > (i64)m1)) {         // warp-uniform
+                        one(i, d2 <= b.bandwidth && d2 <= i, (i - d2) % RING, v2, t2, ra2);
+                        a2 = v2 ? ra2 + t2 : INT_MIN;
+                    }
                     const i32 best = max(a1, a2);
-                    m = __reduce_max_sync(FULLM, best);
+                    m = max(m1, __reduce_max_sync(FULLM, a2));
                     dmin = __reduce_min_sync(FULLM, best == m && best != INT_MIN ? (a1 == m && v1 ? d1 : d2) : 0x7fffffffu);
                 }
                 // operands of anchor i+1 while the reduction is in flight (its own coordinates were staged a block ahead)
@@ -216,13 +233,14 @@ __global__ void __launch_bounds__(CHAIN_WARPS * 32) chain_kernel(ChainBuffers b,
                 r_prev = r_i;
                 if (lane == 0) {
                     ((i32*)&ring[i % RING])[3] = r_i;
-                    b.f[base + i] = div1000(r_i);                        // :360-363
-                    if (FUSED) { rr2[2 * i + 1] = r_i; pd[i] = p < 0 ? 0 : (u8)dmin; }
-                    else b.pred[base + i] = p;
+                    if (FUSED) { rr2[2 * i + 1] = r_i; pd[i] = p < 0 ? 0 : (u8)dmin; }       // the f64 scores follow after the loop, 32 at a time
+                    else { b.f[base + i] = div1000(r_i); b.pred[base + i] = p; }            // :360-363
                     if (b.pred_dbg) b.pred_dbg[base + i] = p < 0 ? -1 : (i32)(FUSED ? (u32)keys[p] : b.sidx[base + p]);
                 }
                 __syncwarp();
             }
+            if (FUSED)
+                for (u32 i = lane; i < n; i += 32) b.f[base + i] = div1000(rr2[2 * i + 1]);     // :360-363
         }
         if (!INTDP)
         for (u32 i = 0; i < n; i++) {

@@ -108,8 +108,9 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
     // ---- sweep 2: H, E', trace words, row maximum keyed by column, smallest reachable H
     i32 kl = INT_MIN, kr = INT_MIN;          // max of (H, -t) and (H, t): lane maximum with its leftmost / rightmost column
     u32 lminu = 0xffffffffu;                 // min of H + 2^27 as unsigned: unreachable cells (H <= -2^27) wrap to huge values
-    i32 hprev_new = 0;                       // new H of column t-1
-    u32 w0 = 0; i32 f1_0 = 0, f2_0 = 0;      // column 0: its F fields need the left lane's last new H
+    i32 hprev_new = 1 << 29;                 // new H of column t-1; column 0 of the lane: so large that both F fields come out as 0 —
+                                             // they are relative to the LEFT lane's last new H and are added after the loop
+    u32 w0 = 0;
     u32* const trl = tr + lane * CR;
     {
         i32 hd = hleft;
@@ -130,17 +131,15 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
             const i32 d2 = __viaddmax_s32(x2, K.o2 - h, 0);
             u32 hi = (u32)d2 * 8u + (u32)d1;
             const u32 dnew = hi;
-            if (t > 0) {
-                hi = (u32)__viaddmax_s32(f1, 1 + K.oe1 - hprev_new, 0) * 256u + hi;
-                hi = (u32)__viaddmax_s32(f2, 1 + K.oe2 - hprev_new, 0) * 2048u + hi;
-            }
+            hi = (u32)__viaddmax_s32(f1, 1 + K.oe1 - hprev_new, 0) * 256u + hi;
+            hi = (u32)__viaddmax_s32(f2, 1 + K.oe2 - hprev_new, 0) * 2048u + hi;
             const i32 hrel = imax(h - ref, -32768);
             const u32 wd = __byte_perm((u32)hrel, hi, 0x5410);
-            if (t == 0) { w0 = wd; f1_0 = f1; f2_0 = f2; }
+            if (t == 0) w0 = wd;
             hprev_new = h;
             sh[t] = h;
             sd[t] = (u8)dnew;
-            if (t > 0) trl[t] = wd;
+            trl[t] = wd;                                             // column 0 is stored again below, with its F fields
             const i32 hk = hrel * 64;                                // the row maximum is far above ref - 32768
             kl = imax(kl, hk + 63 - t);
             kr = imax(kr, hk + t);
@@ -149,6 +148,7 @@ __device__ __forceinline__ LongRowOut long_row(const LongConst& K, u32 lane, i32
     }
     {   // F fields of the lane's first column: relative to the left lane's last H
         const i32 hl = __shfl_up_sync(FULLW, hprev_new, 1);
+        const i32 f1_0 = imax(cin1, POA_DEEP), f2_0 = imax(cin2, POA_DEEP);     // F of column 0: the carry, no lane-local part yet
         if (lane > 0) w0 += ((u32)imax(f1_0 + 1 + K.oe1 - hl, 0) << 24) + ((u32)imax(f2_0 + 1 + K.oe2 - hl, 0) << 27);
         if (n > 0) trl[0] = w0;
     }
