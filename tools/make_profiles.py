@@ -45,7 +45,10 @@ traffic = {"source": "ncu --set full captures of tools/gpu_evidence.sh %s, tree 
            "dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel on the named workload size, and the algorithmic units of "
            "that same launch (cells / lookup bytes from a bench run with the same --reads): bench.py scales bytes per unit to its own launches"}
 for wl, reads, key, rep, unit_key in (("C4", 250000, "poa_fill", "pair_C4", "poa_cells"), ("C2", 100000, "poa_fill", "pair_C2", "poa_cells"),
-                                      ("C4", 1000000, "seed", "seed_count_C4", "lookup_bytes")):      # C5: a launch is one wave of several, not scaled
+                                      ("C4", 1000000, "seed", "seed_count_C4", "lookup_bytes"),
+                                      # C5: the fused long-read kernel is ONE launch per call; the call's cell count also holds the few
+                                      # alignments that end on the wide kernel, so bytes per cell come out slightly low
+                                      ("C5", 12500, "poa_fill", "long_C5", "poa_cells")):
     r = raw(os.path.join(G, "%s_full_%s.ncu-rep" % (tag, rep)))
     cj = os.path.join(G, "%s_counts_%s_%d.json" % (tag, wl, reads))
     if r is None or not os.path.exists(cj):
@@ -72,5 +75,7 @@ for wl, reads, key, rep, unit_key in (("C4", 250000, "poa_fill", "pair_C4", "poa
     e[key + "_kernel"] = r.get("Kernel Name")
     e[key + "_units_in_launch"] = units
     e[key + "_note"] = "%s on %s with %d reads in one call: %.3f GB read + %.3f GB written; %s = %d" % (rep, wl, reads, rd / 1e9, wr / 1e9, unit_key, units)
+    if wl == "C5":
+        e[key + "_note"] += " (cells of the whole call: the fused kernel's launch plus the alignments that moved on to the wide kernel)"
 json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
 print(json.dumps(traffic, indent=1))
