@@ -406,6 +406,8 @@ def gpu_record(G, name, wl, args):
     ms_dev_max, e2e_pin_max, e2e_pg_max = float(red[0]), float(red[1]), float(red[2])
     total_reads, total_aligned = float(tot[0]), float(tot[1])
     if rank != 0:
+        if not args.no_sharded:
+            G.keep.append((None, name, wl, ix, gix, batch))     # this rank's part of the sharded leg (after every record is complete)
         return None
 
     K = args.steps
@@ -491,8 +493,92 @@ def gpu_record(G, name, wl, args):
         g.free()
         if bad:
             log("PARITY FAILURE on %s: %s differ from the oracle" % (name, bad))
-    ix.free_device()
+    if world > 1 and not args.no_sharded:
+        G.keep.append((rec, name, wl, ix, gix, batch))          # the sharded leg runs after every record is complete
+    else:
+        ix.free_device()
     return rec
+
+
+def pack_results(vg, L, outs):
+    """Every result array of the calls of one shard as ONE byte buffer (what a rank ships to the process that owns the output)."""
+    import ctypes as C
+
+    import numpy as np
+    parts = []
+    u8 = C.POINTER(C.c_uint8)
+
+    def raw(ptr, count, dt):
+        nb = int(count) * np.dtype(dt).itemsize
+        return np.ctypeslib.as_array(C.cast(ptr, u8), shape=(nb,)) if nb and ptr else np.zeros(0, np.uint8)
+
+    for out in outs:
+        v = vg.VgaResultsView()
+        L.vga_results_view(out, C.byref(v))
+        n, c, m = v.n_reads, v.n_chains, v.n_chain_anchors
+        size = {"n": n, "n+1": n + 1, "c+1": c + 1, "m": m}
+        n_path = int(v.aln_path_off[n]) if n else 0
+        n_runs = int(v.aln_run_off[n]) if n else 0
+        parts.append(np.array([n, c, m, n_path, n_runs], dtype=np.uint64).view(np.uint8))
+        for fname, (sz, dt) in vg._FIELDS.items():
+            parts.append(raw(getattr(v, fname), size[sz], dt))
+        parts.append(raw(v.aln_path, n_path, np.uint64))
+        parts.append(raw(v.aln_runs, n_runs, np.uint32))
+    return np.concatenate(parts) if parts else np.zeros(0, np.uint8)
+
+
+def sharded_leg(G, name, wl, ix, gix, batch, args):
+    """ONE process owns the reads and wants every result array back (what `vgaligner map` is): rank 0 holds the whole read set, scatters
+    contiguous shards (host -> device -> NCCL -> device -> host), every rank maps its shard from host buffers through vga_map_batch,
+    and the packed result arrays are gathered on rank 0.  One pass, caller's clock, barriers between the phases."""
+    import ctypes as C
+    import importlib
+
+    import torch
+    import torch.distributed as dist
+    shards = importlib.import_module("rs_vgaligner_b200.shards")
+    vg, L, dev, rank, world = G.vg, G.L, G.dev, G.rank, G.world
+    total = wl["reads"]
+
+    def barrier():
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    t0 = time.perf_counter()
+    whole = vg.simulate_reads_mt(ix, total, wl["length"], *wl["err"], 0.1, wl["seed"], first_id=0) if rank == 0 else None
+    t_sim = time.perf_counter() - t0
+    params = vg.default_params()
+    barrier()
+    t0 = time.perf_counter()
+    mine = shards.scatter_reads(whole, rank, world, dist, device=dev, with_names=False)
+    barrier()
+    t1 = time.perf_counter()
+    n_calls = max(1, (mine.n + batch - 1) // batch)
+    cuts = [mine.n * i // n_calls for i in range(n_calls + 1)]
+    outs = []
+    for i in range(n_calls):
+        out = C.c_void_p()
+        rc = L.vga_map_batch(gix, C.c_void_p(mine.seqs.ctypes.data), C.c_void_p(mine.offsets.ctypes.data + 8 * cuts[i]), cuts[i + 1] - cuts[i],
+                             C.byref(params), C.byref(out))
+        if rc != 0:
+            raise RuntimeError("vga_map_batch: " + L.vga_last_error().decode())
+        outs.append(out)
+    barrier()
+    t2 = time.perf_counter()
+    packed = pack_results(vg, L, outs)
+    t_pack = time.perf_counter() - t2
+    got = shards.gather_bytes(packed, rank, world, dist, device=dev)
+    barrier()
+    t3 = time.perf_counter()
+    for out in outs:
+        L.vga_results_free(out)
+    if rank != 0:
+        return None
+    return {"value": total / (t3 - t0), "unit": "reads/s", "scatter_s": t1 - t0, "map_s": t2 - t1, "gather_s": t3 - t2, "pack_s_rank0": t_pack,
+            "scatter_bytes": int(whole.offsets[-1]) + 8 * (total + world), "gather_bytes": int(sum(g.size for g in got)),
+            "read_simulation_s_rank0": t_sim, "passes": 1,
+            "what": "rank 0 owns all reads: scatter of the shards + vga_map_batch on every rank (pageable host buffers) + gather of every result "
+                    "array on rank 0, caller's clock; the limiter is the phase with the largest share"}
 
 
 def main():
@@ -511,6 +597,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-gaf", action="store_true")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the scatter + map + gather leg of a multi-rank run (e2e_sharded)")
+    ap.add_argument("--sharded-timeout", type=float, default=240.0, help="seconds after which the sharded leg is abandoned and the line printed without it")
     ap.add_argument("--no-index-build", action="store_true", help="skip the GPU index build measurement of the setup section")
     args = ap.parse_args()
 
@@ -559,13 +647,41 @@ def main():
         raise SystemExit("vga_init: " + G.L.vga_last_error().decode())
     G.int32_peak = vg.measure_int32_peak() if rank == 0 else 0.0
 
+    G.keep = []
     recs = [gpu_record(G, n, w, args) for n, w in zip(names, wls)]
-    if rank == 0:
+
+    def build_line():
         line = dict(base)
         line.update(recs[0])
         if len(recs) > 1:
             line["long_reads"] = recs[1]
             line["config"]["also_measured"] = recs[1]["config"]["workload"] + " (record under long_reads)"
+        return line
+
+    if G.keep:
+        # every record is complete: the sharded leg may not take the line with it if a rank falls out of step
+        def give_up():
+            log("sharded leg: no end after %.0f s, printing the line without it" % args.sharded_timeout)
+            if rank == 0:
+                for r in recs:
+                    r.setdefault("e2e_sharded", {"error": "abandoned after %.0f s" % args.sharded_timeout})
+                emit(build_line())
+            os._exit(0)
+        timer = threading.Timer(args.sharded_timeout, give_up)
+        timer.daemon = True
+        timer.start()
+        for rec, n, w, ix, gix, batch in G.keep:
+            try:
+                res = sharded_leg(G, n, w, ix, gix, batch, args)
+            except Exception as e:           # a rank that fails here leaves the others waiting: the timer ends the run
+                log("sharded leg of %s failed on rank %d: %r" % (n, rank, e))
+                res = {"error": repr(e)}
+            if rank == 0:
+                rec["e2e_sharded"] = res
+            ix.free_device()
+        timer.cancel()
+    if rank == 0:
+        line = build_line()
         emit(line)
         bad = [r["config"]["workload"] for r in recs if r.get("parity_sample") and not r["parity_sample"]["equal"]]
         if bad:

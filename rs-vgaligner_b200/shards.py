@@ -34,17 +34,18 @@ class ReadShard:
         return self.seqs[int(self.offsets[i]):int(self.offsets[i + 1])].tobytes().decode()
 
 
-def shard_reads(reads, rank, world):
-    """The reads rank `rank` of `world` maps, rebased to offset 0."""
+def shard_reads(reads, rank, world, with_names=True):
+    """The reads rank `rank` of `world` maps, rebased to offset 0.  with_names=False leaves the (lazily built) name list of a
+    simulated set of millions of reads alone."""
     b = shard_bounds(reads.n, world)
     lo, hi = b[rank], b[rank + 1]
     o = np.asarray(reads.offsets[lo:hi + 1], dtype=np.uint64)
     base = int(o[0]) if len(o) else 0
     seqs = np.asarray(reads.seqs[base:int(o[-1])] if len(o) else np.zeros(0, np.uint8))
-    return ReadShard(seqs, o - np.uint64(base), list(reads.names[lo:hi]) if reads.names else None)
+    return ReadShard(seqs, o - np.uint64(base), list(reads.names[lo:hi]) if with_names and reads.names else None)
 
 
-def scatter_reads(reads, rank, world, dist, device=None, src=0):
+def scatter_reads(reads, rank, world, dist, device=None, src=0, with_names=True):
     """Rank `src` holds `reads` (others pass None); every rank returns its shard.
 
     Point-to-point sends, two tensors per shard (bytes, offsets); names stay on `src` (only the GAF
@@ -52,12 +53,12 @@ def scatter_reads(reads, rank, world, dist, device=None, src=0):
     import torch
     dev = device if device is not None else torch.device("cpu")
     if world == 1:
-        return shard_reads(reads, 0, 1)
+        return shard_reads(reads, 0, 1, with_names)
     mine = None
     meta = torch.zeros(2, dtype=torch.int64, device=dev)
     for r in range(world):
         if rank == src:
-            s = shard_reads(reads, r, world)
+            s = shard_reads(reads, r, world, with_names)
             if r == src:
                 mine = s
                 continue
@@ -96,3 +97,27 @@ def gather_text(text, rank, world, dist, dst=0):
     parts = [None] * world if rank == dst else None
     dist.gather_object(text, parts, dst=dst)
     return "".join(parts) if rank == dst else None
+
+
+def gather_bytes(buf, rank, world, dist, device=None, dst=0):
+    """Every rank contributes a uint8 numpy array (its packed result arrays); `dst` returns all of them in rank order,
+    the other ranks None.  Sizes travel by one all_gather, payloads point to point."""
+    import torch
+    if world == 1:
+        return [buf]
+    dev = device if device is not None else torch.device("cpu")
+    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(sizes, torch.tensor([buf.size], dtype=torch.int64, device=dev))
+    if rank != dst:
+        dist.send(torch.from_numpy(buf).to(dev) if buf.size else torch.zeros(1, dtype=torch.uint8, device=dev), dst)
+        return None
+    out = []
+    for r in range(world):
+        if r == dst:
+            out.append(buf)
+            continue
+        n = int(sizes[r].item())
+        t = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
+        dist.recv(t, r)
+        out.append(t.cpu().numpy()[:n])
+    return out

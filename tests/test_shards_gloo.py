@@ -39,6 +39,16 @@ img = shards.broadcast_image(img, rank, dist)
 assert img.numel() == 100003 and int(img[777]) == 777 %% 256 and int(img[-1]) == 100002 %% 256
 
 mine = shards.scatter_reads(reads, rank, world, dist)
+again = shards.scatter_reads(reads, rank, world, dist, with_names=False)
+assert again.n == mine.n and np.array_equal(again.seqs, mine.seqs) and np.array_equal(again.offsets, mine.offsets)
+# packed result bytes of every rank arrive on rank 0 in rank order (sizes differ, one is empty)
+mineb = np.arange(1000 * rank + 7 * (1 - rank), dtype=np.int64).astype(np.uint8)
+got = shards.gather_bytes(mineb, rank, world, dist)
+if rank == 0:
+    assert [g.size for g in got] == [7, 1000] and np.array_equal(got[1], np.arange(1000).astype(np.uint8)) and np.array_equal(got[0], mineb)
+else:
+    assert got is None
+assert shards.gather_bytes(np.zeros(0, np.uint8), rank, world, dist) in (None,) or rank == 0
 b = shards.shard_bounds(101, world)
 assert mine.n == b[rank + 1] - b[rank], (mine.n, b)
 oi = orc.OracleIndex(ix)

@@ -6,5 +6,5 @@ python - <<PY
 import json
 d=json.load(open("$O/${TAG}_bench_default_n$N.json"))
 for name, r in (("C4", d), ("C5", d.get("long_reads"))):
-    print(name, "n_gpus", d["n_gpus"], "value", round(r["value"]), "e2e", round(r["e2e"]["value"]), "ms/step", round(r["ms_per_step"],1), "bcast_s", round(r["setup"]["index_broadcast_s"],2), "parity", r.get("parity_sample"))
+    print(name, "n_gpus", d["n_gpus"], "value", round(r["value"]), "e2e", round(r["e2e"]["value"]), "ms/step", round(r["ms_per_step"],1), "bcast_s", round(r["setup"]["index_broadcast_s"],2), "parity", r.get("parity_sample"), "sharded", r.get("e2e_sharded"))
 PY
