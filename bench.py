@@ -406,8 +406,9 @@ def gpu_record(G, name, wl, args):
     ms_dev_max, e2e_pin_max, e2e_pg_max = float(red[0]), float(red[1]), float(red[2])
     total_reads, total_aligned = float(tot[0]), float(tot[1])
     if rank != 0:
+        ix.free_device()                                        # with its workspace: the next workload sizes its trace pool by the free memory
         if not args.no_sharded:
-            G.keep.append((None, name, wl, ix, gix, batch))     # this rank's part of the sharded leg (after every record is complete)
+            G.keep.append((None, name, wl, ix, batch))          # this rank's part of the sharded leg (after every record is complete)
         return None
 
     K = args.steps
@@ -493,10 +494,9 @@ def gpu_record(G, name, wl, args):
         g.free()
         if bad:
             log("PARITY FAILURE on %s: %s differ from the oracle" % (name, bad))
+    ix.free_device()                                            # with its workspace: the next workload sizes its trace pool by the free memory
     if world > 1 and not args.no_sharded:
-        G.keep.append((rec, name, wl, ix, gix, batch))          # the sharded leg runs after every record is complete
-    else:
-        ix.free_device()
+        G.keep.append((rec, name, wl, ix, batch))               # the sharded leg runs after every record is complete
     return rec
 
 
@@ -527,7 +527,7 @@ def pack_results(vg, L, outs):
     return np.concatenate(parts) if parts else np.zeros(0, np.uint8)
 
 
-def sharded_leg(G, name, wl, ix, gix, batch, args):
+def sharded_leg(G, name, wl, ix, batch, args):
     """ONE process owns the reads and wants every result array back (what `vgaligner map` is): rank 0 holds the whole read set, scatters
     contiguous shards (host -> device -> NCCL -> device -> host), every rank maps its shard from host buffers through vga_map_batch,
     and the packed result arrays are gathered on rank 0.  One pass, caller's clock, barriers between the phases."""
@@ -544,6 +544,13 @@ def sharded_leg(G, name, wl, ix, gix, batch, args):
         torch.cuda.synchronize()
         dist.barrier()
 
+    # the device index again (the records above released theirs together with the workspaces): upload on rank 0 + ONE broadcast
+    cid = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        cid.copy_(torch.frombuffer(bytearray(vg.comm_unique_id()), dtype=torch.uint8))
+    dist.broadcast(cid, 0)
+    gix = vg.index_broadcast(ix.upload() if rank == 0 else None, bytes(cid.cpu().numpy().tobytes()), rank, world)
+    ix._gpu = gix
     t0 = time.perf_counter()
     whole = vg.simulate_reads_mt(ix, total, wl["length"], *wl["err"], 0.1, wl["seed"], first_id=0) if rank == 0 else None
     t_sim = time.perf_counter() - t0
@@ -670,9 +677,9 @@ def main():
         timer = threading.Timer(args.sharded_timeout, give_up)
         timer.daemon = True
         timer.start()
-        for rec, n, w, ix, gix, batch in G.keep:
+        for rec, n, w, ix, batch in G.keep:
             try:
-                res = sharded_leg(G, n, w, ix, gix, batch, args)
+                res = sharded_leg(G, n, w, ix, batch, args)
             except Exception as e:           # a rank that fails here leaves the others waiting: the timer ends the run
                 log("sharded leg of %s failed on rank %d: %r" % (n, rank, e))
                 res = {"error": repr(e)}

@@ -803,6 +803,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     pb.pool = w->b[B_POOL].get<u32>(want_words);
     pb.pool_words = std::min<u64>(std::min<u64>(w->b[B_POOL].cap / 4, (1ull << 34) - 16), pool_cap_env);
     tbuf.pool = pb.pool;
+    if (host_timeline()) fprintf(stderr, "[vga] trace pool: %.2f G words wanted, %.2f G in use (capped at %.2f G by the free memory seen when it last grew)\n",
+                                 (double)(est_total + est_total / 4 + warp_slack) / 1e9, (double)pb.pool_words / 1e9, (double)w->pool_capped_words / 1e9);
     tl_mark("pool ready");
     u32* d_work = w->b[B_WORK].get<u32>(NI);
     u32* d_twork = w->b[B_TWORK].get<u32>(NI);
