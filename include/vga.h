@@ -8,6 +8,11 @@
  * src/serialization.rs:52-53); vga_last_error() returns a thread-local message.  Nothing unwinds
  * across this boundary.  There is no CPU fallback: without a usable CUDA device every compute
  * entry point fails with VGA_ERR_NO_DEVICE.
+ *
+ * Threads: the device chosen by vga_init() belongs to the calling host thread (one thread or process per GPU).  A
+ * vga_index_t carries its own workspace (streams, trace pool): calls on ONE index are serialised by the library, calls on
+ * DIFFERENT indexes (also two uploads of the same index on one GPU) may run concurrently from different threads.  Result
+ * objects are independent of each other and of later calls.
  */
 #ifndef VGA_H
 #define VGA_H
