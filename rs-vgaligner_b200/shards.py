@@ -48,33 +48,40 @@ def shard_reads(reads, rank, world, with_names=True):
 def scatter_reads(reads, rank, world, dist, device=None, src=0, with_names=True):
     """Rank `src` holds `reads` (others pass None); every rank returns its shard.
 
-    Point-to-point sends, two tensors per shard (bytes, offsets); names stay on `src` (only the GAF
-    writer needs them and it runs where the names are)."""
+    The shard sizes travel by one small broadcast, the payloads (bytes, offsets) as ONE batch of point-to-point operations, so
+    the sends to different ranks are in flight together; names stay on `src` (only the GAF writer needs them and it runs where
+    the names are)."""
     import torch
     dev = device if device is not None else torch.device("cpu")
     if world == 1:
         return shard_reads(reads, 0, 1, with_names)
-    mine = None
-    meta = torch.zeros(2, dtype=torch.int64, device=dev)
-    for r in range(world):
-        if rank == src:
-            s = shard_reads(reads, r, world, with_names)
+    meta = torch.zeros(world, 2, dtype=torch.int64, device=dev)
+    parts = None
+    if rank == src:
+        parts = [shard_reads(reads, r, world, with_names) for r in range(world)]
+        meta.copy_(torch.tensor([[s.n, int(s.offsets[-1]) if s.n else 0] for s in parts], dtype=torch.int64))
+    dist.broadcast(meta, src)
+    ops, keep = [], []
+    if rank == src:
+        for r in range(world):
             if r == src:
-                mine = s
                 continue
-            meta[0], meta[1] = s.n, int(s.offsets[-1]) if s.n else 0
-            dist.send(meta, r)
-            dist.send(torch.from_numpy(s.seqs.copy()).to(dev) if s.seqs.size else torch.zeros(1, dtype=torch.uint8, device=dev), r)
-            dist.send(torch.from_numpy(s.offsets.astype(np.int64)).to(dev), r)
-        elif rank == r:
-            dist.recv(meta, src)
-            n, nb = int(meta[0]), int(meta[1])
-            seqs_t = torch.empty(max(nb, 1), dtype=torch.uint8, device=dev)
-            offs_t = torch.empty(n + 1, dtype=torch.int64, device=dev)
-            dist.recv(seqs_t, src)
-            dist.recv(offs_t, src)
-            mine = ReadShard(seqs_t.cpu().numpy()[:nb], offs_t.cpu().numpy().astype(np.uint64))
-    return mine
+            s = parts[r]
+            seqs_t = torch.from_numpy(s.seqs.copy()).to(dev) if s.seqs.size else torch.zeros(1, dtype=torch.uint8, device=dev)
+            offs_t = torch.from_numpy(s.offsets.astype(np.int64)).to(dev)
+            keep += [seqs_t, offs_t]
+            ops += [dist.P2POp(dist.isend, seqs_t, r), dist.P2POp(dist.isend, offs_t, r)]
+    else:
+        n, nb = int(meta[rank, 0]), int(meta[rank, 1])
+        seqs_t = torch.empty(max(nb, 1), dtype=torch.uint8, device=dev)
+        offs_t = torch.empty(n + 1, dtype=torch.int64, device=dev)
+        ops = [dist.P2POp(dist.irecv, seqs_t, src), dist.P2POp(dist.irecv, offs_t, src)]
+    if ops:
+        for q in dist.batch_isend_irecv(ops):
+            q.wait()
+    if rank == src:
+        return parts[src]
+    return ReadShard(seqs_t.cpu().numpy()[:nb], offs_t.cpu().numpy().astype(np.uint64))
 
 
 def broadcast_image(image, rank, dist, device=None, src=0):
@@ -101,7 +108,7 @@ def gather_text(text, rank, world, dist, dst=0):
 
 def gather_bytes(buf, rank, world, dist, device=None, dst=0):
     """Every rank contributes a uint8 numpy array (its packed result arrays); `dst` returns all of them in rank order,
-    the other ranks None.  Sizes travel by one all_gather, payloads point to point."""
+    the other ranks None.  Sizes travel by one all_gather, payloads as ONE batch of point-to-point operations."""
     import torch
     if world == 1:
         return [buf]
@@ -109,15 +116,11 @@ def gather_bytes(buf, rank, world, dist, device=None, dst=0):
     sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
     dist.all_gather(sizes, torch.tensor([buf.size], dtype=torch.int64, device=dev))
     if rank != dst:
-        dist.send(torch.from_numpy(buf).to(dev) if buf.size else torch.zeros(1, dtype=torch.uint8, device=dev), dst)
+        t = torch.from_numpy(buf).to(dev) if buf.size else torch.zeros(1, dtype=torch.uint8, device=dev)
+        for q in dist.batch_isend_irecv([dist.P2POp(dist.isend, t, dst)]):
+            q.wait()
         return None
-    out = []
-    for r in range(world):
-        if r == dst:
-            out.append(buf)
-            continue
-        n = int(sizes[r].item())
-        t = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
-        dist.recv(t, r)
-        out.append(t.cpu().numpy()[:n])
-    return out
+    bufs = {r: torch.empty(max(int(sizes[r].item()), 1), dtype=torch.uint8, device=dev) for r in range(world) if r != dst}
+    for q in dist.batch_isend_irecv([dist.P2POp(dist.irecv, bufs[r], r) for r in bufs]):
+        q.wait()
+    return [buf if r == dst else bufs[r].cpu().numpy()[:int(sizes[r].item())] for r in range(world)]
