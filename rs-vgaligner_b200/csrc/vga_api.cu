@@ -70,6 +70,8 @@ struct vga_workspace {
     std::vector<u64> h_est;
     std::vector<u32> h_key;
     std::vector<std::vector<u32>> h_cls;
+    std::vector<u64> h_off;      // read offsets of the call on the host (chunking); kept for the same reason
+    std::vector<u32> h_trace;    // alignments that wait for their traceback
 };
 
 namespace vga {
@@ -815,7 +817,8 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
     float ms_fill = 0, ms_trace = 0;
     // Fill launches of all classes share the trace pool; the traceback of everything filled so far runs as ONE
     // launch when the pool is about to run out (or at the end), after which the pool starts over.
-    std::vector<u32> trace_list;
+    std::vector<u32>& trace_list = w->h_trace;
+    trace_list.clear();
     trace_list.reserve(NI);
     u64 pool_acc = warp_slack;                  // estimated words in use since the last traceback
     u64 used_prev = 0;                          // pool counter after the previous wave (timeline print only)
@@ -1234,7 +1237,7 @@ static int map_common(vga_index_t* ix, const char* seqs, const u64* seq_off, con
         memset(&R->stats, 0, sizeof(R->stats));
         cudaEvent_t t0 = c.ws->ev[11];
         g_d2h_bytes = 0;
-        std::vector<u64> h_off;
+        std::vector<u64>& h_off = c.ws->h_off;
         const char* d_seqs = d_seqs_in;
         const u64* d_off = d_off_in;
         VGA_CUDA(cudaEventRecord(t0, c.st));
