@@ -844,6 +844,17 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         pool_acc = warp_slack;
         used_prev = 0;
     };
+    // a traceback launched right behind its fill wave (below) is timed when the stream has passed it
+    bool trace_time_pending = false;
+    auto collect_trace_time = [&]() {
+        if (!trace_time_pending) return;
+        VGA_CUDA(cudaEventSynchronize(w->ev_e1));
+        float t = 0;
+        cudaEventElapsedTime(&t, w->ev_e0, w->ev_e1);
+        ms_trace += t;
+        if (host_timeline()) fprintf(stderr, "[vga] poa trace (behind the fill): %.3f ms\n", t);
+        trace_time_pending = false;
+    };
     // what a wave's statuses mean for the lists: retries move on (a wider class, or the same class again after a traceback
     // has emptied the pool), completed alignments wait for their traceback
     auto absorb = [&](int ci, const u32* wave, u32 nw, const u32* hs, bool traced, std::vector<u32>& again, u32& done) {
@@ -1005,37 +1016,40 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
             R.stats.poa_launches++;
             VGA_CUDA(cudaEventRecord(w->ev[9], st));
             if (early_n) { VGA_CUDA(cudaEventRecord(w->ev_stf, st)); st_fill_after_fork = true; }
-            // A wave that holds everything there is to align (the usual short-read batch) is traced right behind its fill,
-            // from the same work list, without the host round trip in between: the traceback skips every item whose status is
-            // not OK, and items a retry brings back are traced by the final flush as before.
-            bool traced_here = trace_list.empty() && pos == 0 && end == list.size() && early_n == 0;
-            for (int cj = ci + 1; cj < NCLS && traced_here; cj++) traced_here = cls[cj].empty();
-            if (traced_here) {
-                tbuf.n_items = nw; tbuf.work = d_work;
-                c.launches += launch_poa_trace(dv, tbuf, st);
-                stage_check(st, "poa_trace");
-                VGA_CUDA(cudaEventRecord(w->ev[10], st));
-            }
+            // A wave that starts on an empty pool (nothing else waits for a traceback) is traced right behind its fill, from the
+            // same work list, without the host round trip in between: the traceback skips every item whose status is not OK
+            // (items a retry brings back run and are traced again later), and the pool starts over for the next wave — the host
+            // reads the statuses while the traceback runs.
+            const bool traced_here = trace_list.empty() && fresh_pool && early_n == 0;
             item_status_kernel<<<(nw + 255) / 256, 256, 0, st>>>(items, d_work, nw, d_status);
             c.launches++;
             queue_chain_d2h();          // host-side queueing (and any pinned allocation) hides behind the fill kernel
             VGA_CUDA(cudaMemcpyAsync(h_status.data(), d_status, 4ull * nw, cudaMemcpyDeviceToHost, st));
             unsigned long long used_now = 0;
             VGA_CUDA(cudaMemcpyAsync(&used_now, ctr + 4, 8, cudaMemcpyDeviceToHost, st));
-            VGA_CUDA(cudaStreamSynchronize(st));
+            VGA_CUDA(cudaEventRecord(w->ev_fork, st));            // fill + statuses of this wave
+            if (traced_here) {
+                collect_trace_time();                             // the previous wave's traceback ended before this fill began
+                tbuf.n_items = nw; tbuf.work = d_work;
+                VGA_CUDA(cudaEventRecord(w->ev_e0, st));
+                c.launches += launch_poa_trace(dv, tbuf, st);
+                stage_check(st, "poa_trace");
+                VGA_CUDA(cudaEventRecord(w->ev_e1, st));
+                trace_time_pending = true;
+            }
+            VGA_CUDA(cudaEventSynchronize(w->ev_fork));
             float a = 0;
             cudaEventElapsedTime(&a, w->ev[8], w->ev[9]);
             ms_fill += a;
-            if (traced_here) {
-                float t = 0;
-                cudaEventElapsedTime(&t, w->ev[9], w->ev[10]);
-                ms_trace += t;
-                if (host_timeline()) fprintf(stderr, "[vga] poa trace (behind the fill): %u items, %.3f ms\n", nw, t);
-            }
             if (host_timeline()) fprintf(stderr, "[vga] poa fill class %d: %u items, %.3f ms (pool: %.2f of the estimate)\n", ci, nw, a,
                                          wave_est && used_now >= used_prev ? (double)(used_now - used_prev) / (double)wave_est : 0.0);
             used_prev = used_now;
             pool_acc = acc;
+            if (traced_here) {                       // everything complete in this wave has its traceback: the pool is free again
+                VGA_CUDA(cudaMemsetAsync(ctr + 4, 0, 8, st));
+                pool_acc = warp_slack;
+                used_prev = 0;
+            }
             std::vector<u32> again;
             u32 done = 0;
             absorb(ci, list.data() + pos, nw, h_status.data(), traced_here, again, done);
@@ -1053,6 +1067,7 @@ static bool process_chunk(Ctx& c, const char* d_seqs, const u64* d_seq_off, u32 
         }
     }
     collect_early();
+    collect_trace_time();
     flush_trace();
     VGA_CUDA(cudaEventRecord(w->ev[5], st));
     tl_mark("poa waves done");
