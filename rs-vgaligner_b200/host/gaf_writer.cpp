@@ -56,6 +56,25 @@ static const char DIG2[201] =
     "5051525354555657585960616263646566676869707172737475767778798081828384858687888990919293949596979899";
 
 static inline char* put_u64(char* p, uint64_t v) {
+    // the common sizes (offsets inside a node, read positions, node ids) straight into place, two digits at a time
+    if (v < 100) {
+        if (v < 10) { *p = (char)('0' + v); return p + 1; }
+        memcpy(p, DIG2 + 2 * v, 2);
+        return p + 2;
+    }
+    if (v < 10000) {
+        const unsigned hi = (unsigned)v / 100, lo = (unsigned)v % 100;
+        if (hi < 10) { *p++ = (char)('0' + hi); } else { memcpy(p, DIG2 + 2 * hi, 2); p += 2; }
+        memcpy(p, DIG2 + 2 * lo, 2);
+        return p + 2;
+    }
+    if (v < 100000000ull) {
+        const unsigned a = (unsigned)(v / 10000), b = (unsigned)(v % 10000);
+        p = put_u64(p, a);                                   // 1 .. 4 digits
+        memcpy(p, DIG2 + 2 * (b / 100), 2);
+        memcpy(p + 2, DIG2 + 2 * (b % 100), 2);
+        return p + 4;
+    }
     char tmp[20];
     int n = 0;
     while (v >= 100) { const uint64_t q = v / 100; const unsigned r = (unsigned)(v - q * 100); tmp[n++] = DIG2[2 * r + 1]; tmp[n++] = DIG2[2 * r]; v = q; }
@@ -112,6 +131,10 @@ static inline char* put_placeholder(char* p, const Job& J, uint32_t r) {
 static void format_chains(const Job& J, uint32_t r0, uint32_t r1, Buf& out) {
     const VgaResultsView& R = *J.R;
     const uint32_t k = J.ix->k;
+    uint64_t c_lo = 1, c_hi = 0;              // forward positions [c_lo, c_hi) of the cached node (empty at first)
+    uint32_t c_node = 0;
+    char c_txt[24];
+    size_t c_len = 0;
     for (uint32_t r = r0; r < r1; r++) {
         const size_t nl = J.names->len(r);
         if (R.chain_off[r] == R.chain_off[r + 1]) {
@@ -137,15 +160,28 @@ static void format_chains(const Job& J, uint32_t r0, uint32_t r1, Buf& out) {
                 // FORWARD start also from a reverse-strand position (src/chain.rs:96-121): u64 arithmetic, wrapping like a release build
                 const bool r1 = R.ca_tb[a] >> 31, r2 = R.ca_te[a] >> 31;
                 const uint64_t tb = R.ca_tb[a] & 0x7fffffffu, tei = (uint64_t)(R.ca_te[a] & 0x7fffffffu) - 1;      // get_end_seqpos_inclusive, src/chain.rs:65-70
-                const uint32_t n1 = J.tb->pos2node[r1 ? J.ix->seq_len - 1 - tb : tb], n2 = J.tb->pos2node[r2 ? J.ix->seq_len - 1 - tei : tei];
+                // consecutive anchors of a chain mostly stay on one node: the node of the previous position is tried first, and its
+                // decimal id is kept as text
+                const uint64_t f1 = r1 ? J.ix->seq_len - 1 - tb : tb, f2 = r2 ? J.ix->seq_len - 1 - tei : tei;
+                if (f1 < c_lo || f1 >= c_hi) {
+                    c_node = J.tb->pos2node[f1];
+                    c_lo = J.tb->starts[c_node - 1]; c_hi = J.tb->starts[c_node];
+                    c_len = (size_t)(put_u64(c_txt, c_node) - c_txt);
+                }
+                const uint64_t s1 = c_lo;
                 *p++ = '('; *p++ = r1 ? '<' : '>';
-                p = put_u64(p, n1);
+                memcpy(p, c_txt, 16); p += c_len;                  // a u32 id has at most 10 digits; the 16 bytes are inside the reserve
                 *p++ = ':';
-                p = put_u64(p, tb - J.tb->starts[n1 - 1]);
+                p = put_u64(p, tb - s1);
+                if (f2 < c_lo || f2 >= c_hi) {
+                    c_node = J.tb->pos2node[f2];
+                    c_lo = J.tb->starts[c_node - 1]; c_hi = J.tb->starts[c_node];
+                    c_len = (size_t)(put_u64(c_txt, c_node) - c_txt);
+                }
                 *p++ = ','; *p++ = r2 ? '<' : '>';
-                p = put_u64(p, n2);
+                memcpy(p, c_txt, 16); p += c_len;
                 *p++ = ':';
-                p = put_u64(p, tei - J.tb->starts[n2 - 1]);
+                p = put_u64(p, tei - c_lo);
                 *p++ = ')'; *p++ = ',';
             }
             p = PUT_LIT(p, "\t0\t0\t0\t0\t0\t0\tta:Z:chain,n_anchors: ");
