@@ -51,6 +51,29 @@ struct Buf {
     char* cur() { return v.data() + n; }
 };
 
+// buffers of finished calls, reused by later ones (any thread); at most POOL_MAX of at most POOL_BYTES each are kept
+static std::mutex g_buf_mu;
+static std::vector<Buf*> g_buf_pool;
+static const size_t POOL_MAX = 64, POOL_BYTES = 256u << 20;
+struct BufLease {
+    std::vector<Buf*> b;
+    explicit BufLease(int n) : b((size_t)n, nullptr) {
+        std::lock_guard<std::mutex> lk(g_buf_mu);
+        for (auto& x : b) {
+            if (!g_buf_pool.empty()) { x = g_buf_pool.back(); g_buf_pool.pop_back(); }
+            else x = new Buf();
+        }
+    }
+    ~BufLease() {
+        std::lock_guard<std::mutex> lk(g_buf_mu);
+        for (Buf* x : b) {
+            if (g_buf_pool.size() < POOL_MAX && x->v.size() <= POOL_BYTES) g_buf_pool.push_back(x);
+            else delete x;
+        }
+    }
+    Buf& operator[](int t) { return *b[(size_t)t]; }
+};
+
 static const char DIG2[201] =
     "0001020304050607080910111213141516171819202122232425262728293031323334353637383940414243444546474849"
     "5051525354555657585960616263646566676869707172737475767778798081828384858687888990919293949596979899";
@@ -308,10 +331,14 @@ char* gaf_format(const FlatIndex& ix, const GafTables& tb, const VgaResultsView*
             while (t < T && acc >= total * (uint64_t)t / (uint64_t)T) cut[t++] = r + 1;
         }
     }
-    std::vector<Buf> bufs(T);
+    // per-thread buffers come from a small pool and keep their size between calls: a fresh buffer is zero-filled and page-faulted
+    // in by 16 threads at once, which cost more than the formatting itself
+    BufLease bufs(T);
     std::vector<uint64_t> failed(T, 0);
     auto work = [&](int t) {
-        bufs[t].v.resize((size_t)((which == 0 ? 40 : 24) * (total / (uint64_t)T + 64)) + (1u << 16));
+        const size_t want = (size_t)((which == 0 ? 40 : 24) * (total / (uint64_t)T + 64)) + (1u << 16);
+        bufs[t].n = 0;
+        if (bufs[t].v.size() < want) bufs[t].v.resize(want);
         if (which == 0) format_chains(J, cut[t], cut[t + 1], bufs[t]);
         else format_alignments(J, cut[t], cut[t + 1], bufs[t], failed[t]);
     };
