@@ -425,6 +425,18 @@ def test_c3_full_shard_size(graph, n):
     assert_same(g, o, FULL)
 
 
+@pytest.mark.parametrize("bandwidth,max_gap", [(1, 1000), (20, 1000), (32, 1000), (33, 1000), (50, 100), (50, 2000), (64, 1000), (65, 1000), (96, 500)])
+def test_chaining_parameters(bandwidth, max_gap):
+    """chain_anchors with other windows and gap limits than map_main's (bandwidth 50 is fixed there, -g sets max_gap): windows up to
+    32 predecessors (near half only), 33..64 (far half evaluated on demand), above 64 (the generic f64 body); sorted order, DP
+    scores, predecessors and chains against the oracle on reads with spurious anchors (k = 7 on DRB1-3123)."""
+    ix = vg.Index.build(fixture_path("graphs/2-DRB1-3123.gfa"), 7)
+    reads = vg.simulate_reads(ix, 300, 150, 0.02, 0.002, 0.002, 0.1, 31)
+    g, o = both(ix, reads, bandwidth=bandwidth, max_gap=max_gap, flags=vg.VGA_FLAG_NO_ALIGN)
+    assert_same(g, o, SEED + SORT + CHAIN)
+    assert int(g.chain_off[-1]) > 100
+
+
 def test_failed_alignment_status_reaches_the_gaf_text(synth, monkeypatch):
     """A device alignment that did not complete (status other than OK / PLACEHOLDER; patched into real results here, the
     inputs of this suite never produce one) is written as a placeholder line and counted, never as a well-formed record."""
