@@ -437,6 +437,21 @@ def test_chaining_parameters(bandwidth, max_gap):
     assert int(g.chain_off[-1]) > 100
 
 
+@pytest.mark.parametrize("kw", [dict(match=1, mismatch=3, o1=5, e1=2, o2=20, e2=1), dict(wb=5, wf=0.03), dict(match=3, mismatch=5, wb=20, wf=0.0),
+                                dict(match=2, mismatch=6, o1=6, e1=3, o2=30, e2=2, wb=8, wf=0.02)])
+def test_other_scoring_and_band_parameters(synth, kw):
+    """The POA with other scores, gap models and band parameters than abPOA's defaults (inside the range map_common admits): the
+    16x2 kernel is compiled for the default gap model, so these go through the 32-lane group kernel (short reads) and the
+    shared-memory / SLIDE kernels (long reads) — every alignment array against the oracle."""
+    ix = vg.Index.build(fixture_path("graphs/2-DRB1-3123.gfa"), 11)
+    g, o = both(ix, vg.simulate_reads(ix, 400, 150, 0.02, 0.002, 0.002, 0.1, 61), **kw)
+    check_all(g, o)
+    assert (g.aln_status == vg.ALN_OK).sum() > 300
+    g, o = both(synth, vg.simulate_reads(synth, 24, 3000, 0.03, 0.02, 0.02, 0.1, 62), **kw)
+    check_all(g, o)
+    assert (g.aln_status == vg.ALN_OK).sum() >= 16
+
+
 def test_failed_alignment_status_reaches_the_gaf_text(synth, monkeypatch):
     """A device alignment that did not complete (status other than OK / PLACEHOLDER; patched into real results here, the
     inputs of this suite never produce one) is written as a placeholder line and counted, never as a well-formed record."""
