@@ -25,6 +25,12 @@ def test_header_symbols_are_exported():
     assert sorted(vg.GPU_SYMBOLS) == names
 
 
+def test_integration_binding_lists_every_symbol():
+    """The Rust extern block of INTEGRATION.md declares exactly the functions of include/vga.h."""
+    text = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    assert sorted(set(re.findall(r"pub fn (vga_[a-z0-9_]+)", text))) == declared_symbols()
+
+
 def test_no_oracle_in_product():
     """Nothing under the package or the CUDA library refers to oracle/."""
     pkg = os.path.join(ROOT, "rs-vgaligner_b200")
