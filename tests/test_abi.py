@@ -31,6 +31,40 @@ def test_integration_binding_lists_every_symbol():
     assert sorted(set(re.findall(r"pub fn (vga_[a-z0-9_]+)", text))) == declared_symbols()
 
 
+def header_structs():
+    """field names, in order, of every `typedef struct { ... } Name;` of include/vga.h"""
+    text = open(os.path.join(ROOT, "include", "vga.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    out = {}
+    for m in re.finditer(r"typedef\s+struct\s*\w*\s*\{(.*?)\}\s*(\w+)\s*;", text, flags=re.S):
+        fields = []
+        for decl in m.group(1).split(";"):
+            for part in decl.strip().split(","):
+                if part.strip():
+                    fields.append(re.findall(r"(\w+)\s*(?:\[\d+\])?$", part.strip())[0])
+        out[m.group(2)] = fields
+    return out
+
+
+def test_struct_fields_agree_between_header_ctypes_and_rust():
+    """Same field names in the same order in include/vga.h, the ctypes mirror and the #[repr(C)] structs of INTEGRATION.md
+    (Rust spells `match` as `match_` and folds the trailing debug pointers into one array)."""
+    structs = header_structs()
+    assert set(structs) >= {"VgaIndexView", "VgaParams", "VgaResultsView", "VgaStats", "VgaGraphView"}
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    for name, fields in structs.items():
+        assert [f for f, _ in getattr(vg, name)._fields_] == fields, name
+        m = re.search(r"pub struct " + name + r"\s*\{(.*?)\n\}", doc, flags=re.S)
+        assert m, name + " has no #[repr(C)] struct in INTEGRATION.md"
+        body = re.sub(r"//[^\n]*", "", m.group(1))
+        rust = []
+        for fname, ftype in re.findall(r"pub (\w+)\s*:\s*([^,\n]+)", body):
+            arr = re.match(r"\[\*const c_void;\s*(\d+)\]", ftype.strip())
+            rust += [fname] * int(arr.group(1)) if arr else [fname.rstrip("_")]
+        expect = [("dbg" if f.startswith("dbg_") else f) for f in fields]
+        assert rust == expect, (name, rust, expect)
+
+
 def test_no_oracle_in_product():
     """Nothing under the package or the CUDA library refers to oracle/."""
     pkg = os.path.join(ROOT, "rs-vgaligner_b200")
